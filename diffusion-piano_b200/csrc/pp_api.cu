@@ -1,0 +1,454 @@
+// pp_api.cu - the C-ABI of include/piano_step.h: handle lifetime, model upload, launches.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/piano_step.h"
+#include "pp_env.cuh"
+
+static thread_local std::string g_err;
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+#define CUDA_OK(expr)                                                                        \
+  do {                                                                                       \
+    cudaError_t e_ = (expr);                                                                 \
+    if (e_ != cudaSuccess) return fail(PP_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+
+struct pp_env {
+  pp_config cfg;
+  int nv, nu, action_dim, obs_dim, nsite;
+  DevModel* dm = nullptr;
+  uint8_t* goal = nullptr;
+  int16_t* pairs = nullptr;
+  float *qpos = nullptr, *qvel = nullptr, *warm = nullptr, *sustain = nullptr, *qfrc_applied = nullptr;
+  int* t_idx = nullptr;
+  uint8_t* needs_reset = nullptr;
+  float *qacc = nullptr, *act_force = nullptr, *act_vel = nullptr, *site_xpos = nullptr;
+  uint8_t* activation = nullptr;
+  int* counters = nullptr;
+  float *act_min_d = nullptr, *act_max_d = nullptr;
+  std::vector<float> act_min, act_max;
+  bool use_applied = false;
+  long long launches = 0;
+  // host-buffer path
+  cudaStream_t hstream = nullptr;
+  float *h_actions = nullptr, *h_obs = nullptr, *h_reward = nullptr, *h_terms = nullptr, *h_discount = nullptr;
+  uint8_t* h_done = nullptr;
+  float *d_actions = nullptr, *d_obs = nullptr, *d_reward = nullptr, *d_terms = nullptr, *d_discount = nullptr;
+  uint8_t *d_done = nullptr, *d_mask = nullptr;
+};
+
+static void f3cpy(float* dst, const double* src, int n = 3) {
+  for (int i = 0; i < n; i++) dst[i] = (float)src[i];
+}
+
+// Convert the generic tables into the fixed-structure fp32 image; verify the structure.
+static int build_dev_model(const pp_model* m, DevModel* out) {
+  DevModel& d = *out;
+  memset(&d, 0, sizeof(d));
+  if (m->nkey != PP_NKEY) return fail(PP_ERR_UNSUPPORTED, "model must have 88 keys");
+  const int nv_expected = PP_NKEY + (m->has_hands ? PP_NHD : 0);
+  if (m->nv != nv_expected) return fail(PP_ERR_UNSUPPORTED, "nv=%d, expected %d", m->nv, nv_expected);
+  Options& o = d.opt;
+  o.h = (float)m->timestep; f3cpy(o.g, m->gravity);
+  o.impratio = (float)m->impratio; o.tolerance = (float)m->tolerance; o.meaninertia = (float)m->meaninertia;
+  o.iterations = m->iterations; o.ls_iterations = m->ls_iterations;
+  f3cpy(o.limit_solref, m->limit_solref, 2); f3cpy(o.limit_solimp, m->limit_solimp, 5);
+  f3cpy(o.friction_solref, m->friction_solref, 2); f3cpy(o.friction_solimp, m->friction_solimp, 5);
+  for (int c = 0; c < 2; c++) {
+    f3cpy(o.pair_solref[c], m->pair_solref[c], 2); f3cpy(o.pair_solimp[c], m->pair_solimp[c], 5);
+    o.pair_friction[c] = (float)m->pair_friction[c]; o.pair_margin[c] = (float)m->pair_margin[c];
+  }
+  // ---- keys: dof k, body k+1, geom k (hinge about +y through body_pos + jnt_pos)
+  KeyTables& kt = d.key;
+  const double g = -m->gravity[2];
+  for (int k = 0; k < PP_NKEY; k++) {
+    int b = k + 1;
+    if (m->jnt_body[k] != b || m->jnt_type[k] != PP_JNT_HINGE || m->geom_body[k] != b ||
+        m->geom_type[k] != PP_GEOM_BOX || m->body_parent[b] != 0)
+      return fail(PP_ERR_UNSUPPORTED, "key %d does not have the expected body/joint/geom layout", k);
+    const double* ax = m->jnt_axis + 3 * k;
+    if (ax[0] != 0 || ax[1] != 1 || ax[2] != 0) return fail(PP_ERR_UNSUPPORTED, "key axis must be +y");
+    double hx = -m->jnt_pos[3 * k];  // COM is hx in front of the hinge
+    double mass = m->body_mass[b];
+    double Iyy = m->body_inertia[3 * b + 1];
+    kt.M[k] = (float)(Iyy + mass * hx * hx + m->dof_armature[k]);
+    kt.mghx[k] = (float)(mass * g * hx);
+    kt.hi[k] = (float)m->jnt_range[2 * k + 1];
+    kt.invw[k] = (float)m->dof_invweight0[k];
+    kt.binvw[k] = (float)m->body_invweight0[2 * b];
+    f3cpy(kt.pos[k], m->body_pos + 3 * b);
+    f3cpy(kt.half[k], m->geom_size + 3 * k);
+    if (m->jnt_range[2 * k] != 0) return fail(PP_ERR_UNSUPPORTED, "key range must start at 0");
+  }
+  kt.stiffness = (float)m->jnt_stiffness[0]; kt.springref = (float)m->jnt_springref[0];
+  kt.damping = (float)m->dof_damping[0];
+  for (int k = 0; k < PP_NKEY; k++) d.key_ctrl_hi[k] = kt.hi[k];
+  if (m->nu >= PP_NKEY && !m->has_hands)
+    for (int k = 0; k < PP_NKEY; k++) d.key_ctrl_hi[k] = (float)m->act_ctrlrange[2 * k + 1];
+  // white-key / black-key lookup by y (used by the key broad phase)
+  {
+    int nw = 0;
+    for (int n = 0; n < 53; n++) kt.boundary_black[n] = -1;
+    for (int k = 0; k < PP_NKEY; k++) {
+      bool black = kt.half[k][0] < 0.06f;
+      if (!black) kt.white_key[nw++] = (int8_t)k;
+      else kt.boundary_black[nw] = (int8_t)k;  // sits on the boundary before white #nw
+    }
+    if (nw != 52) return fail(PP_ERR_UNSUPPORTED, "expected 52 white keys, found %d", nw);
+  }
+  // base box = geom 88 on the world body
+  if (m->ngeom > PP_NKEY) {
+    f3cpy(o.base_pos, m->geom_pos + 3 * PP_NKEY);
+    f3cpy(o.base_half, m->geom_size + 3 * PP_NKEY);
+  }
+  if (!m->has_hands) return PP_OK;
+
+  // ---- hands: bodies 89.., dofs 88..; local layout forearm(2 slides) + 24 single-hinge bodies
+  HandTables& ht = d.hand;
+  const int b0 = PP_NKEY + 1, d0 = PP_NKEY;
+  if (m->nbody != b0 + PP_NHB) return fail(PP_ERR_UNSUPPORTED, "nbody=%d unexpected", m->nbody);
+  for (int hb = 0; hb < PP_NHB; hb++) {
+    int b = b0 + hb, h = hb / PP_HB, lb = hb % PP_HB;
+    int expect_adr = d0 + h * PP_HD + (lb == 0 ? 0 : lb + 1), expect_num = lb == 0 ? 2 : 1;
+    if (m->body_dofadr[b] != expect_adr || m->body_dofnum[b] != expect_num)
+      return fail(PP_ERR_UNSUPPORTED, "hand body %d has an unexpected dof layout", hb);
+    int p = m->body_parent[b];
+    if (lb == 0 ? p != 0 : (p < b0 + h * PP_HB || p >= b))
+      return fail(PP_ERR_UNSUPPORTED, "hand body %d has an unexpected parent", hb);
+    f3cpy(ht.body_pos[hb], m->body_pos + 3 * b); f3cpy(ht.body_quat[hb], m->body_quat + 4 * b, 4);
+    f3cpy(ht.ipos[hb], m->body_ipos + 3 * b); f3cpy(ht.iquat[hb], m->body_iquat + 4 * b, 4);
+    ht.mass[hb] = (float)m->body_mass[b]; f3cpy(ht.inertia[hb], m->body_inertia + 3 * b);
+    ht.gravcomp[hb] = (float)m->body_gravcomp[b]; ht.binvw[hb] = (float)m->body_invweight0[2 * b];
+  }
+  for (int hd = 0; hd < PP_NHD; hd++) {
+    int j = d0 + hd, ld = hd % PP_HD;
+    int want = ld < 2 ? PP_JNT_SLIDE : PP_JNT_HINGE;
+    if (m->jnt_type[j] != want) return fail(PP_ERR_UNSUPPORTED, "hand dof %d has an unexpected type", hd);
+    const double* jp = m->jnt_pos + 3 * j;
+    if (jp[0] != 0 || jp[1] != 0 || jp[2] != 0) return fail(PP_ERR_UNSUPPORTED, "hand joint anchors must be 0");
+    if (m->jnt_stiffness[j] != 0 || !m->jnt_limited[j] || m->qpos0[j] != 0)
+      return fail(PP_ERR_UNSUPPORTED, "hand dof %d: springs / unlimited joints / qpos0 != 0 unsupported", hd);
+    f3cpy(ht.axis[hd], m->jnt_axis + 3 * j); f3cpy(ht.range[hd], m->jnt_range + 2 * j, 2);
+    ht.damping[hd] = (float)m->dof_damping[j]; ht.armature[hd] = (float)m->dof_armature[j];
+    ht.frictionloss[hd] = (float)m->dof_frictionloss[j]; ht.invw[hd] = (float)m->dof_invweight0[j];
+  }
+  // parent table check: finger chains (local bodies) 3-6, 7-10, 11-14, 15-19, 20-24 hang off the palm (2)
+  static const int kStart[5] = {3, 7, 11, 15, 20}, kLen[5] = {4, 4, 4, 5, 5};
+  for (int h = 0; h < 2; h++) {
+    auto par = [&](int lb) { return m->body_parent[b0 + h * PP_HB + lb] - (b0 + h * PP_HB); };
+    if (par(1) != 0 || par(2) != 1) return fail(PP_ERR_UNSUPPORTED, "wrist/palm chain unexpected");
+    for (int f = 0; f < 5; f++)
+      for (int i = 0; i < kLen[f]; i++)
+        if (par(kStart[f] + i) != (i == 0 ? 2 : kStart[f] + i - 1))
+          return fail(PP_ERR_UNSUPPORTED, "finger %d chain unexpected", f);
+  }
+  // collider geoms (after the 88 key boxes and the base box)
+  ht.ngeom = m->ngeom - (PP_NKEY + 1);
+  if (ht.ngeom > PP_MAXGEOM) return fail(PP_ERR_UNSUPPORTED, "too many hand geoms");
+  for (int hg = 0; hg < ht.ngeom; hg++) {
+    int g_ = PP_NKEY + 1 + hg, b = m->geom_body[g_];
+    if (m->geom_type[g_] != PP_GEOM_CAPSULE && m->geom_type[g_] != PP_GEOM_SPHERE)
+      return fail(PP_ERR_UNSUPPORTED, "hand colliders must be capsules or spheres");
+    const double* gq = m->geom_quat + 4 * g_;
+    if (gq[0] != 1) return fail(PP_ERR_UNSUPPORTED, "hand collider axes must be body-z aligned");
+    ht.geom_body[hg] = (int8_t)(b - b0); ht.geom_cls[hg] = (int8_t)m->geom_cls[g_];
+    f3cpy(ht.geom_pos[hg], m->geom_pos + 3 * g_);
+    ht.geom_r[hg] = (float)m->geom_size[3 * g_];
+    ht.geom_hl[hg] = m->geom_type[g_] == PP_GEOM_CAPSULE ? (float)m->geom_size[3 * g_ + 1] : 0.f;
+    // dof chain, root first
+    int chain[64], n = 0;
+    for (int bb = b; bb > 0; bb = m->body_parent[bb])
+      for (int k = m->body_dofnum[bb] - 1; k >= 0; k--) chain[n++] = m->body_dofadr[bb] + k - d0;
+    if (n > PP_MAXCHAIN) return fail(PP_ERR_UNSUPPORTED, "dof chain too long");
+    ht.geom_nchain[hg] = (int8_t)n;
+    for (int i = 0; i < n; i++) ht.geom_chain[hg][i] = (int8_t)chain[n - 1 - i];
+  }
+  if (m->npair > PP_MAXPAIR) return fail(PP_ERR_UNSUPPORTED, "too many fixed geom pairs");
+  ht.npair = m->npair;
+  for (int p = 0; p < m->npair; p++) {
+    ht.pair_g1[p] = (int8_t)(m->pair_geom1[p] - (PP_NKEY + 1));
+    ht.pair_g2[p] = (int8_t)(m->pair_geom2[p] - (PP_NKEY + 1));
+  }
+  if (m->nsite != PP_NSITE) return fail(PP_ERR_UNSUPPORTED, "expected 10 fingertip sites");
+  for (int s = 0; s < PP_NSITE; s++) {
+    ht.site_body[s] = (int8_t)(m->site_body[s] - b0);
+    f3cpy(ht.site_pos[s], m->site_pos + 3 * s);
+  }
+  if (m->nu != PP_NU_HANDS) return fail(PP_ERR_UNSUPPORTED, "expected 44 hand actuators");
+  for (int i = 0; i < PP_NU_HANDS; i++) {
+    ht.act_trn0[i] = (int8_t)(m->act_trn0[i] - d0);
+    ht.act_trn1[i] = (int8_t)(m->act_trn1[i] >= 0 ? m->act_trn1[i] - d0 : -1);
+    ht.act_forcelimited[i] = (int8_t)m->act_forcelimited[i];
+    ht.act_kp[i] = (float)m->act_kp[i];
+    f3cpy(ht.act_ctrlrange[i], m->act_ctrlrange + 2 * i, 2);
+    f3cpy(ht.act_forcerange[i], m->act_forcerange + 2 * i, 2);
+    if (m->act_gain_only[i]) return fail(PP_ERR_UNSUPPORTED, "hand actuators must be position servos");
+  }
+  return PP_OK;
+}
+
+// ------------------------------------------------------------------ handle lifetime
+template <typename T>
+static cudaError_t dalloc(T** p, size_t n) {
+  cudaError_t e = cudaMalloc((void**)p, (n ? n : 1) * sizeof(T));
+  if (e == cudaSuccess) e = cudaMemset(*p, 0, (n ? n : 1) * sizeof(T));
+  return e;
+}
+
+extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** out) {
+  if (!model || !cfg || !out) return fail(PP_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (cfg->num_envs <= 0 || cfg->n_frames <= 0 || cfg->n_substeps <= 0 || !cfg->goal)
+    return fail(PP_ERR_INVALID, "num_envs, n_frames, n_substeps must be > 0 and goal non-null");
+  if (cfg->n_steps_lookahead < 0) return fail(PP_ERR_INVALID, "n_steps_lookahead must be >= 0");
+  const bool hands = cfg->task == PP_TASK_PIANO_WITH_SHADOW_HANDS;
+  if (hands != (model->has_hands != 0)) return fail(PP_ERR_INVALID, "task / model mismatch");
+  if (hands && cfg->has_fingering && !cfg->pairs) return fail(PP_ERR_INVALID, "pairs table required");
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev == 0)
+    return fail(PP_ERR_CUDA, "no CUDA device available (%s); there is no CPU fallback",
+                cudaGetErrorString(ce));
+  CUDA_OK(cudaSetDevice(cfg->device));
+  DevModel* hm = new DevModel;
+  int rc = build_dev_model(model, hm);
+  if (rc != PP_OK) { delete hm; return rc; }
+  pp_env* e = new pp_env;
+  e->cfg = *cfg;
+  e->nv = model->nv; e->nu = model->nu; e->nsite = model->nsite;
+  const int N = cfg->num_envs, L = cfg->n_steps_lookahead;
+  if (hands) {
+    e->action_dim = 45;
+    e->obs_dim = (L + 1) * 89 + (cfg->has_fingering ? 10 : 0) + 88 + 1 + 26 + 26;
+    e->act_min.resize(45); e->act_max.resize(45);
+    for (int i = 0; i < 44; i++) {
+      e->act_min[i] = (float)model->act_ctrlrange[2 * i];
+      e->act_max[i] = (float)model->act_ctrlrange[2 * i + 1];
+    }
+    e->act_min[44] = 0.f; e->act_max[44] = 1.f;
+  } else {
+    e->action_dim = 89;
+    e->obs_dim = (L + 1) * 89 + 88 + 1;
+    e->act_min.assign(89, 0.f); e->act_max.resize(89);
+    for (int k = 0; k < 88; k++) e->act_max[k] = hm->key_ctrl_hi[k];
+    e->act_max[88] = 1.f;
+  }
+  CUDA_OK(dalloc(&e->dm, 1));
+  CUDA_OK(cudaMemcpy(e->dm, hm, sizeof(DevModel), cudaMemcpyHostToDevice));
+  delete hm;
+  const size_t T = cfg->n_frames;
+  CUDA_OK(dalloc(&e->goal, T * 89));
+  CUDA_OK(cudaMemcpy(e->goal, cfg->goal, T * 89, cudaMemcpyHostToDevice));
+  if (cfg->pairs && cfg->pmax > 0) {
+    CUDA_OK(dalloc(&e->pairs, T * cfg->pmax * 2));
+    CUDA_OK(cudaMemcpy(e->pairs, cfg->pairs, T * cfg->pmax * 2 * sizeof(int16_t), cudaMemcpyHostToDevice));
+  }
+  e->cfg.goal = nullptr; e->cfg.pairs = nullptr;
+  const size_t nv = e->nv;
+  CUDA_OK(dalloc(&e->qpos, N * nv)); CUDA_OK(dalloc(&e->qvel, N * nv)); CUDA_OK(dalloc(&e->warm, N * nv));
+  CUDA_OK(dalloc(&e->qfrc_applied, N * nv)); CUDA_OK(dalloc(&e->qacc, N * nv));
+  CUDA_OK(dalloc(&e->sustain, N)); CUDA_OK(dalloc(&e->t_idx, N)); CUDA_OK(dalloc(&e->needs_reset, N));
+  CUDA_OK(dalloc(&e->act_force, (size_t)N * (e->nu ? e->nu : 1)));
+  CUDA_OK(dalloc(&e->act_vel, (size_t)N * (e->nu ? e->nu : 1)));
+  CUDA_OK(dalloc(&e->site_xpos, (size_t)N * 3 * PP_NSITE));
+  CUDA_OK(dalloc(&e->activation, (size_t)N * 88)); CUDA_OK(dalloc(&e->counters, (size_t)N * 4));
+  CUDA_OK(dalloc(&e->act_min_d, e->action_dim)); CUDA_OK(dalloc(&e->act_max_d, e->action_dim));
+  CUDA_OK(cudaMemcpy(e->act_min_d, e->act_min.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy(e->act_max_d, e->act_max.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
+  // host-buffer path: pinned staging + device mirrors
+  CUDA_OK(cudaStreamCreateWithFlags(&e->hstream, cudaStreamNonBlocking));
+  CUDA_OK(cudaMallocHost((void**)&e->h_actions, (size_t)N * e->action_dim * 4));
+  CUDA_OK(cudaMallocHost((void**)&e->h_obs, (size_t)N * e->obs_dim * 4));
+  CUDA_OK(cudaMallocHost((void**)&e->h_reward, (size_t)N * 4));
+  CUDA_OK(cudaMallocHost((void**)&e->h_terms, (size_t)N * 5 * 4));
+  CUDA_OK(cudaMallocHost((void**)&e->h_discount, (size_t)N * 4));
+  CUDA_OK(cudaMallocHost((void**)&e->h_done, (size_t)N));
+  CUDA_OK(dalloc(&e->d_actions, (size_t)N * e->action_dim)); CUDA_OK(dalloc(&e->d_obs, (size_t)N * e->obs_dim));
+  CUDA_OK(dalloc(&e->d_reward, N)); CUDA_OK(dalloc(&e->d_terms, (size_t)N * 5));
+  CUDA_OK(dalloc(&e->d_discount, N)); CUDA_OK(dalloc(&e->d_done, N)); CUDA_OK(dalloc(&e->d_mask, N));
+  *out = e;
+  int r = pp_reset(e, nullptr, nullptr, nullptr);
+  if (r != PP_OK) return r;
+  CUDA_OK(cudaDeviceSynchronize());
+  return PP_OK;
+}
+
+extern "C" int pp_destroy(pp_env* e) {
+  if (!e) return PP_OK;
+  cudaSetDevice(e->cfg.device);
+  cudaDeviceSynchronize();
+  void* dev[] = {e->dm, e->goal, e->pairs, e->qpos, e->qvel, e->warm, e->sustain, e->qfrc_applied, e->t_idx,
+                 e->needs_reset, e->qacc, e->act_force, e->act_vel, e->site_xpos, e->activation, e->counters,
+                 e->act_min_d, e->act_max_d, e->d_actions, e->d_obs, e->d_reward, e->d_terms, e->d_discount,
+                 e->d_done, e->d_mask};
+  for (void* p : dev) if (p) cudaFree(p);
+  void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
+  for (void* p : host) if (p) cudaFreeHost(p);
+  if (e->hstream) cudaStreamDestroy(e->hstream);
+  delete e;
+  return PP_OK;
+}
+
+extern "C" int pp_num_envs(const pp_env* e) { return e ? e->cfg.num_envs : 0; }
+extern "C" int pp_nv(const pp_env* e) { return e ? e->nv : 0; }
+extern "C" int pp_action_dim(const pp_env* e) { return e ? e->action_dim : 0; }
+extern "C" int pp_obs_dim(const pp_env* e) { return e ? e->obs_dim : 0; }
+extern "C" long long pp_launch_count(const pp_env* e) { return e ? e->launches : 0; }
+extern "C" const char* pp_last_error(void) { return g_err.c_str(); }
+extern "C" const char* pp_version(void) { return "piano_step 0.1 (sm_100a)"; }
+extern "C" int pp_action_bounds(const pp_env* e, float* lo, float* hi) {
+  if (!e || !lo || !hi) return fail(PP_ERR_INVALID, "null argument");
+  memcpy(lo, e->act_min.data(), e->action_dim * 4);
+  memcpy(hi, e->act_max.data(), e->action_dim * 4);
+  return PP_OK;
+}
+
+// ------------------------------------------------------------------ launches
+static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions, float* obs, float* reward,
+                  float* terms, uint8_t* done, float* discount, cudaStream_t s) {
+  const pp_config& c = e->cfg;
+  if (c.task == PP_TASK_SELF_ACTUATED_PIANO) {
+    PianoOnlyArgs A;
+    memset(&A, 0, sizeof(A));
+    A.dm = e->dm; A.num_envs = c.num_envs; A.mode = mode; A.n_substeps = c.n_substeps;
+    A.n_frames = c.n_frames; A.lookahead = c.n_steps_lookahead; A.obs_dim = e->obs_dim;
+    A.canonical = c.canonical_actions; A.reward_type = c.reward_type; A.auto_reset = c.auto_reset;
+    A.goal = e->goal; A.reset_mask = mask; A.actions = actions;
+    A.qfrc_applied = e->use_applied ? e->qfrc_applied : nullptr;
+    A.qpos = e->qpos; A.qvel = e->qvel; A.t_idx = e->t_idx; A.sustain = e->sustain;
+    A.needs_reset = e->needs_reset; A.obs = obs; A.reward = reward; A.reward_terms = terms;
+    A.discount = discount; A.done = done; A.qacc = e->qacc; A.activation = e->activation;
+    pp_launch_piano_only(A, s);
+  } else {
+    HandsArgs A;
+    memset(&A, 0, sizeof(A));
+    A.dm = e->dm; A.num_envs = c.num_envs; A.mode = mode; A.n_substeps = c.n_substeps;
+    A.n_frames = c.n_frames; A.lookahead = c.n_steps_lookahead; A.obs_dim = e->obs_dim; A.pmax = c.pmax;
+    A.canonical = c.canonical_actions; A.has_fingering = c.has_fingering;
+    A.disable_forearm_reward = c.disable_forearm_reward;
+    A.wrong_press_termination = c.wrong_press_termination; A.auto_reset = c.auto_reset;
+    A.max_contacts = c.max_contacts; A.energy_coef = (float)c.energy_penalty_coef;
+    A.goal = e->goal; A.pairs = e->pairs; A.reset_mask = mask; A.actions = actions;
+    A.act_min = e->act_min_d; A.act_max = e->act_max_d;
+    A.qfrc_applied = e->use_applied ? e->qfrc_applied : nullptr;
+    A.qpos = e->qpos; A.qvel = e->qvel; A.warm = e->warm; A.t_idx = e->t_idx; A.sustain = e->sustain;
+    A.needs_reset = e->needs_reset; A.obs = obs; A.reward = reward; A.reward_terms = terms;
+    A.discount = discount; A.done = done; A.qacc = e->qacc; A.act_force = e->act_force;
+    A.act_vel = e->act_vel; A.site_xpos = e->site_xpos; A.activation = e->activation;
+    A.counters = e->counters;
+    pp_launch_hands(A, s);
+  }
+  e->launches++;
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) return fail(PP_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(err));
+  return PP_OK;
+}
+
+extern "C" int pp_reset(pp_env* e, const uint8_t* mask_dev, float* obs_dev, void* stream) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  return launch(e, PP_MODE_RESET, mask_dev, nullptr, obs_dev, nullptr, nullptr, nullptr, nullptr,
+                (cudaStream_t)stream);
+}
+
+extern "C" int pp_step(pp_env* e, const float* actions_dev, float* obs_dev, float* reward_dev,
+                       float* reward_terms_dev, uint8_t* done_dev, float* discount_dev, void* stream) {
+  if (!e || !actions_dev || !reward_dev || !done_dev) return fail(PP_ERR_INVALID, "null argument");
+  return launch(e, PP_MODE_STEP, nullptr, actions_dev, obs_dev, reward_dev, reward_terms_dev, done_dev,
+                discount_dev, (cudaStream_t)stream);
+}
+
+extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* reward, float* terms,
+                            uint8_t* done, float* discount) {
+  if (!e || !actions || !reward || !done) return fail(PP_ERR_INVALID, "null argument");
+  const size_t N = e->cfg.num_envs;
+  cudaStream_t s = e->hstream;
+  memcpy(e->h_actions, actions, N * e->action_dim * 4);
+  CUDA_OK(cudaMemcpyAsync(e->d_actions, e->h_actions, N * e->action_dim * 4, cudaMemcpyHostToDevice, s));
+  int rc = launch(e, PP_MODE_STEP, nullptr, e->d_actions, obs ? e->d_obs : nullptr, e->d_reward,
+                  terms ? e->d_terms : nullptr, e->d_done, discount ? e->d_discount : nullptr, s);
+  if (rc != PP_OK) return rc;
+  if (obs) CUDA_OK(cudaMemcpyAsync(e->h_obs, e->d_obs, N * e->obs_dim * 4, cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaMemcpyAsync(e->h_reward, e->d_reward, N * 4, cudaMemcpyDeviceToHost, s));
+  if (terms) CUDA_OK(cudaMemcpyAsync(e->h_terms, e->d_terms, N * 5 * 4, cudaMemcpyDeviceToHost, s));
+  if (discount) CUDA_OK(cudaMemcpyAsync(e->h_discount, e->d_discount, N * 4, cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaMemcpyAsync(e->h_done, e->d_done, N, cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaStreamSynchronize(s));
+  if (obs) memcpy(obs, e->h_obs, N * e->obs_dim * 4);
+  memcpy(reward, e->h_reward, N * 4);
+  if (terms) memcpy(terms, e->h_terms, N * 5 * 4);
+  if (discount) memcpy(discount, e->h_discount, N * 4);
+  memcpy(done, e->h_done, N);
+  return PP_OK;
+}
+
+extern "C" int pp_reset_host(pp_env* e, const uint8_t* mask, float* obs) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  const size_t N = e->cfg.num_envs;
+  cudaStream_t s = e->hstream;
+  if (mask) CUDA_OK(cudaMemcpyAsync(e->d_mask, mask, N, cudaMemcpyHostToDevice, s));
+  int rc = launch(e, PP_MODE_RESET, mask ? e->d_mask : nullptr, nullptr, obs ? e->d_obs : nullptr, nullptr,
+                  nullptr, nullptr, nullptr, s);
+  if (rc != PP_OK) return rc;
+  if (obs) CUDA_OK(cudaMemcpyAsync(e->h_obs, e->d_obs, N * e->obs_dim * 4, cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaStreamSynchronize(s));
+  if (obs) memcpy(obs, e->h_obs, N * e->obs_dim * 4);
+  return PP_OK;
+}
+
+#define COPY_IF(dst, src, bytes)                                                              \
+  if (dst) CUDA_OK(cudaMemcpyAsync((void*)(dst), (const void*)(src), (bytes), cudaMemcpyDeviceToDevice, s))
+
+extern "C" int pp_get_state(pp_env* e, float* qpos, float* qvel, float* warm, int32_t* t_idx, float* sustain,
+                            void* stream) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t N = e->cfg.num_envs, nv = e->nv;
+  COPY_IF(qpos, e->qpos, N * nv * 4); COPY_IF(qvel, e->qvel, N * nv * 4); COPY_IF(warm, e->warm, N * nv * 4);
+  COPY_IF(t_idx, e->t_idx, N * 4); COPY_IF(sustain, e->sustain, N * 4);
+  return PP_OK;
+}
+
+extern "C" int pp_set_state(pp_env* e, const float* qpos, const float* qvel, const float* warm,
+                            const int32_t* t_idx, const float* sustain, void* stream) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t N = e->cfg.num_envs, nv = e->nv;
+  if (qpos) COPY_IF(e->qpos, qpos, N * nv * 4);
+  if (qvel) COPY_IF(e->qvel, qvel, N * nv * 4);
+  if (warm) COPY_IF(e->warm, warm, N * nv * 4);
+  if (t_idx) COPY_IF(e->t_idx, t_idx, N * 4);
+  if (sustain) COPY_IF(e->sustain, sustain, N * 4);
+  return PP_OK;
+}
+
+extern "C" int pp_set_qfrc_applied(pp_env* e, const float* qfrc, void* stream) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  cudaStream_t s = (cudaStream_t)stream;
+  e->use_applied = qfrc != nullptr;
+  if (qfrc) COPY_IF(e->qfrc_applied, qfrc, (size_t)e->cfg.num_envs * e->nv * 4);
+  return PP_OK;
+}
+
+extern "C" int pp_get_diag(pp_env* e, float* qacc, float* act_force, float* act_vel, float* site_xpos,
+                           uint8_t* activation, int32_t* counters, void* stream) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t N = e->cfg.num_envs;
+  COPY_IF(qacc, e->qacc, N * e->nv * 4);
+  if (e->nu) { COPY_IF(act_force, e->act_force, N * e->nu * 4); COPY_IF(act_vel, e->act_vel, N * e->nu * 4); }
+  COPY_IF(site_xpos, e->site_xpos, N * 3 * PP_NSITE * 4);
+  COPY_IF(activation, e->activation, N * 88);
+  COPY_IF(counters, e->counters, N * 4 * 4);
+  return PP_OK;
+}

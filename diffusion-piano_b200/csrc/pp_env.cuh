@@ -1,0 +1,54 @@
+// pp_env.cuh - kernel argument blocks (plain structs of device pointers) and launchers.
+#pragma once
+#include "pp_common.cuh"
+
+enum { PP_MODE_STEP = 0, PP_MODE_RESET = 1 };
+
+struct PianoOnlyArgs {
+  const DevModel* dm;
+  int num_envs, mode, n_substeps, n_frames, lookahead, obs_dim;
+  int canonical, reward_type, auto_reset;
+  const uint8_t* goal;        // [T,89]
+  const uint8_t* reset_mask;  // [N] or null (RESET mode)
+  const float* actions;       // [N,89]
+  const float* qfrc_applied;  // [N,88] or null
+  float *qpos, *qvel;         // [N,88]
+  int* t_idx;                 // [N]
+  float* sustain;             // [N]
+  uint8_t* needs_reset;       // [N]
+  float* obs;                 // [N,obs_dim] or null
+  float *reward, *reward_terms, *discount;
+  uint8_t* done;
+  float* qacc;                // diag [N,88] or null
+  uint8_t* activation;        // diag [N,88] or null
+};
+
+struct HandsArgs {
+  const DevModel* dm;
+  int num_envs, mode, n_substeps, n_frames, lookahead, obs_dim, pmax;
+  int canonical, has_fingering, disable_forearm_reward, wrong_press_termination, auto_reset;
+  int max_contacts;
+  float energy_coef;
+  const uint8_t* goal;    // [T,89]
+  const int16_t* pairs;   // [T,pmax,2]
+  const uint8_t* reset_mask;
+  const float* actions;   // [N,45]
+  const float* act_min;   // [45] action spec
+  const float* act_max;   // [45]
+  const float* qfrc_applied;  // [N,140] or null
+  float *qpos, *qvel, *warm;  // [N,140]
+  int* t_idx;
+  float* sustain;
+  uint8_t* needs_reset;
+  float* obs;
+  float *reward, *reward_terms, *discount;
+  uint8_t* done;
+  // diagnostics (always allocated by the handle)
+  float *qacc, *act_force, *act_vel, *site_xpos;
+  uint8_t* activation;
+  int* counters;  // [N,4]
+};
+
+void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);
+void pp_launch_hands(const HandsArgs& A, cudaStream_t stream);
+size_t pp_hands_smem_bytes();

@@ -1,0 +1,124 @@
+"""BatchedPianoEngine: thin Python owner of one pp_env handle (one per GPU).
+
+torch is used only for device buffers and streams; every step goes through the C-ABI
+(`pp_step` with device pointers, `pp_step_host` with numpy buffers).
+"""
+
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Dict, Optional
+
+import numpy as np
+
+from . import _lib
+from .music.midi_file import SongTables
+from .scene.compile import CompiledModel, to_ctypes
+
+
+@dataclass
+class EngineConfig:
+    num_envs: int
+    task: int
+    n_substeps: int
+    n_steps_lookahead: int = 0
+    canonical_actions: bool = False
+    has_fingering: bool = False
+    disable_forearm_reward: bool = False
+    wrong_press_termination: bool = False
+    reward_type: int = _lib.REWARD_NEGATIVE_L2
+    auto_reset: bool = True
+    max_contacts: int = 0
+    energy_penalty_coef: float = 5e-3
+    device: int = 0
+
+
+def _ptr(t) -> Optional[int]:
+    """Device/host pointer of a torch tensor or numpy array (None passes NULL)."""
+    if t is None:
+        return None
+    if isinstance(t, np.ndarray):
+        assert t.flags["C_CONTIGUOUS"]
+        return t.ctypes.data
+    assert t.is_contiguous()
+    return t.data_ptr()
+
+
+class BatchedPianoEngine:
+    def __init__(self, model: CompiledModel, song: SongTables, cfg: EngineConfig):
+        self.lib = _lib.load()
+        self.model, self.song, self.cfg = model, song, cfg
+        self._cm = to_ctypes(model)
+        self._goal = np.ascontiguousarray(song.goal, np.uint8)
+        self._pairs = np.ascontiguousarray(song.pairs, np.int16)
+        c = _lib.PPConfig()
+        c.num_envs, c.device, c.task = cfg.num_envs, cfg.device, cfg.task
+        c.n_substeps, c.n_steps_lookahead = cfg.n_substeps, cfg.n_steps_lookahead
+        c.n_frames, c.pmax = song.n_frames, song.pmax
+        c.canonical_actions, c.has_fingering = int(cfg.canonical_actions), int(cfg.has_fingering)
+        c.disable_forearm_reward = int(cfg.disable_forearm_reward)
+        c.wrong_press_termination = int(cfg.wrong_press_termination)
+        c.reward_type, c.auto_reset, c.max_contacts = cfg.reward_type, int(cfg.auto_reset), cfg.max_contacts
+        c.energy_penalty_coef = cfg.energy_penalty_coef
+        c.goal, c.pairs = self._goal.ctypes.data, self._pairs.ctypes.data
+        h = ctypes.c_void_p()
+        _lib.check(self.lib.pp_create(ctypes.cast(ctypes.pointer(self._cm), ctypes.c_void_p),
+                                      ctypes.byref(c), ctypes.byref(h)))
+        self._h = h
+        self.num_envs = cfg.num_envs
+        self.nv = self.lib.pp_nv(h)
+        self.action_dim = self.lib.pp_action_dim(h)
+        self.obs_dim = self.lib.pp_obs_dim(h)
+        lo = np.zeros(self.action_dim, np.float32)
+        hi = np.zeros(self.action_dim, np.float32)
+        _lib.check(self.lib.pp_action_bounds(h, lo.ctypes.data, hi.ctypes.data))
+        self.action_minimum, self.action_maximum = lo, hi
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.pp_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- device-pointer path (torch CUDA tensors)
+    def reset(self, obs=None, mask=None, stream: int = 0):
+        _lib.check(self.lib.pp_reset(self._h, _ptr(mask), _ptr(obs), stream))
+
+    def step(self, actions, obs, reward, done, reward_terms=None, discount=None, stream: int = 0):
+        _lib.check(self.lib.pp_step(self._h, _ptr(actions), _ptr(obs), _ptr(reward), _ptr(reward_terms),
+                                    _ptr(done), _ptr(discount), stream))
+
+    # ---- host-buffer path (numpy), copies inside the call
+    def reset_host(self, obs: Optional[np.ndarray] = None, mask: Optional[np.ndarray] = None):
+        _lib.check(self.lib.pp_reset_host(self._h, _ptr(mask), _ptr(obs)))
+
+    def step_host(self, actions: np.ndarray, obs, reward, done, reward_terms=None, discount=None):
+        _lib.check(self.lib.pp_step_host(self._h, _ptr(actions), _ptr(obs), _ptr(reward),
+                                         _ptr(reward_terms), _ptr(done), _ptr(discount)))
+
+    # ---- state / diagnostics (torch CUDA tensors)
+    def get_state(self, qpos=None, qvel=None, warm=None, t_idx=None, sustain=None, stream: int = 0):
+        _lib.check(self.lib.pp_get_state(self._h, _ptr(qpos), _ptr(qvel), _ptr(warm), _ptr(t_idx),
+                                         _ptr(sustain), stream))
+
+    def set_state(self, qpos=None, qvel=None, warm=None, t_idx=None, sustain=None, stream: int = 0):
+        _lib.check(self.lib.pp_set_state(self._h, _ptr(qpos), _ptr(qvel), _ptr(warm), _ptr(t_idx),
+                                         _ptr(sustain), stream))
+
+    def set_qfrc_applied(self, qfrc, stream: int = 0):
+        _lib.check(self.lib.pp_set_qfrc_applied(self._h, _ptr(qfrc), stream))
+
+    def get_diag(self, qacc=None, actuator_force=None, actuator_velocity=None, site_xpos=None,
+                 activation=None, counters=None, stream: int = 0):
+        _lib.check(self.lib.pp_get_diag(self._h, _ptr(qacc), _ptr(actuator_force), _ptr(actuator_velocity),
+                                        _ptr(site_xpos), _ptr(activation), _ptr(counters), stream))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.pp_launch_count(self._h))

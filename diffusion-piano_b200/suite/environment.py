@@ -1,0 +1,181 @@
+"""Environment façades over the CUDA step.
+
+* `BatchedEnvironment`  - N envs on one GPU; device-tensor API (`step_device`) for training
+  loops that stay on the GPU, and the reference's numpy dict API (`reset`/`step`).
+* `VectorizedPianoEnv`  - drop-in for reference `parallelized_base_v2.py:21-67` (boundary B1).
+* `Environment`         - single-env dm_env API of `composer_utils.Environment(task=...)` /
+  `robopianist.suite.load` (boundary B2): reset()/step() -> TimeStep, FIRST has reward None.
+"""
+
+from __future__ import annotations
+
+from collections import OrderedDict
+from typing import Dict, Optional
+
+import numpy as np
+
+from ..engine import BatchedPianoEngine
+from . import specs
+
+
+class BatchedEnvironment:
+    def __init__(self, task, num_envs: int, device: int = 0, canonical_actions: bool = False,
+                 auto_reset: bool = True):
+        import torch  # device memory + streams only
+
+        self._torch = torch
+        self.task = task
+        self.num_envs = int(num_envs)
+        cfg = task.engine_config(num_envs, device, canonical_actions)
+        cfg.auto_reset = auto_reset
+        self.engine = BatchedPianoEngine(task.model, task.song, cfg)
+        self.device = torch.device("cuda", device)
+        self.layout = task.observation_layout()
+        self.obs_dim, self.action_dim = self.engine.obs_dim, self.engine.action_dim
+        n = self.num_envs
+        self._obs = torch.zeros((n, self.obs_dim), dtype=torch.float32, device=self.device)
+        self._reward = torch.zeros(n, dtype=torch.float32, device=self.device)
+        self._terms = torch.zeros((n, 5), dtype=torch.float32, device=self.device)
+        self._discount = torch.ones(n, dtype=torch.float32, device=self.device)
+        self._done = torch.zeros(n, dtype=torch.uint8, device=self.device)
+        self._canonical = canonical_actions
+        # host staging for the numpy API
+        self._h_obs = np.zeros((n, self.obs_dim), np.float32)
+        self._h_reward = np.zeros(n, np.float32)
+        self._h_terms = np.zeros((n, 5), np.float32)
+        self._h_discount = np.ones(n, np.float32)
+        self._h_done = np.zeros(n, np.uint8)
+
+    # ---- specs
+    def action_spec(self) -> specs.BoundedArray:
+        if self._canonical:
+            return specs.BoundedArray((self.action_dim,), np.float64, -1.0, 1.0, name="action")
+        return specs.BoundedArray((self.action_dim,), np.float64, self.engine.action_minimum,
+                                  self.engine.action_maximum, name="action")
+
+    def observation_spec(self) -> "OrderedDict[str, specs.Array]":
+        return OrderedDict((k, specs.Array((size,), np.float64, name=k)) for k, (_, size) in self.layout.items())
+
+    # ---- device API: everything stays in HBM; returned tensors are reused between calls
+    def reset_device(self, mask=None):
+        stream = self._torch.cuda.current_stream(self.device).cuda_stream
+        self.engine.reset(obs=self._obs, mask=mask, stream=stream)
+        return self._obs
+
+    def step_device(self, actions):
+        """actions: float32 CUDA tensor (N, action_dim). Returns (obs, reward, done, terms, discount)."""
+        stream = self._torch.cuda.current_stream(self.device).cuda_stream
+        self.engine.step(actions, self._obs, self._reward, self._done, self._terms, self._discount, stream)
+        return self._obs, self._reward, self._done, self._terms, self._discount
+
+    # ---- numpy API (host buffers; copies inside pp_step_host)
+    def _split(self, flat: np.ndarray) -> Dict[str, np.ndarray]:
+        return OrderedDict((k, flat[:, o:o + s].astype(np.float64)) for k, (o, s) in self.layout.items())
+
+    def reset(self) -> Dict[str, np.ndarray]:
+        self.engine.reset_host(obs=self._h_obs)
+        return self._split(self._h_obs)
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions, np.float32)
+        if a.shape != (self.num_envs, self.action_dim):
+            raise ValueError(f"actions must have shape {(self.num_envs, self.action_dim)}, got {a.shape}")
+        self.engine.step_host(a, self._h_obs, self._h_reward, self._h_done, self._h_terms, self._h_discount)
+        return self._split(self._h_obs), self._h_reward.astype(np.float64), self._h_done.astype(bool)
+
+    @property
+    def reward_terms(self) -> Dict[str, np.ndarray]:
+        """Per-term rewards of the last numpy step (CompositeReward.reward_terms, per env)."""
+        cols = {"key_press_reward": 0, "sustain_reward": 1, "energy_reward": 2, "fingering_reward": 3,
+                "ot_fingering_reward": 3, "forearm_reward": 4}
+        return OrderedDict((n, self._h_terms[:, cols[n]].astype(np.float64)) for n in self.task.reward_names)
+
+    def close(self):
+        self.engine.close()
+
+
+class _SpecView:
+    """What `vec_env.envs[0]` must answer (parallelized_base_v2.py:82-86)."""
+
+    def __init__(self, batched: BatchedEnvironment):
+        self._b = batched
+
+    def observation_spec(self):
+        return self._b.observation_spec()
+
+    def action_spec(self):
+        return self._b.action_spec()
+
+
+class VectorizedPianoEnv:
+    """Same constructor and methods as reference parallelized_base_v2.py:21-67; the N envs are
+    one batched CUDA step instead of a Python loop. Task kwargs are the reference's (:28-38);
+    actions are canonical [-1, 1] (CanonicalSpecWrapper, :44)."""
+
+    def __init__(self, num_envs, midi_sequence, device: int = 0, **task_overrides):
+        from .tasks import PianoWithShadowHands
+
+        kwargs = dict(n_steps_lookahead=1, trim_silence=True, wrong_press_termination=False,
+                      initial_buffer_time=0.0, disable_fingering_reward=False, disable_forearm_reward=False,
+                      disable_colorization=False, disable_hand_collisions=False)
+        kwargs.update(task_overrides)
+        self.num_envs = num_envs
+        self.task = PianoWithShadowHands(midi=midi_sequence, **kwargs)
+        self.batched = BatchedEnvironment(self.task, num_envs, device=device, canonical_actions=True,
+                                          auto_reset=True)
+        self.envs = [_SpecView(self.batched)] * num_envs
+
+    def reset(self):
+        return self.batched.reset()
+
+    def step(self, actions):
+        return self.batched.step(actions)
+
+
+class Environment:
+    """dm_env-style single environment (N = 1 batch)."""
+
+    def __init__(self, task, device: int = 0, canonical_actions: bool = False, random_state=None,
+                 strip_singleton_obs_buffer_dim: bool = True, recompile_physics: bool = False,
+                 legacy_step: bool = True):
+        del random_state, strip_singleton_obs_buffer_dim, recompile_physics
+        if not legacy_step:
+            raise NotImplementedError("only dm_control's legacy_step=True ordering is implemented")
+        self._b = BatchedEnvironment(task, 1, device=device, canonical_actions=canonical_actions,
+                                     auto_reset=False)
+        self.task = task
+        self._reset_next_step = True
+
+    def action_spec(self):
+        return self._b.action_spec()
+
+    def observation_spec(self):
+        return self._b.observation_spec()
+
+    def _obs(self, d):
+        return OrderedDict((k, v[0]) for k, v in d.items())
+
+    def reset(self) -> specs.TimeStep:
+        self._reset_next_step = False
+        return specs.TimeStep(specs.StepType.FIRST, None, None, self._obs(self._b.reset()))
+
+    def step(self, action) -> specs.TimeStep:
+        if self._reset_next_step:
+            return self.reset()
+        obs, reward, done = self._b.step(np.asarray(action, np.float32)[None])
+        discount = float(self._b._h_discount[0])
+        if done[0]:
+            self._reset_next_step = True
+            return specs.TimeStep(specs.StepType.LAST, float(reward[0]), discount, self._obs(obs))
+        return specs.TimeStep(specs.StepType.MID, float(reward[0]), 1.0, self._obs(obs))
+
+    @property
+    def reward_terms(self):
+        return OrderedDict((k, float(v[0])) for k, v in self._b.reward_terms.items())
+
+    @property
+    def batched(self) -> BatchedEnvironment:
+        return self._b
+
+    def close(self):
+        self._b.close()

@@ -1,0 +1,116 @@
+/* piano_step.h - C-ABI of the B200-native batched RoboPianist environment step.
+ *
+ * The reference has no FFI for this path: it calls MuJoCo through dm_control from Python.
+ * Each entry point below names the reference interface it replaces.
+ *
+ *   pp_create   <- building N envs: VectorizedPianoEnv.__init__
+ *                  (reference parallelized_base_v2.py:21-46) / suite.load
+ *                  (robopianist/suite/__init__.py:50-93): compiles the model, uploads tables.
+ *   pp_reset    <- VectorizedPianoEnv.reset (parallelized_base_v2.py:48-51) ->
+ *                  composer Environment.reset -> task.initialize_episode
+ *                  (piano_with_shadow_hands.py:169-174, piano.py:145-152).
+ *   pp_step     <- VectorizedPianoEnv.step (parallelized_base_v2.py:53-60): for every env,
+ *                  CanonicalSpecWrapper action scaling, task.before_step (:176-186),
+ *                  n_substeps x [mj_step + Piano.after_substep (piano.py:154-192)],
+ *                  task.after_step (:188-204), observation update (:371-412), reward
+ *                  (composite_reward.py:46-56), termination (:209-220).
+ *   pp_step_host<- the same call with HOST (numpy) buffers, as the reference's callers pass.
+ *   pp_get_state / pp_set_state <- physics.bind(...).qpos/qvel / physics.set_state, used by
+ *                  parity tests ("identical qpos/qvel/ctrl").
+ *   pp_get_diag <- mjData fields (qacc, actuator_force, sensordata, site_xpos, ncon, ...).
+ *
+ * Conventions: every *_dev pointer is a CUDA device pointer (e.g. torch tensor.data_ptr()),
+ * caller-owned, contiguous, 16-byte aligned; `stream` is a cudaStream_t (0 = legacy default).
+ * Nothing here synchronises the host except pp_create/pp_destroy/pp_step_host/pp_get_*_host.
+ * Return value 0 = ok, negative = error (message via pp_last_error()). One handle per GPU;
+ * a handle is not thread-safe. No CPU fallback exists: without a CUDA device pp_create fails.
+ */
+#ifndef PIANO_STEP_H_
+#define PIANO_STEP_H_
+
+#include <stdint.h>
+
+#include "pp_model.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { PP_TASK_SELF_ACTUATED_PIANO = 0, PP_TASK_PIANO_WITH_SHADOW_HANDS = 1 };
+enum { PP_REWARD_NEGATIVE_L2 = 0, PP_REWARD_NEGATIVE_XENT = 1 };
+enum { PP_OK = 0, PP_ERR_INVALID = -1, PP_ERR_CUDA = -2, PP_ERR_UNSUPPORTED = -3 };
+
+/* reward_terms columns of pp_step (PianoWithShadowHands; insertion order of
+ * piano_with_shadow_hands.py:130-144): */
+enum { PP_TERM_KEY_PRESS = 0, PP_TERM_SUSTAIN = 1, PP_TERM_ENERGY = 2, PP_TERM_FINGERING = 3,
+       PP_TERM_FOREARM = 4, PP_NUM_TERMS = 5 };
+
+typedef struct pp_config {
+  int32_t num_envs;
+  int32_t device;            /* CUDA ordinal */
+  int32_t task;              /* PP_TASK_* */
+  int32_t n_substeps;        /* control_timestep / physics_timestep (10; 2 in config 1) */
+  int32_t n_steps_lookahead; /* L: goal observation has (L+1)*89 entries */
+  int32_t n_frames;          /* T = len(NoteTrajectory.notes) */
+  int32_t pmax;              /* max notes per frame in `pairs` */
+  int32_t canonical_actions; /* 1: actions are in [-1,1] and are affinely mapped to the spec */
+  int32_t has_fingering;     /* 1: fingering obs + fingering reward; 0: OT fingering reward */
+  int32_t disable_forearm_reward;
+  int32_t wrong_press_termination;
+  int32_t reward_type;       /* PP_REWARD_* (self-actuated piano only) */
+  int32_t auto_reset;        /* 1: an env whose previous step was LAST resets on the next step */
+  int32_t max_contacts;      /* 0 = library default */
+  double energy_penalty_coef;
+  const uint8_t *goal;  /* host [T,89]: keys to hold + sustain, per control frame */
+  const int16_t *pairs; /* host [T,pmax,2]: (key, finger 0..9), key=-1 padding; may be NULL */
+} pp_config;
+
+typedef struct pp_env pp_env;
+
+int pp_create(const pp_model *model, const pp_config *config, pp_env **out);
+int pp_destroy(pp_env *env);
+int pp_num_envs(const pp_env *env);
+int pp_nv(const pp_env *env);
+int pp_action_dim(const pp_env *env);
+int pp_obs_dim(const pp_env *env);
+/* action spec (minimum/maximum of the un-canonicalised action), host arrays [action_dim] */
+int pp_action_bounds(const pp_env *env, float *minimum, float *maximum);
+
+/* mask_dev: uint8 [N] (1 = reset this env) or NULL for all. obs_dev may be NULL. */
+int pp_reset(pp_env *env, const uint8_t *mask_dev, float *obs_dev, void *stream);
+/* actions_dev [N,action_dim] f32; obs_dev [N,obs_dim] f32; reward_dev [N] f32;
+ * reward_terms_dev [N,PP_NUM_TERMS] f32 or NULL; done_dev [N] u8 (1 = LAST);
+ * discount_dev [N] f32 or NULL. */
+int pp_step(pp_env *env, const float *actions_dev, float *obs_dev, float *reward_dev,
+            float *reward_terms_dev, uint8_t *done_dev, float *discount_dev, void *stream);
+/* Host-buffer variant: H2D of actions, step, D2H of obs/reward/done inside the call
+ * (pinned staging owned by the handle); returns after the results are on the host. */
+int pp_step_host(pp_env *env, const float *actions, float *obs, float *reward,
+                 float *reward_terms, uint8_t *done, float *discount);
+int pp_reset_host(pp_env *env, const uint8_t *mask, float *obs);
+
+/* state: qpos/qvel/qacc_warmstart [N,nv] f32, t_idx [N] i32, sustain [N] f32 (device);
+ * any pointer may be NULL */
+int pp_get_state(pp_env *env, float *qpos_dev, float *qvel_dev, float *warm_dev,
+                 int32_t *t_idx_dev, float *sustain_dev, void *stream);
+int pp_set_state(pp_env *env, const float *qpos_dev, const float *qvel_dev, const float *warm_dev,
+                 const int32_t *t_idx_dev, const float *sustain_dev, void *stream);
+/* generalized force added to every substep (tests use it like physics.bind().qfrc_applied) */
+int pp_set_qfrc_applied(pp_env *env, const float *qfrc_dev, void *stream);
+
+/* diagnostics of the LAST substep of the last pp_step (device pointers, any may be NULL):
+ * qacc [N,nv]; actuator_force [N,nu]; actuator_velocity [N,nu]; site_xpos [N,nsite,3];
+ * activation [N,88] u8; counters [N,4] i32 = {ncon, nefc, newton iterations, dropped contacts} */
+int pp_get_diag(pp_env *env, float *qacc_dev, float *actuator_force_dev,
+                float *actuator_velocity_dev, float *site_xpos_dev, uint8_t *activation_dev,
+                int32_t *counters_dev, void *stream);
+
+/* number of kernels launched by this handle since creation (for bench's gpu_launches) */
+long long pp_launch_count(const pp_env *env);
+const char *pp_last_error(void);
+const char *pp_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIANO_STEP_H_ */
