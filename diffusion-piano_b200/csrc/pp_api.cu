@@ -106,6 +106,9 @@ static int build_dev_model(const pp_model* m, DevModel* out) {
       else kt.boundary_black[nw] = (int8_t)k;  // sits on the boundary before white #nw
     }
     if (nw != 52) return fail(PP_ERR_UNSUPPORTED, "expected 52 white keys, found %d", nw);
+    const int w0 = kt.white_key[0], w51 = kt.white_key[51];
+    kt.y0 = kt.pos[w0][1] - kt.half[w0][1];
+    kt.pitch = (kt.pos[w51][1] - kt.pos[w0][1]) / 51.f;
   }
   // base box = geom 88 on the world body
   if (m->ngeom > PP_NKEY) {
@@ -176,9 +179,31 @@ static int build_dev_model(const pp_model* m, DevModel* out) {
   }
   if (m->npair > PP_MAXPAIR) return fail(PP_ERR_UNSUPPORTED, "too many fixed geom pairs");
   ht.npair = m->npair;
-  for (int p = 0; p < m->npair; p++) {
-    ht.pair_g1[p] = (int8_t)(m->pair_geom1[p] - (PP_NKEY + 1));
-    ht.pair_g2[p] = (int8_t)(m->pair_geom2[p] - (PP_NKEY + 1));
+  {  // same-hand pairs first, rh x lh pairs last (the kernel culls the latter as a block)
+    const int ngh = ht.ngeom / 2;
+    int n = 0;
+    for (int pass = 0; pass < 2; pass++) {
+      for (int p = 0; p < m->npair; p++) {
+        int g1 = m->pair_geom1[p] - (PP_NKEY + 1), g2 = m->pair_geom2[p] - (PP_NKEY + 1);
+        if (g1 < 0 || g2 < 0 || g1 >= ht.ngeom || g2 >= ht.ngeom)
+          return fail(PP_ERR_UNSUPPORTED, "fixed pair %d does not reference hand colliders", p);
+        bool cross = (g1 / ngh) != (g2 / ngh);
+        if ((int)cross != pass) continue;
+        if (cross && g1 / ngh != 0) { int t = g1; g1 = g2; g2 = t; }  // rh collider first
+        ht.pair_g1[n] = (int8_t)g1; ht.pair_g2[n] = (int8_t)g2; n++;
+      }
+      if (pass == 0) ht.npair_same = n;
+    }
+  }
+  if (ht.ngeom % 2 != 0 || ht.ngeom / 2 > 32) return fail(PP_ERR_UNSUPPORTED, "hands must have equal collider counts <= 32");
+  ht.forearm_geom[0] = ht.forearm_geom[1] = -1;
+  for (int hg = 0; hg < ht.ngeom; hg++) {
+    if (ht.geom_cls[hg] == PP_CLS_RH_FOREARM) ht.forearm_geom[0] = (int8_t)hg;
+    if (ht.geom_cls[hg] == PP_CLS_LH_FOREARM) ht.forearm_geom[1] = (int8_t)hg;
+    // the kernel mirrors the two hands lane by lane: collider hg of the left hand must sit on the
+    // same local body as collider hg - ngeom/2 of the right hand
+    if (hg >= ht.ngeom / 2 && ht.geom_body[hg] - PP_HB != ht.geom_body[hg - ht.ngeom / 2])
+      return fail(PP_ERR_UNSUPPORTED, "left/right hand collider layouts differ");
   }
   if (m->nsite != PP_NSITE) return fail(PP_ERR_UNSUPPORTED, "expected 10 fingertip sites");
   for (int s = 0; s < PP_NSITE; s++) {
@@ -195,6 +220,18 @@ static int build_dev_model(const pp_model* m, DevModel* out) {
     f3cpy(ht.act_forcerange[i], m->act_forcerange + 2 * i, 2);
     if (m->act_gain_only[i]) return fail(PP_ERR_UNSUPPORTED, "hand actuators must be position servos");
   }
+  for (int hd = 0; hd < PP_NHD; hd++) ht.dof_act[hd] = -1;
+  for (int i = 0; i < PP_NU_HANDS; i++) {
+    const int h = i / 22;
+    for (int t : {(int)ht.act_trn0[i], (int)ht.act_trn1[i]}) {
+      if (t < 0) continue;
+      if (t / PP_HD != h || ht.dof_act[t] >= 0)
+        return fail(PP_ERR_UNSUPPORTED, "actuator %d: every hand dof must be driven by one actuator of its own hand", i);
+      ht.dof_act[t] = (int8_t)(i % 22);
+    }
+  }
+  for (int hd = 0; hd < PP_NHD; hd++)
+    if (ht.dof_act[hd] < 0) return fail(PP_ERR_UNSUPPORTED, "hand dof %d is not actuated", hd);
   return PP_OK;
 }
 

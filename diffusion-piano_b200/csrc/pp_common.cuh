@@ -29,6 +29,7 @@ struct KeyTables {
   float stiffness, springref, damping;
   int8_t white_key[52];    // key number of the i-th white key
   int8_t boundary_black[53];  // key number of the black key on boundary n (between white n-1 and n), -1 none
+  float y0, pitch;         // white key i spans y0 + i*pitch .. y0 + i*pitch + width
 };
 
 struct HandTables {
@@ -45,8 +46,11 @@ struct HandTables {
   int8_t geom_nchain[PP_MAXGEOM];
   int8_t geom_chain[PP_MAXGEOM][PP_MAXCHAIN];  // hand dof indices 0..51, root first
   float geom_pos[PP_MAXGEOM][3], geom_r[PP_MAXGEOM], geom_hl[PP_MAXGEOM];
-  int npair;
+  int npair;        // fixed hand-hand candidate pairs; [0,npair_same) same hand, the rest rh x lh
+  int npair_same;
   int8_t pair_g1[PP_MAXPAIR], pair_g2[PP_MAXPAIR];
+  int8_t forearm_geom[2];  // collider index of each hand's forearm capsule
+  int8_t dof_act[PP_NHD];  // local actuator (0..21) driving each hand dof
   // sites
   int8_t site_body[PP_NSITE];
   float site_pos[PP_NSITE][3];

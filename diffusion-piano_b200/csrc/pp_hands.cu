@@ -1,4 +1,1409 @@
-// placeholder - replaced below
+// pp_hands.cu - PianoWithShadowHands step (BASELINE configs 2-5): 88 key hinges + two 26-dof
+// Shadow Hands. ONE WARP OWNS ONE ENVIRONMENT for the whole control step (n_substeps x mj_step
+// + task epilogue); lane l owns hand dof l of BOTH hands (two independent instruction streams
+// per lane) and piano keys l, l+32, l+64.
+//
+// Replaces, per env and per call (reference file:line):
+//   CanonicalSpecWrapper.step affine map                     parallelized_base_v2.py:44
+//   PianoWithShadowHands.before_step / apply_action          piano_with_shadow_hands.py:176-186
+//   n_substeps x physics.step() (MuJoCo mj_step, third party) + Piano.after_substep
+//                                                            piano.py:154-192
+//   after_step, rewards, goal/fingering observables, termination
+//                                                            piano_with_shadow_hands.py:188-412
+// Per substep (names follow mjData; the fp64 restatement is oracle/piano_oracle.c):
+//   kinematics + RNE forward pass (level loop over the fixed tree, warp shuffles)
+//   CRBA: composite inertias by subtree sums, M as <=9 ancestor entries per dof (registers)
+//   actuator / passive / bias forces -> qfrc_smooth
+//   collision: finger capsules vs the <=9 candidate keys under them (y-band lookup) + base,
+//              fixed hand-hand capsule pairs
+//   constraints: dof frictionloss, joint limits, pyramidal contacts (4 rows each)
+//   Newton on the primal cost with exact line search. Untouched keys are solved in closed
+//   form (pp_keys.cuh); touched keys are eliminated first (Schur complement), the hand blocks
+//   are factorised leaves-first so the kinematic-tree sparsity of M + path cliques is kept
+//   (envelope Cholesky in shared memory), dense / coupled envelopes only when a hand-hand
+//   contact needs them.
+//   mj_Euler with implicit joint damping.
+#include "../../include/pp_model.h"
 #include "pp_env.cuh"
-void pp_launch_hands(const HandsArgs&, cudaStream_t) {}
-size_t pp_hands_smem_bytes() { return 0; }
+#include "pp_keys.cuh"
+
+namespace {
+
+constexpr int NC = 24;   // contact cap per env
+constexpr int KS = 16;   // touched-key slots per env
+constexpr int NE = 18;   // jacobian entries per contact (two 9-dof chains, or chain + key)
+constexpr unsigned FULL = 0xffffffffu;
+constexpr float ZCULL = 0.045f;  // nothing of the piano is above this height
+
+struct WarpShared {
+  float xpos[52][3];   // joint anchor (= body origin) of every hand dof node, world
+  float xaxis[52][3];  // joint axis, world
+  float xquat[52][4];  // body orientation of the node
+  float S[52][6];      // spatial motion axis about the hand's reference point
+  float kq[PP_NKEY], kv[PP_NKEY], kw[PP_NKEY];  // key qpos, qvel, warm-start acceleration
+  int8_t key_slot[PP_NKEY];
+  int8_t slot_key[KS];
+  union {
+    struct { float raw[52][16]; float comp[10][16]; } dyn;  // spatial inertia (10) + force (6)
+    float H[52 * 53 / 2];  // packed upper envelope: A(gi<=gk) at gk(gk+1)/2 + gi
+  } u;
+  float Kc[KS][52];       // H(hand dof, key slot)
+  float hss[KS];          // 1 / H(slot, slot)
+  float va[52 + KS];      // vector exchange (acceleration / velocity / search direction)
+  // contacts, SoA over the contact index
+  float c_u[NE * 3][NC];  // per entry: (n, t1, t2) . jacobian column
+  uint8_t c_col[NE][NC];  // column of the entry: hand dof 0..51 or 52+slot
+  unsigned c_mask[2][NC]; // hand dofs in the entry list, per hand (ascending dof order)
+  int8_t c_slot[NC], c_nent[NC];
+  float c_w[5][NC];       // D * (sum c, mu (c0-c1), mu^2 (c0+c1), mu (c2-c3), mu^2 (c2+c3))
+  float c_wf[3][NC];      // 3-vector weight of the rows (forces, or curvature * jp)
+  float c_geo[7][NC];     // pos, normal, dist
+  int c_ids[NC];          // h1 | node1<<1 | kind<<6 | (key or h2|node2<<1)<<8
+};
+
+struct NodeInfo { int parent, depth, nsub, cs; unsigned anc; };
+__device__ __forceinline__ NodeInfo node_info(int l) {
+  NodeInfo n;
+  if (l < 4) { n.cs = 0; n.parent = l > 0 ? l - 1 : 0; n.depth = l; n.nsub = 26 - l; n.anc = (2u << l) - 1u; }
+  else {
+    const int cs = l >= 21 ? 21 : l >= 16 ? 16 : l >= 12 ? 12 : l >= 8 ? 8 : 4;
+    const int ce = cs == 4 ? 7 : cs == 8 ? 11 : cs == 12 ? 15 : cs == 16 ? 20 : 25;
+    n.cs = cs; n.parent = l == cs ? 3 : l - 1; n.depth = 4 + l - cs; n.nsub = ce - l + 1;
+    n.anc = 0xFu | (((2u << (l - cs)) - 1u) << cs);
+  }
+  return n;
+}
+__device__ __forceinline__ int nsub_of(int l) {
+  if (l < 4) return 26 - l;
+  const int ce = l >= 21 ? 25 : l >= 16 ? 20 : l >= 12 ? 15 : l >= 8 ? 11 : 7;
+  return ce - l + 1;
+}
+__device__ __forceinline__ unsigned anc_of(int l) { return node_info(l).anc; }
+__device__ __forceinline__ int tri(int i) { return (i * (i + 1)) >> 1; }
+__device__ __forceinline__ int hidx(int gi, int gk) { return tri(gk) + gi; }  // gi <= gk
+__device__ __forceinline__ f3 shfl3(f3 v, int src) {
+  return mk3(__shfl_sync(FULL, v.x, src), __shfl_sync(FULL, v.y, src), __shfl_sync(FULL, v.z, src));
+}
+__device__ __forceinline__ f4 shfl4(f4 v, int src) {
+  f4 r; r.w = __shfl_sync(FULL, v.w, src); r.x = __shfl_sync(FULL, v.x, src);
+  r.y = __shfl_sync(FULL, v.y, src); r.z = __shfl_sync(FULL, v.z, src); return r;
+}
+__device__ __forceinline__ float wsum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ f4 ld4(const float* p) { f4 r; r.w = p[0]; r.x = p[1]; r.y = p[2]; r.z = p[3]; return r; }
+
+// ------------------------------------------------------------------ narrow phase
+// Same closest-feature rules as oracle/piano_oracle.c (sphere_box, capsule_box,
+// capsule_capsule): normal from geom1 to geom2, dist < 0 is penetration, pos is the midpoint.
+struct Hit { bool ok; float dist; f3 n, pos; };
+struct Box { f3 p; float cq, sq; f3 h; };  // box rotated by angle q about world +y
+
+__device__ __forceinline__ f3 to_box(const Box& b, f3 r) { return mk3(r.x * b.cq - r.z * b.sq, r.y, r.x * b.sq + r.z * b.cq); }
+__device__ __forceinline__ f3 from_box(const Box& b, f3 r) { return mk3(r.x * b.cq + r.z * b.sq, r.y, -r.x * b.sq + r.z * b.cq); }
+
+__device__ __forceinline__ Hit sphere_box(f3 c, float r, const Box& b, float margin) {
+  Hit o; o.ok = false; o.dist = 0.f; o.n = mk3(0, 0, 1); o.pos = c;
+  const f3 cl = to_box(b, c - b.p);
+  const f3 q = mk3(clampf(cl.x, -b.h.x, b.h.x), clampf(cl.y, -b.h.y, b.h.y), clampf(cl.z, -b.h.z, b.h.z));
+  bool outside = (q.x != cl.x) || (q.y != cl.y) || (q.z != cl.z);
+  f3 nl = q - cl;
+  float len = 0.f, dist;
+  if (outside) { len = norm(nl); if (len < PP_MINVAL) outside = false; }
+  if (outside) {
+    dist = len - r;
+    if (dist >= margin) return o;
+    nl = (1.f / len) * nl;
+  } else {
+    const float vx = fabsf(cl.x) - b.h.x, vy = fabsf(cl.y) - b.h.y, vz = fabsf(cl.z) - b.h.z;
+    int best = 0; float bestv = vx;
+    if (vy > bestv) { bestv = vy; best = 1; }
+    if (vz > bestv) { bestv = vz; best = 2; }
+    const float cb = best == 0 ? cl.x : best == 1 ? cl.y : cl.z;
+    const float s = cb < 0.f ? 1.f : -1.f;
+    nl = mk3(best == 0 ? s : 0.f, best == 1 ? s : 0.f, best == 2 ? s : 0.f);
+    dist = bestv - r;
+  }
+  o.n = from_box(b, nl);
+  o.pos = c + (r + 0.5f * dist) * o.n;
+  o.dist = dist; o.ok = true;
+  return o;
+}
+
+__device__ __forceinline__ float seg_box_dgrad(f3 al, f3 dv, f3 h, float t) {
+  const float sx = al.x + t * dv.x, sy = al.y + t * dv.y, sz = al.z + t * dv.z;
+  const float ex = sx < -h.x ? sx + h.x : (sx > h.x ? sx - h.x : 0.f);
+  const float ey = sy < -h.y ? sy + h.y : (sy > h.y ? sy - h.y : 0.f);
+  const float ez = sz < -h.z ? sz + h.z : (sz > h.z ? sz - h.z : 0.f);
+  return dv.x * ex + dv.y * ey + dv.z * ez;
+}
+
+// capsule / sphere (geom1) against a box: contact at the closest segment point, plus one at the
+// far segment end when it also penetrates
+__device__ __forceinline__ void capsule_box(f3 cp, f3 axis, float r, float hl, const Box& b, float margin,
+                                            Hit& h0, Hit& h1) {
+  h1.ok = false;
+  if (hl == 0.f) { h0 = sphere_box(cp, r, b, margin); return; }
+  const f3 a = cp - hl * axis, e = cp + hl * axis;
+  const f3 al = to_box(b, a - b.p), bl = to_box(b, e - b.p), dv = bl - al;
+  float lo = 0.f, hi = 1.f, glo = seg_box_dgrad(al, dv, b.h, 0.f), ghi = seg_box_dgrad(al, dv, b.h, 1.f), t;
+  if (glo >= 0.f) t = 0.f;
+  else if (ghi <= 0.f) t = 1.f;
+  else {
+    const float alv[3] = {al.x, al.y, al.z}, dvv[3] = {dv.x, dv.y, dv.z}, hv[3] = {b.h.x, b.h.y, b.h.z};
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      if (fabsf(dvv[i]) <= 1e-12f) continue;
+#pragma unroll
+      for (int sg = -1; sg <= 1; sg += 2) {
+        const float tb = ((float)sg * hv[i] - alv[i]) / dvv[i];
+        if (tb > lo && tb < hi) {
+          const float g = seg_box_dgrad(al, dv, b.h, tb);
+          if (g <= 0.f) { lo = tb; glo = g; } else { hi = tb; ghi = g; }
+        }
+      }
+    }
+    t = (ghi - glo > 0.f) ? lo + (hi - lo) * (-glo) / (ghi - glo) : lo;
+  }
+  h0 = sphere_box(a + (2.f * hl * t) * axis, r, b, margin);
+  h1 = sphere_box(t > 0.5f ? a : e, r, b, margin);
+}
+
+__device__ __forceinline__ Hit capsule_capsule(f3 p1, f3 u, float r1, float h1, f3 p2, f3 v, float r2, float h2,
+                                               float margin) {
+  Hit o; o.ok = false; o.dist = 0.f; o.n = mk3(0, 0, 1); o.pos = p1;
+  const f3 w = p1 - p2;
+  const float b = dot(u, v), dd = dot(u, w), e = dot(v, w), den = 1.f - b * b;
+  float s, t;
+  if (h1 == 0.f) s = 0.f;
+  else if (den > 1e-9f) s = clampf((b * e - dd) / den, -h1, h1);
+  else s = 0.f;
+  t = h2 == 0.f ? 0.f : b * s + e;
+  t = clampf(t, -h2, h2);
+  if (h1 != 0.f) s = clampf(b * t - dd, -h1, h1);
+  const f3 c1 = p1 + s * u, c2 = p2 + t * v;
+  f3 n = c2 - c1;
+  const float len = norm(n), dist = len - r1 - r2;
+  if (dist >= margin) return o;
+  n = len < PP_MINVAL ? mk3(0, 0, 1) : (1.f / len) * n;
+  o.n = n; o.pos = c1 + (r1 + 0.5f * dist) * n; o.dist = dist; o.ok = true;
+  return o;
+}
+
+// ------------------------------------------------------------------ constraint rows
+// inequality row (limit / contact): active while x < 0
+__device__ __forceinline__ void row_ineq(float D, float x, float& f, float& c) {
+  if (x < 0.f) { f = -D * x; c = D; } else { f = 0.f; c = 0.f; }
+}
+// frictionloss row: quadratic inside |x| < floss/D, linear outside. zone: -1, 0, +1
+__device__ __forceinline__ void row_fric(float D, float floss, float x, float& f, float& c, int& zone) {
+  const float rf = floss / D;
+  if (x <= -rf) { f = floss; c = 0.f; zone = -1; }
+  else if (x >= rf) { f = -floss; c = 0.f; zone = 1; }
+  else { f = -D * x; c = D; zone = 0; }
+}
+
+struct LaneCtx {
+  int lane;
+  NodeInfo ni;
+  bool dof;  // lane < 26
+};
+
+// One warp-wide ordered append of a contact candidate (deterministic order: call order, then lane)
+__device__ __forceinline__ void push_contact(WarpShared& W, bool ok, int& ncon, int& ndrop, int cap, const Hit& h,
+                                             int ids) {
+  const unsigned b = __ballot_sync(FULL, ok);
+  if (b == 0u) return;
+  const int idx = ncon + __popc(b & ((1u << (threadIdx.x & 31)) - 1u));
+  if (ok && idx < cap) {
+    W.c_geo[0][idx] = h.pos.x; W.c_geo[1][idx] = h.pos.y; W.c_geo[2][idx] = h.pos.z;
+    W.c_geo[3][idx] = h.n.x; W.c_geo[4][idx] = h.n.y; W.c_geo[5][idx] = h.n.z;
+    W.c_geo[6][idx] = h.dist;
+    W.c_ids[idx] = ids;
+  }
+  const int tot = ncon + __popc(b);
+  if (tot > cap) { ndrop += tot - cap; ncon = cap; } else ncon = tot;
+}
+
+// sum over contacts of U[entry of my dof] . wf[c]: J^T applied to per-contact 3-vector weights.
+// out[h] for the lane's hand dofs, outs for the lane's key slot.
+__device__ __forceinline__ void gather_jt(const WarpShared& W, int ncon, int lane, float out[2], float& outs) {
+  out[0] = out[1] = 0.f; outs = 0.f;
+  const unsigned lt = (1u << lane) - 1u;
+  for (int c = 0; c < ncon; c++) {
+    const unsigned m0 = W.c_mask[0][c], m1 = W.c_mask[1][c];
+    const float w0 = W.c_wf[0][c], w1 = W.c_wf[1][c], w2 = W.c_wf[2][c];
+    const int n0 = __popc(m0);
+    if ((m0 >> lane) & 1u) {
+      const int e = __popc(m0 & lt) * 3;
+      out[0] += W.c_u[e][c] * w0 + W.c_u[e + 1][c] * w1 + W.c_u[e + 2][c] * w2;
+    }
+    if ((m1 >> lane) & 1u) {
+      const int e = (n0 + __popc(m1 & lt)) * 3;
+      out[1] += W.c_u[e][c] * w0 + W.c_u[e + 1][c] * w1 + W.c_u[e + 2][c] * w2;
+    }
+    if (W.c_slot[c] == lane) {
+      const int e = (n0 + __popc(m1)) * 3;
+      outs += W.c_u[e][c] * w0 + W.c_u[e + 1][c] * w1 + W.c_u[e + 2][c] * w2;
+    }
+  }
+}
+
+// U x for contact `lane`: x lives in W.va (hand dofs 0..51, key slots 52..)
+__device__ __forceinline__ f3 contact_ux(const WarpShared& W, int c, int nent) {
+  f3 r = mk3(0, 0, 0);
+  for (int e = 0; e < nent; e++) {
+    const float x = W.va[W.c_col[e][c]];
+    r.x += W.c_u[3 * e][c] * x; r.y += W.c_u[3 * e + 1][c] * x; r.z += W.c_u[3 * e + 2][c] * x;
+  }
+  return r;
+}
+
+// ------------------------------------------------------------------ envelope Cholesky
+// Hand rows are eliminated leaves-first (dof 25 .. 0), so a row's off-diagonals are its
+// descendants: row g holds A(g, g+1 .. e(g)). In tree mode e(g) = last descendant and there
+// is no fill-in; dense / coupled modes only widen e(g). Lane l owns rows l (rh) and 26+l (lh).
+// el[h]: local envelope end of the lane's row of hand h (uncoupled), dinv[h]: 1/L(g,g).
+__device__ __forceinline__ void chol_uncoupled(float* H, int lane, bool dof, const int el[2], const bool dense[2],
+                                               float dinv[2]) {
+  for (int lj = 25; lj >= 0; lj--) {
+    const int nsj = nsub_of(lj);
+    float s[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int ej = dense[h] ? 25 : lj + nsj - 1;
+      const int g = h * 26 + lane, gj = h * 26 + lj;
+      const bool act = dof && lane <= lj && el[h] >= lj;
+      float acc = 0.f;
+      if (act) {
+        acc = H[hidx(g, gj)];
+        const int kend = min(el[h], ej);
+        for (int k = lj + 1; k <= kend; k++) acc -= H[hidx(g, h * 26 + k)] * H[hidx(gj, h * 26 + k)];
+      }
+      s[h] = acc;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const float d = fmaxf(__shfl_sync(FULL, s[h], lj), 1e-30f);
+      const float inv = rsqrtf(d);
+      const bool act = dof && lane <= lj && el[h] >= lj;
+      if (act) H[hidx(h * 26 + lane, h * 26 + lj)] = s[h] * inv;
+      if (lane == lj) dinv[h] = inv;
+    }
+    __syncwarp();
+  }
+}
+
+// solves (L L^T) x = b in place; b[h] per lane
+__device__ __forceinline__ void solve_uncoupled(const float* H, int lane, bool dof, const int el[2],
+                                                const float dinv[2], float b[2]) {
+  for (int lj = 25; lj >= 0; lj--) {  // forward: leaves first
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const float y = __shfl_sync(FULL, b[h] * dinv[h], lj);
+      if (lane == lj) b[h] = y;
+      else if (dof && lane < lj && el[h] >= lj) b[h] -= H[hidx(h * 26 + lane, h * 26 + lj)] * y;
+    }
+  }
+  for (int li = 0; li < 26; li++) {  // backward: root first
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const float x = __shfl_sync(FULL, b[h] * dinv[h], li);
+      const int ei = __shfl_sync(FULL, el[h], li);
+      if (lane == li) b[h] = x;
+      else if (dof && lane > li && lane <= ei) b[h] -= H[hidx(h * 26 + li, h * 26 + lane)] * x;
+    }
+  }
+}
+
+// coupled 52x52 (an rh-lh contact or a key touched by both hands): full envelopes
+__device__ __forceinline__ void chol_coupled(float* H, int lane, bool dof, float dinv[2]) {
+  for (int gj = 51; gj >= 0; gj--) {
+    float s[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int g = h * 26 + lane;
+      float acc = 0.f;
+      if (dof && g <= gj) {
+        acc = H[hidx(g, gj)];
+        for (int k = gj + 1; k < 52; k++) acc -= H[hidx(g, k)] * H[hidx(gj, k)];
+      }
+      s[h] = acc;
+    }
+    __syncwarp();
+    const int hj = gj >= 26 ? 1 : 0, lj = gj - 26 * hj;
+    const float d = fmaxf(__shfl_sync(FULL, hj ? s[1] : s[0], lj), 1e-30f);
+    const float inv = rsqrtf(d);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int g = h * 26 + lane;
+      if (dof && g <= gj) H[hidx(g, gj)] = s[h] * inv;
+      if (g == gj) dinv[h] = inv;
+    }
+    __syncwarp();
+  }
+}
+
+__device__ __forceinline__ void solve_coupled(const float* H, int lane, bool dof, const float dinv[2], float b[2]) {
+  for (int gj = 51; gj >= 0; gj--) {
+    const int hj = gj >= 26 ? 1 : 0, lj = gj - 26 * hj;
+    const float y = __shfl_sync(FULL, (hj ? b[1] : b[0]) * (hj ? dinv[1] : dinv[0]), lj);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int g = h * 26 + lane;
+      if (g == gj) b[h] = y;
+      else if (dof && g < gj) b[h] -= H[hidx(g, gj)] * y;
+    }
+  }
+  for (int gi = 0; gi < 52; gi++) {
+    const int hi = gi >= 26 ? 1 : 0, li = gi - 26 * hi;
+    const float x = __shfl_sync(FULL, (hi ? b[1] : b[0]) * (hi ? dinv[1] : dinv[0]), li);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int g = h * 26 + lane;
+      if (g == gi) b[h] = x;
+      else if (dof && g > gi) b[h] -= H[hidx(gi, g)] * x;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ kinematics
+struct Kin {
+  f3 pos[2];   // node origin (world)
+  f4 quat[2];  // node orientation
+  f3 axw[2];   // joint axis (world)
+  f3 ref[2];   // per-hand reference point for spatial quantities
+  f3 w[2], vl[2], aa[2], al[2];  // spatial velocity / bias acceleration about ref (DYN only)
+};
+
+template <bool DYN>
+__device__ __forceinline__ void forward_kinematics(const HandTables& ht, const Options& o, const LaneCtx& L,
+                                                   const float q[2], const float v[2], Kin& K) {
+  const int l = L.dof ? L.lane : 25;
+  f3 lpos[2], axl[2]; f4 lquat[2];
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    const int hb = h * PP_HB + (l >= 2 ? l - 1 : 0);
+    lpos[h] = ld3(ht.body_pos[hb]); lquat[h] = ld4(ht.body_quat[hb]);
+    axl[h] = ld3(ht.axis[h * PP_HD + l]);
+  }
+  // forearm (nodes 0, 1): two slides, constant orientation -> closed form
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    const f4 qf = ld4(ht.body_quat[h * PP_HB]);
+    const f3 a0 = qrot(qf, ld3(ht.axis[h * PP_HD])), a1 = qrot(qf, ld3(ht.axis[h * PP_HD + 1]));
+    const float q0 = __shfl_sync(FULL, q[h], 0), q1 = __shfl_sync(FULL, q[h], 1);
+    const f3 pf = ld3(ht.body_pos[h * PP_HB]) + q0 * a0 + q1 * a1;
+    K.ref[h] = pf + qrot(qf, mk3(0.f, 0.f, 0.25f));
+    K.pos[h] = pf; K.quat[h] = qf; K.axw[h] = l == 0 ? a0 : a1;
+    if (DYN) {
+      const float v0 = __shfl_sync(FULL, v[h], 0), v1 = __shfl_sync(FULL, v[h], 1);
+      K.w[h] = mk3(0, 0, 0); K.aa[h] = mk3(0, 0, 0);
+      K.vl[h] = l == 0 ? v0 * a0 : v0 * a0 + v1 * a1;
+      K.al[h] = mk3(-o.g[0], -o.g[1], -o.g[2]);
+    }
+  }
+  float sh[2], ch[2];
+#pragma unroll
+  for (int h = 0; h < 2; h++) sincosf(0.5f * q[h], &sh[h], &ch[h]);
+  const int par = L.ni.parent;
+  for (int d = 2; d <= 8; d++) {
+    const bool mine = L.dof && L.ni.depth == d;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const f3 pp = shfl3(K.pos[h], par); const f4 qp = shfl4(K.quat[h], par);
+      f3 wp, vlp, aap, alp;
+      if (DYN) { wp = shfl3(K.w[h], par); vlp = shfl3(K.vl[h], par); aap = shfl3(K.aa[h], par); alp = shfl3(K.al[h], par); }
+      if (mine) {
+        const f4 qpre = qmul(qp, lquat[h]);
+        const f3 pos = pp + qrot(qp, lpos[h]);
+        const f3 axw = qrot(qpre, axl[h]);
+        f4 qj; qj.w = ch[h]; qj.x = sh[h] * axl[h].x; qj.y = sh[h] * axl[h].y; qj.z = sh[h] * axl[h].z;
+        K.quat[h] = qnormalize(qmul(qpre, qj));
+        K.pos[h] = pos; K.axw[h] = axw;
+        if (DYN) {
+          const f3 sl = cross(pos - K.ref[h], axw);
+          const float qd = v[h];
+          K.aa[h] = aap + qd * cross(wp, axw);
+          K.al[h] = alp + qd * (cross(wp, sl) + cross(vlp, axw));
+          K.w[h] = wp + qd * axw;
+          K.vl[h] = vlp + qd * sl;
+        }
+      }
+    }
+  }
+}
+
+}  // namespace
+
+// ====================================================================== the step kernel
+__global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpShared& W = *reinterpret_cast<WarpShared*>(smem_raw);
+  const int lane = threadIdx.x & 31;
+  const int env = blockIdx.x;
+  if (env >= A.num_envs) return;
+  const DevModel& dm = *A.dm;
+  const Options& o = dm.opt;
+  const HandTables& ht = dm.hand;
+  const KeyTables& kt = dm.key;
+  const int T = A.n_frames, Lk = A.lookahead, OD = A.obs_dim;
+  LaneCtx L; L.lane = lane; L.dof = lane < PP_HD; L.ni = node_info(L.dof ? lane : 25);
+  const int l = L.dof ? lane : 25;  // safe table index
+
+  int t_idx = A.t_idx[env];
+  const bool do_reset = A.mode == PP_MODE_RESET ? (A.reset_mask ? A.reset_mask[env] != 0 : true)
+                                                : (A.auto_reset && A.needs_reset[env]);
+  if (A.mode == PP_MODE_RESET && !do_reset) return;
+
+  // ---- state: lane l holds hand dof l of both hands and keys l, l+32, l+64
+  float q[2] = {0.f, 0.f}, v[2] = {0.f, 0.f}, acc[2] = {0.f, 0.f};
+  float qk[3] = {0.f, 0.f, 0.f}, vk[3] = {0.f, 0.f, 0.f}, ak[3] = {0.f, 0.f, 0.f};
+  float ctrl[2] = {0.f, 0.f}, sustain = 0.f, act_force[2] = {0.f, 0.f};
+  int cnt_ncon = 0, cnt_nefc = 0, cnt_iter = 0, cnt_drop = 0;
+  const size_t sbase = (size_t)env * PP_NV;
+  const int cap = A.max_contacts > 0 && A.max_contacts < NC ? A.max_contacts : NC;
+  const int ngh = ht.ngeom >> 1;
+
+  if (!do_reset) {
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+      if (L.dof) {
+        q[h] = A.qpos[sbase + PP_NKEY + h * PP_HD + lane];
+        v[h] = A.qvel[sbase + PP_NKEY + h * PP_HD + lane];
+        acc[h] = A.warm[sbase + PP_NKEY + h * PP_HD + lane];
+      }
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      const int k = lane + 32 * i;
+      if (k < PP_NKEY) { qk[i] = A.qpos[sbase + k]; vk[i] = A.qvel[sbase + k]; ak[i] = A.warm[sbase + k]; }
+    }
+    const float* act = A.actions + (size_t)env * 45;
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+      if (lane < 22) {
+        float a = act[h * 22 + lane];
+        if (A.canonical) { const float lo = A.act_min[h * 22 + lane], hi = A.act_max[h * 22 + lane]; a = lo + 0.5f * (a + 1.f) * (hi - lo); }
+        ctrl[h] = a;
+      }
+    sustain = act[44];
+    if (A.canonical) sustain = 0.5f * (sustain + 1.f);
+
+    // ================================================================ substeps
+    for (int sub = 0; sub < A.n_substeps; sub++) {
+      // ---- key state to shared memory
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        const int k = lane + 32 * i;
+        if (k < PP_NKEY) { W.kq[k] = qk[i]; W.kv[k] = vk[i]; W.kw[k] = ak[i]; W.key_slot[k] = -1; }
+      }
+      // ---- mj_kinematics + RNE forward pass
+      Kin K;
+      forward_kinematics<true>(ht, o, L, q, v, K);
+      f3 Sl[2];
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const bool slide = lane < 2;
+        Sl[h] = slide ? K.axw[h] : cross(K.pos[h] - K.ref[h], K.axw[h]);
+        if (L.dof) {
+          const int g = h * 26 + lane;
+          st3(W.xpos[g], K.pos[h]); st3(W.xaxis[g], K.axw[h]);
+          W.xquat[g][0] = K.quat[h].w; W.xquat[g][1] = K.quat[h].x; W.xquat[g][2] = K.quat[h].y; W.xquat[g][3] = K.quat[h].z;
+          const f3 sa = slide ? mk3(0, 0, 0) : K.axw[h];
+          W.S[g][0] = sa.x; W.S[g][1] = sa.y; W.S[g][2] = sa.z; W.S[g][3] = Sl[h].x; W.S[g][4] = Sl[h].y; W.S[g][5] = Sl[h].z;
+        }
+      }
+      // ---- body spatial inertia about ref + RNE body force (node 0 is massless)
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        float r16[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) r16[i] = 0.f;
+        if (L.dof && lane >= 1) {
+          const int hb = h * PP_HB + lane - 1;
+          const float m = ht.mass[hb];
+          const f3 c = K.pos[h] + qrot(K.quat[h], ld3(ht.ipos[hb])) - K.ref[h];
+          const f4 qi = qmul(K.quat[h], ld4(ht.iquat[hb]));
+          const f3 di = ld3(ht.inertia[hb]);
+          // rotation matrix columns of the inertial frame
+          const f3 ex = qrot(qi, mk3(1, 0, 0)), ey = qrot(qi, mk3(0, 1, 0)), ez = qrot(qi, mk3(0, 0, 1));
+          const float cc = dot(c, c);
+          r16[0] = m; r16[1] = m * c.x; r16[2] = m * c.y; r16[3] = m * c.z;
+          r16[4] = di.x * ex.x * ex.x + di.y * ey.x * ey.x + di.z * ez.x * ez.x + m * (cc - c.x * c.x);  // xx
+          r16[5] = di.x * ex.x * ex.y + di.y * ey.x * ey.y + di.z * ez.x * ez.y - m * c.x * c.y;         // xy
+          r16[6] = di.x * ex.x * ex.z + di.y * ey.x * ey.z + di.z * ez.x * ez.z - m * c.x * c.z;         // xz
+          r16[7] = di.x * ex.y * ex.y + di.y * ey.y * ey.y + di.z * ez.y * ez.y + m * (cc - c.y * c.y);  // yy
+          r16[8] = di.x * ex.y * ex.z + di.y * ey.y * ey.z + di.z * ez.y * ez.z - m * c.y * c.z;         // yz
+          r16[9] = di.x * ex.z * ex.z + di.y * ey.z * ey.z + di.z * ez.z * ez.z + m * (cc - c.z * c.z);  // zz
+          // f = I a_eff + v x* (I v), through the centre of mass (no cancellation)
+          const float gc = ht.gravcomp[hb];
+          const f3 ale = K.al[h] + gc * mk3(o.g[0], o.g[1], o.g[2]);
+          auto icw = [&](f3 x) {  // R diag(I) R^T x
+            return (di.x * dot(ex, x)) * ex + (di.y * dot(ey, x)) * ey + (di.z * dot(ez, x)) * ez;
+          };
+          const f3 f1 = m * (ale + cross(K.aa[h], c));
+          const f3 n1 = icw(K.aa[h]) + cross(c, f1);
+          const f3 fh = m * (K.vl[h] + cross(K.w[h], c));
+          const f3 nh = icw(K.w[h]) + cross(c, fh);
+          const f3 nn = n1 + cross(K.w[h], nh) + cross(K.vl[h], fh);
+          const f3 ff = f1 + cross(K.w[h], fh);
+          r16[10] = nn.x; r16[11] = nn.y; r16[12] = nn.z; r16[13] = ff.x; r16[14] = ff.y; r16[15] = ff.z;
+        }
+        if (L.dof) {
+#pragma unroll
+          for (int i = 0; i < 16; i++) W.u.dyn.raw[h * 26 + lane][i] = r16[i];
+        }
+      }
+      __syncwarp();
+      // ---- composite (subtree) sums: chains first, then the 4 root nodes
+      float comp[2][16];
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) comp[h][i] = 0.f;
+        if (L.dof && lane >= 4) {
+          for (int k = 0; k < L.ni.nsub; k++)
+#pragma unroll
+            for (int i = 0; i < 16; i++) comp[h][i] += W.u.dyn.raw[h * 26 + lane + k][i];
+          if (lane == L.ni.cs) {
+            const int ci = h * 5 + (lane == 4 ? 0 : lane == 8 ? 1 : lane == 12 ? 2 : lane == 16 ? 3 : 4);
+#pragma unroll
+            for (int i = 0; i < 16; i++) W.u.dyn.comp[ci][i] = comp[h][i];
+          }
+        }
+      }
+      __syncwarp();
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        if (lane < 4) {
+          for (int k = lane; k < 4; k++)
+#pragma unroll
+            for (int i = 0; i < 16; i++) comp[h][i] += W.u.dyn.raw[h * 26 + k][i];
+          for (int k = 0; k < 5; k++)
+#pragma unroll
+            for (int i = 0; i < 16; i++) comp[h][i] += W.u.dyn.comp[h * 5 + k][i];
+        }
+      }
+      __syncwarp();  // u.dyn is dead from here on (H aliases it)
+      // ---- CRBA row (ancestors of the dof) and RNE bias
+      float Mr[2][9], bias[2];
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const float* cI = comp[h];
+        const f3 sa = lane < 2 ? mk3(0, 0, 0) : K.axw[h], sl = Sl[h];
+        const f3 mc = mk3(cI[1], cI[2], cI[3]);
+        const f3 Is = mk3(cI[4] * sa.x + cI[5] * sa.y + cI[6] * sa.z, cI[5] * sa.x + cI[7] * sa.y + cI[8] * sa.z,
+                          cI[6] * sa.x + cI[8] * sa.y + cI[9] * sa.z);
+        const f3 Fn = Is + cross(mc, sl);
+        const f3 Ff = cI[0] * sl - cross(mc, sa);
+        bias[h] = sa.x * cI[10] + sa.y * cI[11] + sa.z * cI[12] + sl.x * cI[13] + sl.y * cI[14] + sl.z * cI[15];
+#pragma unroll
+        for (int j = 0; j < 9; j++) {
+          const int a = j < 4 ? j : L.ni.cs + j - 4;
+          const bool valid = L.dof && (j < 4 ? (j <= lane) : (lane >= 4 && a <= lane));
+          float mv = 0.f;
+          if (valid) {
+            const float* Sa = W.S[h * 26 + a];
+            mv = Sa[0] * Fn.x + Sa[1] * Fn.y + Sa[2] * Fn.z + Sa[3] * Ff.x + Sa[4] * Ff.y + Sa[5] * Ff.z;
+            if (a == lane) mv += ht.armature[h * PP_HD + l];
+          }
+          Mr[h][j] = mv;
+        }
+      }
+      // ---- mj_fwdActuation (position servos on joints / 2-joint fixed tendons) + qfrc_smooth
+      float fs[2], damp[2];
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        float f = 0.f;
+        const int ai = h * 22 + (lane < 22 ? lane : 0);
+        const int t0 = ht.act_trn0[ai] - h * 26, t1 = ht.act_trn1[ai] - h * 26;
+        float len = __shfl_sync(FULL, q[h], t0);
+        const float q1 = __shfl_sync(FULL, q[h], t1 >= 0 ? t1 : 0);
+        if (ht.act_trn1[ai] >= 0) len += q1;
+        if (lane < 22) {
+          const float c = clampf(ctrl[h], ht.act_ctrlrange[ai][0], ht.act_ctrlrange[ai][1]);
+          f = ht.act_kp[ai] * c - ht.act_kp[ai] * len;
+          if (ht.act_forcelimited[ai]) f = clampf(f, ht.act_forcerange[ai][0], ht.act_forcerange[ai][1]);
+          act_force[h] = f;
+        }
+        const float fa = __shfl_sync(FULL, f, ht.dof_act[h * PP_HD + l]);
+        damp[h] = ht.damping[h * PP_HD + l];
+        const float applied = (A.qfrc_applied && L.dof) ? A.qfrc_applied[sbase + PP_NKEY + h * PP_HD + lane] : 0.f;
+        fs[h] = L.dof ? (-damp[h] * v[h] - bias[h] + fa + applied) : 0.f;
+      }
+      float fsk[3];
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        const int k = lane + 32 * i;
+        fsk[i] = 0.f;
+        if (k < PP_NKEY) {
+          const float applied = A.qfrc_applied ? A.qfrc_applied[sbase + k] : 0.f;
+          fsk[i] = pp_key_smooth(kt, k, qk[i], vk[i], applied);
+        }
+      }
+
+      // ================================================================ mj_collision
+      int ncon = 0, ndrop = 0;
+      {
+        f3 gc[2], gax[2]; float gr = 0.f, ghl = 0.f; int gnode = 0; bool finger = false;
+        const bool hasg = lane < ngh;
+        if (hasg) { gr = ht.geom_r[lane]; ghl = ht.geom_hl[lane]; gnode = ht.geom_body[lane] + 1; if (gnode == 1) gnode = 1; finger = ht.geom_cls[lane] == PP_CLS_RH_FINGER; }
+        float ylo[2], yhi[2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          gc[h] = mk3(0, 0, 1); gax[h] = mk3(0, 0, 1); ylo[h] = 1e9f; yhi[h] = -1e9f;
+          if (hasg) {
+            const int g = h * 26 + gnode;
+            f4 qq; qq.w = W.xquat[g][0]; qq.x = W.xquat[g][1]; qq.y = W.xquat[g][2]; qq.z = W.xquat[g][3];
+            gc[h] = ld3(W.xpos[g]) + qrot(qq, ld3(ht.geom_pos[h * ngh + lane]));
+            gax[h] = qrot(qq, mk3(0, 0, 1));
+            ylo[h] = gc[h].y - gr - ghl; yhi[h] = gc[h].y + gr + ghl;
+          }
+        }
+        // -- finger colliders against the keys under them and the base
+        int i_lo[2], nW[2], ntot[2];
+        const float Rb = gr + ghl;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          i_lo[h] = 0; nW[h] = 0; ntot[h] = 0;
+          if (hasg && finger && gc[h].z - Rb < ZCULL) {
+            int a = (int)floorf((gc[h].y - Rb - kt.y0) / kt.pitch), b = (int)floorf((gc[h].y + Rb - kt.y0) / kt.pitch);
+            if (b >= 0 && a <= 51) {
+              a = max(a, 0); b = min(b, 51);
+              i_lo[h] = a; nW[h] = b - a + 1; ntot[h] = 2 * nW[h] + 2;  // whites, boundaries a..b+1, base
+            }
+          }
+        }
+        int tmax = max(ntot[0], ntot[1]);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) tmax = max(tmax, __shfl_xor_sync(FULL, tmax, off));
+        const float margin_p = o.pair_margin[PP_PAIRCLS_PIANO];
+        for (int t = 0; t < tmax; t++) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            int key = -1;
+            if (t < nW[h]) key = kt.white_key[i_lo[h] + t];
+            else if (t < 2 * nW[h] + 1) key = kt.boundary_black[i_lo[h] + t - nW[h]];
+            else if (t == 2 * nW[h] + 1 && ntot[h] > 0) key = PP_NKEY;
+            Hit h0, h1; h0.ok = false; h1.ok = false;
+            if (key >= 0) {
+              Box b;
+              if (key < PP_NKEY) {
+                float sq_, cq_;
+                sincosf(W.kq[key], &sq_, &cq_);
+                const float hx = kt.half[key][0];
+                b.p = mk3(kt.pos[key][0] - hx + hx * cq_, kt.pos[key][1], kt.pos[key][2] - hx * sq_);
+                b.cq = cq_; b.sq = sq_; b.h = ld3(kt.half[key]);
+              } else {
+                b.p = ld3(o.base_pos); b.cq = 1.f; b.sq = 0.f; b.h = ld3(o.base_half);
+              }
+              // the oracle's bounding-sphere cull is implied by the exact test (margin 0)
+              capsule_box(gc[h], gax[h], gr, ghl, b, margin_p, h0, h1);
+            }
+            const int ids = h | (gnode << 1) | (0 << 6) | (key << 8);
+            push_contact(W, h0.ok, ncon, ndrop, cap, h0, ids);
+            push_contact(W, h1.ok, ncon, ndrop, cap, h1, ids);
+          }
+        }
+        // -- fixed hand-hand pairs; the rh x lh block is skipped while the hands' y extents are apart
+        float ymin0 = ylo[0], ymax0 = yhi[0], ymin1 = ylo[1], ymax1 = yhi[1];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+          ymin0 = fminf(ymin0, __shfl_xor_sync(FULL, ymin0, off)); ymax0 = fmaxf(ymax0, __shfl_xor_sync(FULL, ymax0, off));
+          ymin1 = fminf(ymin1, __shfl_xor_sync(FULL, ymin1, off)); ymax1 = fmaxf(ymax1, __shfl_xor_sync(FULL, ymax1, off));
+        }
+        const bool apart = ymin0 > ymax1 || ymin1 > ymax0;
+        const int np = apart ? ht.npair_same : ht.npair;
+        const float margin_h = o.pair_margin[PP_PAIRCLS_HAND];
+        for (int p0 = 0; p0 < np; p0 += 32) {
+          const int p = p0 + lane;
+          Hit hh; hh.ok = false; int ids = 0;
+          if (p < np) {
+            const int g1 = ht.pair_g1[p], g2 = ht.pair_g2[p];
+            const int h1 = g1 >= ngh ? 1 : 0, h2 = g2 >= ngh ? 1 : 0;
+            const int n1 = ht.geom_body[g1] - h1 * PP_HB + 1, n2 = ht.geom_body[g2] - h2 * PP_HB + 1;
+            const int a1 = h1 * 26 + n1, a2 = h2 * 26 + n2;
+            f4 q1; q1.w = W.xquat[a1][0]; q1.x = W.xquat[a1][1]; q1.y = W.xquat[a1][2]; q1.z = W.xquat[a1][3];
+            f4 q2; q2.w = W.xquat[a2][0]; q2.x = W.xquat[a2][1]; q2.y = W.xquat[a2][2]; q2.z = W.xquat[a2][3];
+            const f3 c1 = ld3(W.xpos[a1]) + qrot(q1, ld3(ht.geom_pos[g1]));
+            const f3 c2 = ld3(W.xpos[a2]) + qrot(q2, ld3(ht.geom_pos[g2]));
+            const float r1 = ht.geom_r[g1], r2 = ht.geom_r[g2], l1 = ht.geom_hl[g1], l2 = ht.geom_hl[g2];
+            if (norm(c1 - c2) <= r1 + l1 + r2 + l2 + margin_h)
+              hh = capsule_capsule(c1, qrot(q1, mk3(0, 0, 1)), r1, l1, c2, qrot(q2, mk3(0, 0, 1)), r2, l2, margin_h);
+            ids = h1 | (n1 << 1) | (1 << 6) | ((h2 | (n2 << 1)) << 8);
+          }
+          push_contact(W, hh.ok, ncon, ndrop, cap, hh, ids);
+        }
+      }
+      __syncwarp();
+
+      // ================================================================ mj_makeConstraint
+      // velocities into the exchange vector (for aref)
+#pragma unroll
+      for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = v[h];
+      // key slots: contacts on the same key share one slot
+      int nslot = 0;
+      int my_nent = 0; float cD = 0.f, caref[4] = {0.f, 0.f, 0.f, 0.f}; int my_slot = -1;
+      unsigned cm[2] = {0u, 0u};
+      int ids = 0, kind = 0, key = -1;
+      if (lane < ncon) { ids = W.c_ids[lane]; kind = (ids >> 6) & 1; key = kind == 0 ? (ids >> 8) : -1; }
+      {
+        const bool wants = lane < ncon && kind == 0 && key < PP_NKEY && key >= 0;
+        const unsigned same = __match_any_sync(FULL, wants ? key : -1 - lane);
+        const bool leader = wants && (__ffs(same) - 1) == lane;
+        const unsigned lead = __ballot_sync(FULL, leader);
+        nslot = __popc(lead);
+        if (wants) {
+          const int s = __popc(lead & ((1u << (__ffs(same) - 1)) - 1u));
+          my_slot = s;
+          if (leader && s < KS) { W.slot_key[s] = (int8_t)key; W.key_slot[key] = (int8_t)s; }
+        }
+        if (nslot > KS) {  // out of slots: the contacts on the overflowing keys are dropped
+          const bool dropme = my_slot >= KS;
+          ndrop += __popc(__ballot_sync(FULL, dropme));
+          if (dropme) { my_slot = -2; }
+          nslot = KS;
+        }
+      }
+      __syncwarp();
+      bool dense[2] = {false, false}; bool coupled = false;
+      if (lane < ncon && my_slot != -2) {
+        const int c = lane;
+        const f3 pos = mk3(W.c_geo[0][c], W.c_geo[1][c], W.c_geo[2][c]);
+        const f3 n = mk3(W.c_geo[3][c], W.c_geo[4][c], W.c_geo[5][c]);
+        const float dist = W.c_geo[6][c];
+        // mju_makeFrame
+        f3 t1 = (n.y < 0.5f && n.y > -0.5f) ? mk3(0, 1, 0) : mk3(0, 0, 1);
+        t1 = t1 - dot(n, t1) * n; t1 = (1.f / norm(t1)) * t1;
+        const f3 t2 = cross(n, t1);
+        const int h1 = ids & 1, n1 = (ids >> 1) & 31;
+        int h2 = 0, n2 = 0;
+        const int pc = kind == 0 ? PP_PAIRCLS_PIANO : PP_PAIRCLS_HAND;
+        float tran = ht.binvw[h1 * PP_HB + n1 - 1];
+        unsigned a1 = anc_of(n1), a2 = 0u;
+        if (kind == 1) {
+          h2 = (ids >> 8) & 1; n2 = (ids >> 9) & 31;
+          tran += ht.binvw[h2 * PP_HB + n2 - 1];
+          a2 = anc_of(n2);
+          if (h1 == h2) { const unsigned sh = a1 & a2; a1 &= ~sh; a2 &= ~sh; cm[h1] = a1 | a2; }
+          else { cm[h1] = a1; cm[h2] = a2; }
+        } else {
+          if (key < PP_NKEY) tran += kt.binvw[key];
+          cm[h1] = a1;
+        }
+        // entries: rh dofs ascending, lh dofs ascending, key slot
+        int e = 0; f3 uv = mk3(0, 0, 0);
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          unsigned m = cm[h];
+          while (m) {
+            const int d = __ffs(m) - 1; m &= m - 1;
+            const int g = h * 26 + d;
+            const f3 ax = ld3(W.xaxis[g]);
+            const f3 col = d < 2 ? ax : cross(ax, pos - ld3(W.xpos[g]));
+            // jac(body2) - jac(body1): chain of geom1 enters with -, chain of geom2 with +
+            const bool second = kind == 1 && h == h2 && ((a2 >> d) & 1u) && !(h1 == h2 && ((a1 >> d) & 1u));
+            const float sg = second ? 1.f : -1.f;
+            const f3 u = mk3(sg * dot(n, col), sg * dot(t1, col), sg * dot(t2, col));
+            W.c_u[3 * e][c] = u.x; W.c_u[3 * e + 1][c] = u.y; W.c_u[3 * e + 2][c] = u.z;
+            W.c_col[e][c] = (uint8_t)g;
+            const float vg = W.va[g];
+            uv = uv + vg * u;
+            e++;
+          }
+        }
+        if (my_slot >= 0) {
+          const float hx = kt.half[key][0];
+          const f3 anchor = mk3(kt.pos[key][0] - hx, kt.pos[key][1], kt.pos[key][2]);
+          const f3 col = cross(mk3(0, 1, 0), pos - anchor);
+          const f3 u = mk3(dot(n, col), dot(t1, col), dot(t2, col));
+          W.c_u[3 * e][c] = u.x; W.c_u[3 * e + 1][c] = u.y; W.c_u[3 * e + 2][c] = u.z;
+          W.c_col[e][c] = (uint8_t)(52 + my_slot);
+          uv = uv + W.kv[key] * u;
+          e++;
+        }
+        my_nent = e;
+        W.c_mask[0][c] = cm[0]; W.c_mask[1][c] = cm[1]; W.c_slot[c] = (int8_t)my_slot; W.c_nent[c] = (int8_t)e;
+        // impedance, regularisation, reference acceleration (pyramidal, condim 3)
+        const float mu = o.pair_friction[pc], margin = o.pair_margin[pc];
+        float Kk, Bb;
+        pp_kb(o.pair_solref[pc], o.pair_solimp[pc], o.h, Kk, Bb);
+        const float imp = pp_impedance(o.pair_solimp[pc], dist, margin);
+        const float diag = tran + mu * mu * tran;
+        const float R0 = fmaxf(PP_MINVAL, (1.f - imp) * diag / imp);
+        const float R = 2.f * mu * mu / o.impratio * R0;
+        cD = 1.f / R;
+        const float vr[4] = {uv.x + mu * uv.y, uv.x - mu * uv.y, uv.x + mu * uv.z, uv.x - mu * uv.z};
+#pragma unroll
+        for (int k = 0; k < 4; k++) caref[k] = -Bb * vr[k] - Kk * imp * (dist - margin);
+        if (kind == 1) { if (h1 == h2) dense[h1] = true; else coupled = true; }
+      } else if (lane < ncon) {
+        W.c_mask[0][lane] = 0u; W.c_mask[1][lane] = 0u; W.c_slot[lane] = -1; W.c_nent[lane] = 0;
+      }
+      const float cmu = (lane < ncon) ? o.pair_friction[kind == 0 ? PP_PAIRCLS_PIANO : PP_PAIRCLS_HAND] : 0.f;
+      __syncwarp();
+      // a key touched from two different branches / hands breaks the tree sparsity
+      if (lane < nslot) {
+        unsigned u0 = 0u, u1 = 0u;
+        for (int c = 0; c < ncon; c++)
+          if (W.c_slot[c] == lane) { u0 |= W.c_mask[0][c]; u1 |= W.c_mask[1][c]; }
+        if (u0 && u1) coupled = true;
+        if (u0 && u0 != anc_of(31 - __clz(u0))) dense[0] = true;
+        if (u1 && u1 != anc_of(31 - __clz(u1))) dense[1] = true;
+      }
+      coupled = __any_sync(FULL, coupled);
+      dense[0] = __any_sync(FULL, dense[0]) || coupled;
+      dense[1] = __any_sync(FULL, dense[1]) || coupled;
+
+      // per-dof rows: frictionloss (always) and joint limit (when violated)
+      float fD[2], faref[2], floss[2], lsg[2], lD[2], laref[2];
+      int nefc = 4 * ncon;
+      {
+        float Kf, Bf;
+        pp_kb(o.friction_solref, o.friction_solimp, o.h, Kf, Bf);
+        const float impf = pp_impedance(o.friction_solimp, 0.f, 0.f);
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int hd = h * PP_HD + l;
+          floss[h] = L.dof ? ht.frictionloss[hd] : 0.f;
+          const float invw = ht.invw[hd];
+          fD[h] = 1.f / fmaxf(PP_MINVAL, (1.f - impf) * invw / impf);
+          faref[h] = -Bf * v[h];
+          LimitRow r; r.sgn = 0.f; r.D = 0.f; r.aref = 0.f;
+          if (L.dof) r = pp_limit_row(o, q[h], v[h], ht.range[hd][0], ht.range[hd][1], invw);
+          lsg[h] = r.sgn; lD[h] = r.D; laref[h] = r.aref;
+          nefc += __popc(__ballot_sync(FULL, floss[h] > 0.f)) + __popc(__ballot_sync(FULL, r.sgn != 0.f));
+        }
+      }
+      // key-slot scalars (lane s < nslot)
+      float sM = 1.f, sfs = 0.f, sa = 0.f, ssg = 0.f, sD = 0.f, saref = 0.f; int skey = 0;
+      if (lane < nslot) {
+        skey = W.slot_key[lane];
+        const float kq_ = W.kq[skey], kv_ = W.kv[skey];
+        const float applied = A.qfrc_applied ? A.qfrc_applied[sbase + skey] : 0.f;
+        sM = kt.M[skey]; sfs = pp_key_smooth(kt, skey, kq_, kv_, applied); sa = W.kw[skey];
+        const LimitRow r = pp_limit_row(o, kq_, kv_, 0.f, kt.hi[skey], kt.invw[skey]);
+        ssg = r.sgn; sD = r.D; saref = r.aref;
+      }
+
+      // ================================================================ mj_fwdConstraint (Newton)
+      int el[2];
+#pragma unroll
+      for (int h = 0; h < 2; h++) el[h] = dense[h] ? 25 : lane + L.ni.nsub - 1;
+      float* H = W.u.H;
+      float a[2] = {acc[0], acc[1]};  // warm start
+      float Ma[2] = {0.f, 0.f}, sMa = 0.f;
+      float jar[4] = {0.f, 0.f, 0.f, 0.f};
+      auto build_M = [&](float hdamp) {
+        // H <- M (+ hdamp * damping on the diagonal); zero the widened envelopes first
+        if (L.dof) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            if (dense[h]) {
+              const int g = h * 26 + lane, gend = coupled ? 51 : h * 26 + 25;
+              for (int gk = g; gk <= gend; gk++) H[hidx(g, gk)] = 0.f;
+            }
+          }
+        }
+        __syncwarp();
+        if (L.dof) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+#pragma unroll
+            for (int j = 0; j < 9; j++) {
+              const int an = j < 4 ? j : L.ni.cs + j - 4;
+              const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
+              if (valid) H[hidx(h * 26 + an, h * 26 + lane)] = Mr[h][j] + (an == lane ? hdamp * damp[h] : 0.f);
+            }
+          }
+        }
+        __syncwarp();
+      };
+      build_M(0.f);
+      // Ma at the warm start: tree entries of M only
+#pragma unroll
+      for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = a[h];
+      __syncwarp();
+      if (L.dof) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          float s = 0.f;
+          unsigned m = L.ni.anc;
+          while (m) { const int d = __ffs(m) - 1; m &= m - 1; s += H[hidx(h * 26 + d, h * 26 + lane)] * W.va[h * 26 + d]; }
+          for (int d = lane + 1; d < lane + L.ni.nsub; d++) s += H[hidx(h * 26 + lane, h * 26 + d)] * W.va[h * 26 + d];
+          Ma[h] = s;
+        }
+      }
+      if (lane < nslot) { W.va[52 + lane] = sa; sMa = sM * sa; }
+      __syncwarp();
+      if (lane < ncon) {
+        const f3 ua = contact_ux(W, lane, my_nent);
+        jar[0] = ua.x + cmu * ua.y - caref[0]; jar[1] = ua.x - cmu * ua.y - caref[1];
+        jar[2] = ua.x + cmu * ua.z - caref[2]; jar[3] = ua.x - cmu * ua.z - caref[3];
+      }
+      const float scale = 1.f / (o.meaninertia * (float)PP_NV);
+      int iter = 0;
+      const int maxit = min(o.iterations, 30);
+      for (; iter < maxit; iter++) {
+        // ---- row forces and curvatures at the current point
+        float ff[2], fc[2], lf[2], lc[2]; int fz[2];
+        float cf[4] = {0.f, 0.f, 0.f, 0.f}, cc[4] = {0.f, 0.f, 0.f, 0.f};
+        float sf = 0.f, sc = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          ff[h] = 0.f; fc[h] = 0.f; fz[h] = 0; lf[h] = 0.f; lc[h] = 0.f;
+          if (floss[h] > 0.f) row_fric(fD[h], floss[h], a[h] - faref[h], ff[h], fc[h], fz[h]);
+          if (lsg[h] != 0.f) row_ineq(lD[h], lsg[h] * a[h] - laref[h], lf[h], lc[h]);
+        }
+        if (ssg != 0.f) row_ineq(sD, ssg * sa - saref, sf, sc);
+        if (lane < ncon && my_slot != -2) {
+#pragma unroll
+          for (int k = 0; k < 4; k++) row_ineq(cD, jar[k], cf[k], cc[k]);
+          const int c = lane;
+          W.c_wf[0][c] = cf[0] + cf[1] + cf[2] + cf[3];
+          W.c_wf[1][c] = cmu * (cf[0] - cf[1]);
+          W.c_wf[2][c] = cmu * (cf[2] - cf[3]);
+          W.c_w[0][c] = cc[0] + cc[1] + cc[2] + cc[3];
+          W.c_w[1][c] = cmu * (cc[0] - cc[1]);
+          W.c_w[2][c] = cmu * cmu * (cc[0] + cc[1]);
+          W.c_w[3][c] = cmu * (cc[2] - cc[3]);
+          W.c_w[4][c] = cmu * cmu * (cc[2] + cc[3]);
+        } else if (lane < ncon) {
+          for (int k = 0; k < 3; k++) W.c_wf[k][lane] = 0.f;
+          for (int k = 0; k < 5; k++) W.c_w[k][lane] = 0.f;
+        }
+        __syncwarp();
+        // ---- gradient
+        float gj[2], gjs;
+        gather_jt(W, ncon, lane, gj, gjs);
+        float grad[2], sgrad = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; h++) grad[h] = L.dof ? (Ma[h] - fs[h] - ff[h] - lsg[h] * lf[h] - gj[h]) : 0.f;
+        if (lane < nslot) sgrad = sMa - sfs - ssg * sf - gjs;
+        // ---- Hessian: M + diagonal rows + contact cliques
+        if (iter > 0) build_M(0.f);
+        if (L.dof) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) H[hidx(h * 26 + lane, h * 26 + lane)] += fc[h] + lc[h];
+        }
+        for (int s = 0; s < nslot; s++) {
+          W.Kc[s][lane] = 0.f;
+          if (lane + 32 < 52) W.Kc[s][lane + 32] = 0.f;
+        }
+        __syncwarp();
+        float shss = sM + sc;  // H(slot, slot), lane < nslot
+        {
+          const unsigned lt = (1u << lane) - 1u;
+          for (int c = 0; c < ncon; c++) {
+            const float w0 = W.c_w[0][c];
+            if (w0 == 0.f) continue;  // no active row
+            const float w1 = W.c_w[1][c], w2 = W.c_w[2][c], w3 = W.c_w[3][c], w4 = W.c_w[4][c];
+            const unsigned m0 = W.c_mask[0][c], m1 = W.c_mask[1][c];
+            const int n0 = __popc(m0), n1_ = __popc(m1), slot = W.c_slot[c];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              const unsigned mh = h ? m1 : m0;
+              if (!((mh >> lane) & 1u)) continue;
+              const int e0 = (h ? n0 : 0) + __popc(mh & lt);
+              const float ux = W.c_u[3 * e0][c], uy = W.c_u[3 * e0 + 1][c], uz = W.c_u[3 * e0 + 2][c];
+              // z = W u (W symmetric 3x3 with zero (t1,t2) entry)
+              const float zx = w0 * ux + w1 * uy + w3 * uz, zy = w1 * ux + w2 * uy, zz = w3 * ux + w4 * uz;
+              const int g = h * 26 + lane;
+              const int etot = n0 + n1_ + (slot >= 0 ? 1 : 0);
+              for (int e = e0; e < etot; e++) {
+                const float val = zx * W.c_u[3 * e][c] + zy * W.c_u[3 * e + 1][c] + zz * W.c_u[3 * e + 2][c];
+                const int col = W.c_col[e][c];
+                if (col >= 52) W.Kc[col - 52][g] += val;
+                else H[hidx(g, col)] += val;
+              }
+            }
+            if (slot == lane) {
+              const int e0 = n0 + n1_;
+              const float ux = W.c_u[3 * e0][c], uy = W.c_u[3 * e0 + 1][c], uz = W.c_u[3 * e0 + 2][c];
+              shss += ux * (w0 * ux + w1 * uy + w3 * uz) + uy * (w1 * ux + w2 * uy) + uz * (w3 * ux + w4 * uz);
+            }
+          }
+        }
+        if (lane < nslot) W.hss[lane] = 1.f / shss;
+        __syncwarp();
+        // ---- eliminate the key slots (Schur complement), right-hand side b = -grad
+        float b[2] = {-grad[0], -grad[1]};
+        const float sb = -sgrad;
+        for (int s = 0; s < nslot; s++) {
+          const float ih = W.hss[s];
+          const float bs = __shfl_sync(FULL, sb, s) * ih;
+          if (L.dof) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              const int g = h * 26 + lane;
+              const float kg = W.Kc[s][g];
+              if (kg != 0.f) {
+                b[h] -= kg * bs;
+                const float cf_ = kg * ih;
+                const int gend = coupled ? 51 : h * 26 + el[h];
+                for (int gk = g; gk <= gend; gk++) H[hidx(g, gk)] -= cf_ * W.Kc[s][gk];
+              }
+            }
+          }
+        }
+        __syncwarp();
+        // ---- factorise and solve for the search direction
+        float dinv[2] = {1.f, 1.f};
+        if (coupled) { chol_coupled(H, lane, L.dof, dinv); solve_coupled(H, lane, L.dof, dinv, b); }
+        else { chol_uncoupled(H, lane, L.dof, el, dense, dinv); solve_uncoupled(H, lane, L.dof, el, dinv, b); }
+        float p[2] = {L.dof ? b[0] : 0.f, L.dof ? b[1] : 0.f};
+        __syncwarp();
+#pragma unroll
+        for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = p[h];
+        __syncwarp();
+        float sp = 0.f;
+        if (lane < nslot) {
+          float d = 0.f;
+          for (int g = 0; g < 52; g++) d += W.Kc[lane][g] * W.va[g];
+          sp = (sb - d) * W.hss[lane];
+          W.va[52 + lane] = sp;
+        }
+        __syncwarp();
+        // ---- J p for every row
+        float jp[4] = {0.f, 0.f, 0.f, 0.f};
+        if (lane < ncon && my_slot != -2) {
+          const f3 up = contact_ux(W, lane, my_nent);
+          jp[0] = up.x + cmu * up.y; jp[1] = up.x - cmu * up.y; jp[2] = up.x + cmu * up.z; jp[3] = up.x - cmu * up.z;
+          // curvature-weighted J p, for M p = -grad - J^T C J p
+          W.c_wf[0][lane] = cc[0] * jp[0] + cc[1] * jp[1] + cc[2] * jp[2] + cc[3] * jp[3];
+          W.c_wf[1][lane] = cmu * (cc[0] * jp[0] - cc[1] * jp[1]);
+          W.c_wf[2][lane] = cmu * (cc[2] * jp[2] - cc[3] * jp[3]);
+        }
+        __syncwarp();
+        float cj[2], cjs;
+        gather_jt(W, ncon, lane, cj, cjs);
+        float Mp[2], sMp = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; h++) Mp[h] = L.dof ? (-grad[h] - (fc[h] + lc[h]) * p[h] - cj[h]) : 0.f;
+        if (lane < nslot) sMp = sM * sp;
+        // ---- exact line search on phi(alpha) = cost(a + alpha p)
+        float g1 = grad[0] * p[0] + grad[1] * p[1] + sgrad * sp;
+        float g2 = p[0] * Mp[0] + p[1] * Mp[1] + sp * sMp;
+        float gauss1 = (Ma[0] - fs[0]) * p[0] + (Ma[1] - fs[1]) * p[1] + (sMa - sfs) * sp;
+        g1 = wsum(g1); g2 = wsum(g2); gauss1 = wsum(gauss1);
+        if (!(g1 < 0.f) || 0.5f * scale * (-g1) < 1e-10f) break;  // no descent left: converged
+        float alpha = 0.f, lo = 0.f, hi = -1.f;
+        bool changed = false;
+        for (int ls = 0; ls < 20; ls++) {
+          float dphi = 0.f, ddphi = 0.f;
+          bool ch = false;
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            float f_, c_; int z_;
+            if (floss[h] > 0.f) {
+              row_fric(fD[h], floss[h], a[h] - faref[h] + alpha * p[h], f_, c_, z_);
+              dphi -= f_ * p[h]; ddphi += c_ * p[h] * p[h]; ch |= z_ != fz[h];
+            }
+            if (lsg[h] != 0.f) {
+              const float jp_ = lsg[h] * p[h];
+              row_ineq(lD[h], lsg[h] * a[h] - laref[h] + alpha * jp_, f_, c_);
+              dphi -= f_ * jp_; ddphi += c_ * jp_ * jp_; ch |= (c_ != lc[h]);
+            }
+          }
+          if (ssg != 0.f) {
+            float f_, c_;
+            const float jp_ = ssg * sp;
+            row_ineq(sD, ssg * sa - saref + alpha * jp_, f_, c_);
+            dphi -= f_ * jp_; ddphi += c_ * jp_ * jp_; ch |= (c_ != sc);
+          }
+          if (lane < ncon && my_slot != -2) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+              float f_, c_;
+              row_ineq(cD, jar[k] + alpha * jp[k], f_, c_);
+              dphi -= f_ * jp[k]; ddphi += c_ * jp[k] * jp[k]; ch |= (c_ != cc[k]);
+            }
+          }
+          dphi = wsum(dphi) + gauss1 + alpha * g2;
+          ddphi = wsum(ddphi) + g2;
+          changed = __any_sync(FULL, ch);
+          if (fabsf(dphi) <= 1e-6f * fabsf(g1) || !(ddphi > 0.f)) break;
+          if (dphi < 0.f) lo = alpha; else hi = alpha;
+          float next = alpha - dphi / ddphi;
+          if (hi >= 0.f && (next <= lo || next >= hi)) next = 0.5f * (lo + hi);
+          if (next == alpha) break;
+          alpha = next;
+        }
+        // ---- move
+#pragma unroll
+        for (int h = 0; h < 2; h++) { a[h] += alpha * p[h]; Ma[h] += alpha * Mp[h]; }
+        sa += alpha * sp; sMa += alpha * sMp;
+#pragma unroll
+        for (int k = 0; k < 4; k++) jar[k] += alpha * jp[k];
+        // piecewise-quadratic cost: a full Newton step that crosses no breakpoint is exact
+        if (!changed && fabsf(alpha - 1.f) < 1e-3f) { iter++; break; }
+      }
+      // ---- solution: hand dofs, touched keys (slots), untouched keys in closed form
+#pragma unroll
+      for (int h = 0; h < 2; h++) acc[h] = a[h];
+      if (lane < nslot) W.va[52 + lane] = sa;
+      __syncwarp();
+
+      // ================================================================ mj_Euler (implicit damping)
+      {
+        bool nodense[2] = {false, false};
+        int elt[2] = {lane + L.ni.nsub - 1, lane + L.ni.nsub - 1};
+        const bool sv0 = dense[0], sv1 = dense[1], svc = coupled;
+        dense[0] = dense[1] = false; coupled = false;
+        build_M(o.h);
+        dense[0] = sv0; dense[1] = sv1; coupled = svc;
+        float dinv[2] = {1.f, 1.f};
+        chol_uncoupled(H, lane, L.dof, elt, nodense, dinv);
+        float x[2] = {Ma[0], Ma[1]};
+        solve_uncoupled(H, lane, L.dof, elt, dinv, x);
+        __syncwarp();
+#pragma unroll
+        for (int h = 0; h < 2; h++)
+          if (L.dof) { v[h] += o.h * x[h]; q[h] += o.h * v[h]; }
+      }
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        const int k = lane + 32 * i;
+        if (k >= PP_NKEY) continue;
+        const float Mk = kt.M[k];
+        const int slot = W.key_slot[k];
+        float ftot;
+        if (slot >= 0 && slot < KS) {
+          ak[i] = W.va[52 + slot];
+          ftot = Mk * ak[i];
+        } else {
+          const LimitRow r = pp_limit_row(o, qk[i], vk[i], 0.f, kt.hi[k], kt.invw[k]);
+          const float aa_ = pp_key_solve(Mk, fsk[i], r);
+          const float fcon = (r.sgn != 0.f && r.sgn * aa_ - r.aref < 0.f) ? -r.D * (r.sgn * aa_ - r.aref) * r.sgn : 0.f;
+          ak[i] = aa_;
+          ftot = fsk[i] + fcon;
+          nefc += 0;
+        }
+        pp_scalar_euler(Mk, kt.damping, o.h, ftot, qk[i], vk[i]);
+      }
+      __syncwarp();
+      cnt_ncon = ncon; cnt_iter = iter; cnt_drop = ndrop;
+      {  // key limit rows count towards nefc (diagnostic)
+        int nk = 0;
+#pragma unroll
+        for (int i = 0; i < 3; i++) { const int k = lane + 32 * i; if (k < PP_NKEY && (W.kq[k] < 0.f || W.kq[k] > kt.hi[k])) nk++; }
+        cnt_nefc = nefc + (int)wsum((float)nk);
+      }
+    }  // substeps
+    t_idx += 1;
+  } else {
+    t_idx = 0;
+  }
+
+  // ================================================================== trailing mj_step1: positions
+  Kin K;
+  forward_kinematics<false>(ht, o, L, q, v, K);
+  __syncwarp();
+#pragma unroll
+  for (int h = 0; h < 2; h++)
+    if (L.dof) {
+      const int g = h * 26 + lane;
+      st3(W.xpos[g], K.pos[h]);
+      W.xquat[g][0] = K.quat[h].w; W.xquat[g][1] = K.quat[h].x; W.xquat[g][2] = K.quat[h].y; W.xquat[g][3] = K.quat[h].z;
+    }
+  __syncwarp();
+  // fingertip sites: lanes 0..9
+  f3 site = mk3(0, 0, 0);
+  if (lane < PP_NSITE) {
+    const int hb = ht.site_body[lane], h = hb >= PP_HB ? 1 : 0, g = h * 26 + (hb - h * PP_HB) + 1;
+    f4 qq; qq.w = W.xquat[g][0]; qq.x = W.xquat[g][1]; qq.y = W.xquat[g][2]; qq.z = W.xquat[g][3];
+    site = ld3(W.xpos[g]) + qrot(qq, ld3(ht.site_pos[lane]));
+    st3(A.site_xpos + ((size_t)env * PP_NSITE + lane) * 3, site);
+  }
+  // forearm-forearm contact (forearm reward): the fixed pair of the two forearm capsules
+  bool forearm_hit = false;
+  if (ht.forearm_geom[0] >= 0 && ht.forearm_geom[1] >= 0) {
+    const int g1 = ht.forearm_geom[0], g2 = ht.forearm_geom[1];
+    const int a1 = ht.geom_body[g1] + 1, a2 = 26 + ht.geom_body[g2] - PP_HB + 1;
+    f4 q1; q1.w = W.xquat[a1][0]; q1.x = W.xquat[a1][1]; q1.y = W.xquat[a1][2]; q1.z = W.xquat[a1][3];
+    f4 q2; q2.w = W.xquat[a2][0]; q2.x = W.xquat[a2][1]; q2.y = W.xquat[a2][2]; q2.z = W.xquat[a2][3];
+    const f3 c1 = ld3(W.xpos[a1]) + qrot(q1, ld3(ht.geom_pos[g1]));
+    const f3 c2 = ld3(W.xpos[a2]) + qrot(q2, ld3(ht.geom_pos[g2]));
+    const Hit hh = capsule_capsule(c1, qrot(q1, mk3(0, 0, 1)), ht.geom_r[g1], ht.geom_hl[g1], c2,
+                                   qrot(q2, mk3(0, 0, 1)), ht.geom_r[g2], ht.geom_hl[g2],
+                                   o.pair_margin[PP_PAIRCLS_HAND]);
+    forearm_hit = hh.ok && hh.dist <= 0.f;
+  }
+  // actuatorvel sensor at the integrated velocity (refreshed by the trailing mj_step1)
+  float act_vel[2] = {0.f, 0.f};
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    const int ai = h * 22 + (lane < 22 ? lane : 0);
+    const int t0 = ht.act_trn0[ai] - h * 26, t1 = ht.act_trn1[ai] - h * 26;
+    float vv = __shfl_sync(FULL, v[h], t0);
+    const float v1 = __shfl_sync(FULL, v[h], t1 >= 0 ? t1 : 0);
+    if (ht.act_trn1[ai] >= 0) vv += v1;
+    act_vel[h] = lane < 22 ? vv : 0.f;
+  }
+
+  // ================================================================== task epilogue
+  // Piano._update_key_state (piano.py:178-192)
+  float normalized[3]; bool active[3];
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const int k = lane + 32 * i;
+    normalized[i] = 0.f; active[i] = false;
+    if (k < PP_NKEY) pp_key_state(qk[i], kt.hi[k], normalized[i], active[i]);
+  }
+  const bool sustain_on = sustain >= 0.5f;
+  const int t_cur = t_idx > 0 ? t_idx - 1 : 0;  // frame just played (goal_current)
+  const uint8_t* goal_cur = A.goal + (size_t)t_cur * 89;
+  // key_press reward (piano_with_shadow_hands.py:279-298)
+  float kp_sum = 0.f; int kp_on = 0; bool wrong = false;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const int k = lane + 32 * i;
+    if (k >= PP_NKEY) continue;
+    if (goal_cur[k]) { kp_on++; kp_sum += pp_tolerance(1.f - normalized[i], 0.05f, 0.5f); }
+    else if (active[i]) wrong = true;
+  }
+  kp_sum = wsum(kp_sum);
+  const int n_on = (int)(wsum((float)kp_on) + 0.5f);
+  const bool failure = __any_sync(FULL, wrong);
+  float energy0 = wsum(fabsf(act_force[0]) * fabsf(act_vel[0]));
+  float energy1 = wsum(fabsf(act_force[1]) * fabsf(act_vel[1]));
+  // fingering reward (:300-331): fingertip site to key surface point, world offsets
+  float fing = 0.f;
+  if (A.has_fingering) {
+    float tot = 0.f; int cnt = 0;
+    for (int p0 = 0; p0 < A.pmax; p0 += 32) {
+      int key = -1, finger = 0;
+      if (p0 + lane < A.pmax && !do_reset) {
+        const int16_t* pr = A.pairs + ((size_t)t_cur * A.pmax + p0 + lane) * 2;
+        key = pr[0]; finger = pr[1];
+      }
+      const bool has = key >= 0;
+      // rh fingers 0..4 -> sites 0..4, lh fingers 5..9 -> sites 5..9; -1 wraps like python (rh site 4)
+      const int sidx = has ? (finger < 0 ? 4 : min(finger, 9)) : 0;
+      const f3 tip = shfl3(site, sidx);
+      const int kk = has ? key : 0;
+      // the key angle lives in the owner lane's registers
+      const float q0 = __shfl_sync(FULL, qk[0], kk & 31), q1 = __shfl_sync(FULL, qk[1], kk & 31),
+                  q2 = __shfl_sync(FULL, qk[2], kk & 31);
+      float val = 0.f;
+      if (has) {
+        const float kqv = (kk >> 5) == 0 ? q0 : (kk >> 5) == 1 ? q1 : q2;
+        float sq_, cq_;
+        sincosf(kqv, &sq_, &cq_);
+        const float hx = kt.half[kk][0];
+        // key geom centre (rotated about the hinge) + world-axis offsets (0.35 size_x, 0, 0.5 size_z)
+        const f3 kp = mk3(kt.pos[kk][0] - hx + hx * cq_ + 0.35f * hx, kt.pos[kk][1],
+                          kt.pos[kk][2] - hx * sq_ + 0.5f * kt.half[kk][2]);
+        val = pp_tolerance(norm(kp - tip), 0.01f, 0.1f);
+      }
+      tot += wsum(val);
+      cnt += __popc(__ballot_sync(FULL, has));
+    }
+    fing = cnt > 0 ? tot / (float)cnt : 0.f;
+  } else {
+    fing = n_on == 0 ? 1.f : 0.f;  // OT fingering: exact only for the empty case
+  }
+
+  const bool should_terminate = !do_reset && t_idx == T;
+  bool done = should_terminate;
+  float discount = 1.f;
+  if (!do_reset && A.wrong_press_termination && failure && !should_terminate) { done = true; discount = 0.f; }
+
+  // ---- write back state
+#pragma unroll
+  for (int h = 0; h < 2; h++)
+    if (L.dof) {
+      A.qpos[sbase + PP_NKEY + h * PP_HD + lane] = q[h];
+      A.qvel[sbase + PP_NKEY + h * PP_HD + lane] = v[h];
+      A.warm[sbase + PP_NKEY + h * PP_HD + lane] = acc[h];
+      A.qacc[sbase + PP_NKEY + h * PP_HD + lane] = acc[h];
+    }
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const int k = lane + 32 * i;
+    if (k < PP_NKEY) {
+      A.qpos[sbase + k] = qk[i]; A.qvel[sbase + k] = vk[i]; A.warm[sbase + k] = ak[i]; A.qacc[sbase + k] = ak[i];
+      A.activation[(size_t)env * PP_NKEY + k] = active[i] ? 1 : 0;
+    }
+  }
+#pragma unroll
+  for (int h = 0; h < 2; h++)
+    if (lane < 22) {
+      A.act_force[(size_t)env * PP_NU_HANDS + h * 22 + lane] = act_force[h];
+      A.act_vel[(size_t)env * PP_NU_HANDS + h * 22 + lane] = act_vel[h];
+    }
+  if (lane == 0) {
+    A.t_idx[env] = t_idx;
+    A.sustain[env] = sustain;
+    A.needs_reset[env] = done ? 1 : 0;
+    A.counters[(size_t)env * 4 + 0] = cnt_ncon; A.counters[(size_t)env * 4 + 1] = cnt_nefc;
+    A.counters[(size_t)env * 4 + 2] = cnt_iter; A.counters[(size_t)env * 4 + 3] = cnt_drop;
+    if (A.mode == PP_MODE_STEP) {
+      float terms[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+      if (!do_reset) {
+        // CompositeReward.compute: sum in insertion order (composite_reward.py:46-56)
+        terms[0] = (n_on > 0 ? 0.5f * (kp_sum / (float)n_on) : 0.f) + 0.5f * (failure ? 0.f : 1.f);
+        terms[1] = pp_tolerance((float)goal_cur[88] - (sustain_on ? 1.f : 0.f), 0.05f, 0.5f);
+        terms[2] = 0.f - A.energy_coef * energy0 - A.energy_coef * energy1;
+        terms[3] = fing;
+        terms[4] = A.disable_forearm_reward ? 0.f : (forearm_hit ? 0.f : 0.5f);
+      }
+      float rew = 0.f;
+      for (int j = 0; j < 5; j++) rew += terms[j];
+      A.reward[env] = rew;
+      if (A.reward_terms) for (int j = 0; j < 5; j++) A.reward_terms[(size_t)env * 5 + j] = terms[j];
+      A.done[env] = done ? 1 : 0;
+      if (A.discount) A.discount[env] = discount;
+    }
+  }
+  // ---- observation: goal | fingering | piano/state | sustain_state | rh joints | lh joints
+  if (A.obs) {
+    float* obs = A.obs + (size_t)env * OD;
+    const int t0 = t_idx == T ? T - 1 : t_idx;  // both updates are skipped after the last frame
+    const int ng = (Lk + 1) * 89;
+    for (int i = lane; i < ng; i += 32) {
+      const int f = t0 + i / 89;
+      obs[i] = f < T ? (float)A.goal[(size_t)f * 89 + (i % 89)] : 0.f;
+    }
+    int off = ng;
+    if (A.has_fingering) {
+      // (2,5) flags of the fingers used in frame t0 (:391-412)
+      unsigned used = 0u;
+      for (int p = 0; p < A.pmax; p++) {
+        const int16_t* pr = A.pairs + ((size_t)t0 * A.pmax + p) * 2;
+        if (pr[0] >= 0) {
+          const int f = pr[1];
+          const int slot = f < 5 ? (f < 0 ? f + 5 : f) : 5 + min(f - 5, 4);  // python negative index wraps
+          used |= 1u << slot;
+        }
+      }
+      if (lane < 10) obs[off + lane] = (used >> lane) & 1u ? 1.f : 0.f;
+      off += 10;
+    }
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      const int k = lane + 32 * i;
+      if (k < PP_NKEY) obs[off + k] = normalized[i];
+    }
+    if (lane == 0) obs[off + 88] = sustain;
+    off += 89;
+    // hand.joints order: the 24 menagerie joints, then forearm_tx, forearm_ty
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+      if (L.dof) obs[off + h * 26 + (lane >= 2 ? lane - 2 : 24 + lane)] = q[h];
+  }
+}
+
+void pp_launch_hands(const HandsArgs& A, cudaStream_t stream) {
+  static bool configured = false;
+  const size_t smem = sizeof(WarpShared);
+  if (!configured) {
+    cudaFuncSetAttribute(pp_hands_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured = true;
+  }
+  pp_hands_step_kernel<<<A.num_envs, 32, smem, stream>>>(A);
+}
+size_t pp_hands_smem_bytes() { return sizeof(WarpShared); }
