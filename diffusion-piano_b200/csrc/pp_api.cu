@@ -299,7 +299,7 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(dalloc(&e->act_force, (size_t)N * (e->nu ? e->nu : 1)));
   CUDA_OK(dalloc(&e->act_vel, (size_t)N * (e->nu ? e->nu : 1)));
   CUDA_OK(dalloc(&e->site_xpos, (size_t)N * 3 * PP_NSITE));
-  CUDA_OK(dalloc(&e->activation, (size_t)N * 88)); CUDA_OK(dalloc(&e->counters, (size_t)N * 4));
+  CUDA_OK(dalloc(&e->activation, (size_t)N * 88)); CUDA_OK(dalloc(&e->counters, (size_t)N * 8));
   CUDA_OK(dalloc(&e->act_min_d, e->action_dim)); CUDA_OK(dalloc(&e->act_max_d, e->action_dim));
   CUDA_OK(cudaMemcpy(e->act_min_d, e->act_min.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
   CUDA_OK(cudaMemcpy(e->act_max_d, e->act_max.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
@@ -486,6 +486,6 @@ extern "C" int pp_get_diag(pp_env* e, float* qacc, float* act_force, float* act_
   if (e->nu) { COPY_IF(act_force, e->act_force, N * e->nu * 4); COPY_IF(act_vel, e->act_vel, N * e->nu * 4); }
   COPY_IF(site_xpos, e->site_xpos, N * 3 * PP_NSITE * 4);
   COPY_IF(activation, e->activation, N * 88);
-  COPY_IF(counters, e->counters, N * 4 * 4);
+  COPY_IF(counters, e->counters, N * 8 * 4);
   return PP_OK;
 }

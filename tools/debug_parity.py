@@ -34,7 +34,7 @@ def run(name, ctrl_fn, steps, gravcomp=False, dt=0.005, verbose_every=1):
     dev = "cuda"
     qpos = torch.zeros((2, nv), device=dev); qvel = torch.zeros((2, nv), device=dev); warm = torch.zeros((2, nv), device=dev)
     qacc = torch.zeros((2, nv), device=dev); af = torch.zeros((2, 44), device=dev); av = torch.zeros((2, 44), device=dev)
-    sx = torch.zeros((2, 10, 3), device=dev); cnt = torch.zeros((2, 4), dtype=torch.int32, device=dev)
+    sx = torch.zeros((2, 10, 3), device=dev); cnt = torch.zeros((2, 8), dtype=torch.int32, device=dev)
     print(f"=== {name}: dt={dt} gravcomp={gravcomp}")
     print(" step | ncon g/o | nefc g/o | it g/o | qacc rel hand | qacc rel key | qpos abs | qvel abs | frc abs | site abs | rew g/o | drift qpos")
     worst = dict(qacc=0.0, qpos=0.0)
