@@ -35,29 +35,52 @@ constexpr int NE = 18;   // jacobian entries per contact (two 9-dof chains, or c
 constexpr unsigned FULL = 0xffffffffu;
 constexpr float ZCULL = 0.045f;  // nothing of the piano is above this height
 
+constexpr int LRC = 8;       // contacts that couple two fronts (hand-hand, doubly touched key)
+constexpr int LRR = 3 * LRC; // rank of their Woodbury correction (3 per contact: U V, W = V V^T)
+
+// Shared memory of one warp. Two phases of a substep alias each other: `k` (kinematics ..
+// mj_makeConstraint) and `s` (the solver).
 struct WarpShared {
-  float xpos[52][3];   // joint anchor (= body origin) of every hand dof node, world
-  float xaxis[52][3];  // joint axis, world
-  float xquat[52][4];  // body orientation of the node
-  float S[52][6];      // spatial motion axis about the hand's reference point
+  union {
+    struct {
+      float xpos[52][3];   // joint anchor (= body origin) of every hand dof node, world
+      float xaxis[52][3];  // joint axis, world
+      float xquat[52][4];  // body orientation of the node
+      float S[52][6];      // spatial motion axis about the hand's reference point
+      float raw[52][16];   // body spatial inertia (10) + RNE force (6)
+      float comp[10][16];  // composite sums of the finger chains
+      float c_geo[7][NC];  // contact pos, normal, dist
+    } k;
+    struct {
+      union {
+        struct {
+          float Z[LRR + 1][52 + KS];  // row 0: -grad -> y0; rows 1..m: low-rank columns B -> H_t^-1 B
+          float C[LRR][LRR + 1];      // capacitance I + B^T H_t^-1 B | B^T y0
+        };
+        struct {                      // dense fallback (more than LRC cross-finger contacts)
+          float Hd[52 * 53 / 2];      // packed: A(gi <= gk) at gk(gk+1)/2 + gi
+          float Kcd[KS][52];
+        };
+      };
+      float Ht[52][9];            // H_t(ancestor j of dof, dof): tree entries only (like Mt)
+      float Kc[KS][9];            // H_t(ancestor j on the slot's root path, key slot)
+      float hss[KS];              // 1 / H_t(slot, slot)
+    } s;
+  } a;
   float kq[PP_NKEY], kv[PP_NKEY], kw[PP_NKEY];  // key qpos, qvel, warm-start acceleration
   int8_t key_slot[PP_NKEY];
   int8_t slot_key[KS];
-  union {
-    struct { float raw[52][16]; float comp[10][16]; } dyn;  // spatial inertia (10) + force (6)
-    float H[52 * 53 / 2];  // packed upper envelope: A(gi<=gk) at gk(gk+1)/2 + gi
-  } u;
-  float Kc[KS][52];       // H(hand dof, key slot)
-  float hss[KS];          // 1 / H(slot, slot)
+  unsigned slot_mask[KS]; // hand dofs coupled to the slot (a root path of one finger)
+  int8_t slot_hand[KS];
+  float Mt[52][9];        // M(ancestor j of dof, dof): j < 4 root dofs 0..3, j >= 4 the dof's chain
   float va[52 + KS];      // vector exchange (acceleration / velocity / search direction)
   // contacts, SoA over the contact index
   float c_u[NE * 3][NC];  // per entry: (n, t1, t2) . jacobian column
   uint8_t c_col[NE][NC];  // column of the entry: hand dof 0..51 or 52+slot
   unsigned c_mask[2][NC]; // hand dofs in the entry list, per hand (ascending dof order)
-  int8_t c_slot[NC], c_nent[NC];
+  int8_t c_slot[NC], c_nent[NC], c_lr[NC];
   float c_w[5][NC];       // D * (sum c, mu (c0-c1), mu^2 (c0+c1), mu (c2-c3), mu^2 (c2+c3))
   float c_wf[3][NC];      // 3-vector weight of the rows (forces, or curvature * jp)
-  float c_geo[7][NC];     // pos, normal, dist
   int c_ids[NC];          // h1 | node1<<1 | kind<<6 | (key or h2|node2<<1)<<8
 };
 
@@ -80,7 +103,9 @@ __device__ __forceinline__ int nsub_of(int l) {
 }
 __device__ __forceinline__ unsigned anc_of(int l) { return node_info(l).anc; }
 __device__ __forceinline__ int tri(int i) { return (i * (i + 1)) >> 1; }
-__device__ __forceinline__ int hidx(int gi, int gk) { return tri(gk) + gi; }  // gi <= gk
+__device__ __forceinline__ int cs_of(int l) { return l >= 21 ? 21 : l >= 16 ? 16 : l >= 12 ? 12 : l >= 8 ? 8 : l >= 4 ? 4 : 0; }
+// position of ancestor `a` in the ancestor list of a dof whose chain starts at cs
+__device__ __forceinline__ int apos(int a, int cs) { return a < 4 ? a : 4 + a - cs; }
 __device__ __forceinline__ f3 shfl3(f3 v, int src) {
   return mk3(__shfl_sync(FULL, v.x, src), __shfl_sync(FULL, v.y, src), __shfl_sync(FULL, v.z, src));
 }
@@ -218,9 +243,9 @@ __device__ __forceinline__ void push_contact(WarpShared& W, bool ok, int& ncon, 
   if (b == 0u) return;
   const int idx = ncon + __popc(b & ((1u << (threadIdx.x & 31)) - 1u));
   if (ok && idx < cap) {
-    W.c_geo[0][idx] = h.pos.x; W.c_geo[1][idx] = h.pos.y; W.c_geo[2][idx] = h.pos.z;
-    W.c_geo[3][idx] = h.n.x; W.c_geo[4][idx] = h.n.y; W.c_geo[5][idx] = h.n.z;
-    W.c_geo[6][idx] = h.dist;
+    W.a.k.c_geo[0][idx] = h.pos.x; W.a.k.c_geo[1][idx] = h.pos.y; W.a.k.c_geo[2][idx] = h.pos.z;
+    W.a.k.c_geo[3][idx] = h.n.x; W.a.k.c_geo[4][idx] = h.n.y; W.a.k.c_geo[5][idx] = h.n.z;
+    W.a.k.c_geo[6][idx] = h.dist;
     W.c_ids[idx] = ids;
   }
   const int tot = ncon + __popc(b);
@@ -261,67 +286,12 @@ __device__ __forceinline__ f3 contact_ux(const WarpShared& W, int c, int nent) {
   return r;
 }
 
-// ------------------------------------------------------------------ envelope Cholesky
-// Hand rows are eliminated leaves-first (dof 25 .. 0), so a row's off-diagonals are its
-// descendants: row g holds A(g, g+1 .. e(g)). In tree mode e(g) = last descendant and there
-// is no fill-in; dense / coupled modes only widen e(g). Lane l owns rows l (rh) and 26+l (lh).
-// el[h]: local envelope end of the lane's row of hand h (uncoupled), dinv[h]: 1/L(g,g).
-__device__ __forceinline__ void chol_uncoupled(float* H, int lane, bool dof, const int el[2], const bool dense[2],
-                                               float dinv[2]) {
-  for (int lj = 25; lj >= 0; lj--) {
-    const int nsj = nsub_of(lj);
-    float s[2];
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-      const int ej = dense[h] ? 25 : lj + nsj - 1;
-      const int g = h * 26 + lane, gj = h * 26 + lj;
-      const bool act = dof && lane <= lj && el[h] >= lj;
-      float acc = 0.f;
-      if (act) {
-        acc = H[hidx(g, gj)];
-        const int gend = h * 26 + min(el[h], ej);
-        int gk = gj + 1, base = tri(gk);
-        for (; gk <= gend; gk++) { acc -= H[base + g] * H[base + gj]; base += gk + 1; }
-      }
-      s[h] = acc;
-    }
-    __syncwarp();
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-      const float d = fmaxf(__shfl_sync(FULL, s[h], lj), 1e-30f);
-      const float inv = rsqrtf(d);
-      const bool act = dof && lane <= lj && el[h] >= lj;
-      if (act) H[hidx(h * 26 + lane, h * 26 + lj)] = s[h] * inv;
-      if (lane == lj) dinv[h] = inv;
-    }
-    __syncwarp();
-  }
-}
-
-// solves (L L^T) x = b in place; b[h] per lane
-__device__ __forceinline__ void solve_uncoupled(const float* H, int lane, bool dof, const int el[2],
-                                                const float dinv[2], float b[2]) {
-  for (int lj = 25; lj >= 0; lj--) {  // forward: leaves first
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-      const float y = __shfl_sync(FULL, b[h] * dinv[h], lj);
-      if (lane == lj) b[h] = y;
-      else if (dof && lane < lj && el[h] >= lj) b[h] -= H[hidx(h * 26 + lane, h * 26 + lj)] * y;
-    }
-  }
-  for (int li = 0; li < 26; li++) {  // backward: root first
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-      const float x = __shfl_sync(FULL, b[h] * dinv[h], li);
-      const int ei = __shfl_sync(FULL, el[h], li);
-      if (lane == li) b[h] = x;
-      else if (dof && lane > li && lane <= ei) b[h] -= H[hidx(h * 26 + li, h * 26 + lane)] * x;
-    }
-  }
-}
-
-// coupled 52x52 (an rh-lh contact or a key touched by both hands): full envelopes
-__device__ __forceinline__ void chol_coupled(float* H, int lane, bool dof, float dinv[2]) {
+// ------------------------------------------------------------------ dense fallback
+// More than LRC cross-finger contacts: the whole 52x52 hand block is factorised densely in shared
+// memory (rows eliminated 51 .. 0, lane l owns rows l and 26+l). Rare, kept out of line.
+__device__ __forceinline__ int hidx(int gi, int gk) { return tri(gk) + gi; }  // gi <= gk
+__device__ __noinline__ void dense_factor_solve(float* H, int lane, bool dof, float b[2]) {
+  float dinv[2] = {1.f, 1.f};
   for (int gj = 51; gj >= 0; gj--) {
     float s[2];
 #pragma unroll
@@ -335,10 +305,8 @@ __device__ __forceinline__ void chol_coupled(float* H, int lane, bool dof, float
       }
       s[h] = acc;
     }
-    __syncwarp();
     const int hj = gj >= 26 ? 1 : 0, lj = gj - 26 * hj;
-    const float d = fmaxf(__shfl_sync(FULL, hj ? s[1] : s[0], lj), 1e-30f);
-    const float inv = rsqrtf(d);
+    const float inv = rsqrtf(fmaxf(__shfl_sync(FULL, hj ? s[1] : s[0], lj), 1e-30f));
 #pragma unroll
     for (int h = 0; h < 2; h++) {
       const int g = h * 26 + lane;
@@ -347,9 +315,6 @@ __device__ __forceinline__ void chol_coupled(float* H, int lane, bool dof, float
     }
     __syncwarp();
   }
-}
-
-__device__ __forceinline__ void solve_coupled(const float* H, int lane, bool dof, const float dinv[2], float b[2]) {
   for (int gj = 51; gj >= 0; gj--) {
     const int hj = gj >= 26 ? 1 : 0, lj = gj - 26 * hj;
     const float y = __shfl_sync(FULL, (hj ? b[1] : b[0]) * (hj ? dinv[1] : dinv[0]), lj);
@@ -442,7 +407,7 @@ __device__ __forceinline__ void forward_kinematics(const HandTables& ht, const O
 }  // namespace
 
 // ====================================================================== the step kernel
-__global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
+__global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WarpShared& W = *reinterpret_cast<WarpShared*>(smem_raw);
   const int lane = threadIdx.x & 31;
@@ -468,7 +433,9 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
   int cnt_ncon = 0, cnt_nefc = 0, cnt_iter = 0, cnt_drop = 0;
   int sum_iter = 0, sum_ls = 0, sum_dense = 0, sum_coupled = 0;
   const size_t sbase = (size_t)env * PP_NV;
-  const int cap = A.max_contacts > 0 && A.max_contacts < NC ? A.max_contacts : NC;
+  const int mc_ = A.max_contacts & 255;
+  const bool dbg_all_lr = (A.max_contacts & 256) != 0;  // test hook: every contact through the low-rank path
+  const int cap = mc_ > 0 && mc_ < NC ? mc_ : NC;
   const int ngh = ht.ngeom >> 1;
 
   if (!do_reset) {
@@ -513,10 +480,10 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
         Sl[h] = slide ? K.axw[h] : cross(K.pos[h] - K.ref[h], K.axw[h]);
         if (L.dof) {
           const int g = h * 26 + lane;
-          st3(W.xpos[g], K.pos[h]); st3(W.xaxis[g], K.axw[h]);
-          W.xquat[g][0] = K.quat[h].w; W.xquat[g][1] = K.quat[h].x; W.xquat[g][2] = K.quat[h].y; W.xquat[g][3] = K.quat[h].z;
+          st3(W.a.k.xpos[g], K.pos[h]); st3(W.a.k.xaxis[g], K.axw[h]);
+          W.a.k.xquat[g][0] = K.quat[h].w; W.a.k.xquat[g][1] = K.quat[h].x; W.a.k.xquat[g][2] = K.quat[h].y; W.a.k.xquat[g][3] = K.quat[h].z;
           const f3 sa = slide ? mk3(0, 0, 0) : K.axw[h];
-          W.S[g][0] = sa.x; W.S[g][1] = sa.y; W.S[g][2] = sa.z; W.S[g][3] = Sl[h].x; W.S[g][4] = Sl[h].y; W.S[g][5] = Sl[h].z;
+          W.a.k.S[g][0] = sa.x; W.a.k.S[g][1] = sa.y; W.a.k.S[g][2] = sa.z; W.a.k.S[g][3] = Sl[h].x; W.a.k.S[g][4] = Sl[h].y; W.a.k.S[g][5] = Sl[h].z;
         }
       }
       // ---- body spatial inertia about ref + RNE body force (node 0 is massless)
@@ -557,7 +524,7 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
         }
         if (L.dof) {
 #pragma unroll
-          for (int i = 0; i < 16; i++) W.u.dyn.raw[h * 26 + lane][i] = r16[i];
+          for (int i = 0; i < 16; i++) W.a.k.raw[h * 26 + lane][i] = r16[i];
         }
       }
       __syncwarp();
@@ -570,11 +537,11 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
         if (L.dof && lane >= 4) {
           for (int k = 0; k < L.ni.nsub; k++)
 #pragma unroll
-            for (int i = 0; i < 16; i++) comp[h][i] += W.u.dyn.raw[h * 26 + lane + k][i];
+            for (int i = 0; i < 16; i++) comp[h][i] += W.a.k.raw[h * 26 + lane + k][i];
           if (lane == L.ni.cs) {
             const int ci = h * 5 + (lane == 4 ? 0 : lane == 8 ? 1 : lane == 12 ? 2 : lane == 16 ? 3 : 4);
 #pragma unroll
-            for (int i = 0; i < 16; i++) W.u.dyn.comp[ci][i] = comp[h][i];
+            for (int i = 0; i < 16; i++) W.a.k.comp[ci][i] = comp[h][i];
           }
         }
       }
@@ -584,10 +551,10 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
         if (lane < 4) {
           for (int k = lane; k < 4; k++)
 #pragma unroll
-            for (int i = 0; i < 16; i++) comp[h][i] += W.u.dyn.raw[h * 26 + k][i];
+            for (int i = 0; i < 16; i++) comp[h][i] += W.a.k.raw[h * 26 + k][i];
           for (int k = 0; k < 5; k++)
 #pragma unroll
-            for (int i = 0; i < 16; i++) comp[h][i] += W.u.dyn.comp[h * 5 + k][i];
+            for (int i = 0; i < 16; i++) comp[h][i] += W.a.k.comp[h * 5 + k][i];
         }
       }
       __syncwarp();  // u.dyn is dead from here on (H aliases it)
@@ -609,11 +576,12 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
           const bool valid = L.dof && (j < 4 ? (j <= lane) : (lane >= 4 && a <= lane));
           float mv = 0.f;
           if (valid) {
-            const float* Sa = W.S[h * 26 + a];
+            const float* Sa = W.a.k.S[h * 26 + a];
             mv = Sa[0] * Fn.x + Sa[1] * Fn.y + Sa[2] * Fn.z + Sa[3] * Ff.x + Sa[4] * Ff.y + Sa[5] * Ff.z;
             if (a == lane) mv += ht.armature[h * PP_HD + l];
           }
           Mr[h][j] = mv;
+          if (L.dof) W.Mt[h * 26 + lane][j] = mv;
         }
       }
       // ---- mj_fwdActuation (position servos on joints / 2-joint fixed tendons) + qfrc_smooth
@@ -660,8 +628,8 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
           gc[h] = mk3(0, 0, 1); gax[h] = mk3(0, 0, 1); ylo[h] = 1e9f; yhi[h] = -1e9f;
           if (hasg) {
             const int g = h * 26 + gnode;
-            f4 qq; qq.w = W.xquat[g][0]; qq.x = W.xquat[g][1]; qq.y = W.xquat[g][2]; qq.z = W.xquat[g][3];
-            gc[h] = ld3(W.xpos[g]) + qrot(qq, ld3(ht.geom_pos[h * ngh + lane]));
+            f4 qq; qq.w = W.a.k.xquat[g][0]; qq.x = W.a.k.xquat[g][1]; qq.y = W.a.k.xquat[g][2]; qq.z = W.a.k.xquat[g][3];
+            gc[h] = ld3(W.a.k.xpos[g]) + qrot(qq, ld3(ht.geom_pos[h * ngh + lane]));
             gax[h] = qrot(qq, mk3(0, 0, 1));
             ylo[h] = gc[h].y - gr - ghl; yhi[h] = gc[h].y + gr + ghl;
           }
@@ -729,10 +697,10 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
             const int h1 = g1 >= ngh ? 1 : 0, h2 = g2 >= ngh ? 1 : 0;
             const int n1 = ht.geom_body[g1] - h1 * PP_HB + 1, n2 = ht.geom_body[g2] - h2 * PP_HB + 1;
             const int a1 = h1 * 26 + n1, a2 = h2 * 26 + n2;
-            f4 q1; q1.w = W.xquat[a1][0]; q1.x = W.xquat[a1][1]; q1.y = W.xquat[a1][2]; q1.z = W.xquat[a1][3];
-            f4 q2; q2.w = W.xquat[a2][0]; q2.x = W.xquat[a2][1]; q2.y = W.xquat[a2][2]; q2.z = W.xquat[a2][3];
-            const f3 c1 = ld3(W.xpos[a1]) + qrot(q1, ld3(ht.geom_pos[g1]));
-            const f3 c2 = ld3(W.xpos[a2]) + qrot(q2, ld3(ht.geom_pos[g2]));
+            f4 q1; q1.w = W.a.k.xquat[a1][0]; q1.x = W.a.k.xquat[a1][1]; q1.y = W.a.k.xquat[a1][2]; q1.z = W.a.k.xquat[a1][3];
+            f4 q2; q2.w = W.a.k.xquat[a2][0]; q2.x = W.a.k.xquat[a2][1]; q2.y = W.a.k.xquat[a2][2]; q2.z = W.a.k.xquat[a2][3];
+            const f3 c1 = ld3(W.a.k.xpos[a1]) + qrot(q1, ld3(ht.geom_pos[g1]));
+            const f3 c2 = ld3(W.a.k.xpos[a2]) + qrot(q2, ld3(ht.geom_pos[g2]));
             const float r1 = ht.geom_r[g1], r2 = ht.geom_r[g2], l1 = ht.geom_hl[g1], l2 = ht.geom_hl[g2];
             if (norm(c1 - c2) <= r1 + l1 + r2 + l2 + margin_h)
               hh = capsule_capsule(c1, qrot(q1, mk3(0, 0, 1)), r1, l1, c2, qrot(q2, mk3(0, 0, 1)), r2, l2, margin_h);
@@ -751,7 +719,8 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
       int nslot = 0;
       int my_nent = 0; float cD = 0.f, caref[4] = {0.f, 0.f, 0.f, 0.f}; int my_slot = -1;
       unsigned cm[2] = {0u, 0u};
-      int ids = 0, kind = 0, key = -1;
+      int ids = 0, kind = 0, key = -1, nlr = 0;
+      bool my_lr = false, dense_mode = false;
       if (lane < ncon) { ids = W.c_ids[lane]; kind = (ids >> 6) & 1; key = kind == 0 ? (ids >> 8) : -1; }
       {
         const bool wants = lane < ncon && kind == 0 && key < PP_NKEY && key >= 0;
@@ -770,14 +739,24 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
           if (dropme) { my_slot = -2; }
           nslot = KS;
         }
+        // A contact is "in front" when its jacobian lives on one root path (one finger chain + the
+        // 4 root dofs) plus a key owned by that finger. Hand-hand contacts and contacts on a key
+        // already owned by another finger couple two fronts: they are solved as a low-rank
+        // correction (at most LRC of them, the rest are dropped and counted).
+        const int n1_ = (ids >> 1) & 31;
+        const int my_front = (ids & 1) * 8 + (n1_ >= 21 ? 4 : n1_ >= 16 ? 3 : n1_ >= 12 ? 2 : n1_ >= 8 ? 1 : 0);
+        const int owner = __shfl_sync(FULL, my_front, __ffs(same) - 1);
+        my_lr = lane < ncon && my_slot != -2 && (kind == 1 || dbg_all_lr || (wants && owner != my_front));
+        const unsigned lrb = __ballot_sync(FULL, my_lr);
+        nlr = __popc(lrb);
+        dense_mode = nlr > LRC;  // too many cross-finger contacts for the low-rank path
       }
       __syncwarp();
-      bool dense[2] = {false, false}; bool coupled = false;
       if (lane < ncon && my_slot != -2) {
         const int c = lane;
-        const f3 pos = mk3(W.c_geo[0][c], W.c_geo[1][c], W.c_geo[2][c]);
-        const f3 n = mk3(W.c_geo[3][c], W.c_geo[4][c], W.c_geo[5][c]);
-        const float dist = W.c_geo[6][c];
+        const f3 pos = mk3(W.a.k.c_geo[0][c], W.a.k.c_geo[1][c], W.a.k.c_geo[2][c]);
+        const f3 n = mk3(W.a.k.c_geo[3][c], W.a.k.c_geo[4][c], W.a.k.c_geo[5][c]);
+        const float dist = W.a.k.c_geo[6][c];
         // mju_makeFrame
         f3 t1 = (n.y < 0.5f && n.y > -0.5f) ? mk3(0, 1, 0) : mk3(0, 0, 1);
         t1 = t1 - dot(n, t1) * n; t1 = (1.f / norm(t1)) * t1;
@@ -805,8 +784,8 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
           while (m) {
             const int d = __ffs(m) - 1; m &= m - 1;
             const int g = h * 26 + d;
-            const f3 ax = ld3(W.xaxis[g]);
-            const f3 col = d < 2 ? ax : cross(ax, pos - ld3(W.xpos[g]));
+            const f3 ax = ld3(W.a.k.xaxis[g]);
+            const f3 col = d < 2 ? ax : cross(ax, pos - ld3(W.a.k.xpos[g]));
             // jac(body2) - jac(body1): chain of geom1 enters with -, chain of geom2 with +
             const bool second = kind == 1 && h == h2 && ((a2 >> d) & 1u) && !(h1 == h2 && ((a1 >> d) & 1u));
             const float sg = second ? 1.f : -1.f;
@@ -830,6 +809,7 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
         }
         my_nent = e;
         W.c_mask[0][c] = cm[0]; W.c_mask[1][c] = cm[1]; W.c_slot[c] = (int8_t)my_slot; W.c_nent[c] = (int8_t)e;
+        W.c_lr[c] = my_lr ? 1 : 0;
         // impedance, regularisation, reference acceleration (pyramidal, condim 3)
         const float mu = o.pair_friction[pc], margin = o.pair_margin[pc];
         float Kk, Bb;
@@ -842,24 +822,19 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
         const float vr[4] = {uv.x + mu * uv.y, uv.x - mu * uv.y, uv.x + mu * uv.z, uv.x - mu * uv.z};
 #pragma unroll
         for (int k = 0; k < 4; k++) caref[k] = -Bb * vr[k] - Kk * imp * (dist - margin);
-        if (kind == 1) { if (h1 == h2) dense[h1] = true; else coupled = true; }
       } else if (lane < ncon) {
-        W.c_mask[0][lane] = 0u; W.c_mask[1][lane] = 0u; W.c_slot[lane] = -1; W.c_nent[lane] = 0;
+        W.c_mask[0][lane] = 0u; W.c_mask[1][lane] = 0u; W.c_slot[lane] = -1; W.c_nent[lane] = 0; W.c_lr[lane] = 0;
       }
       const float cmu = (lane < ncon) ? o.pair_friction[kind == 0 ? PP_PAIRCLS_PIANO : PP_PAIRCLS_HAND] : 0.f;
       __syncwarp();
-      // a key touched from two different branches / hands breaks the tree sparsity
+      // slot bookkeeping: the root path (one finger of one hand) that owns each touched key
       if (lane < nslot) {
         unsigned u0 = 0u, u1 = 0u;
         for (int c = 0; c < ncon; c++)
-          if (W.c_slot[c] == lane) { u0 |= W.c_mask[0][c]; u1 |= W.c_mask[1][c]; }
-        if (u0 && u1) coupled = true;
-        if (u0 && u0 != anc_of(31 - __clz(u0))) dense[0] = true;
-        if (u1 && u1 != anc_of(31 - __clz(u1))) dense[1] = true;
+          if (W.c_slot[c] == lane && !W.c_lr[c]) { u0 |= W.c_mask[0][c]; u1 |= W.c_mask[1][c]; }
+        W.slot_mask[lane] = u0 | u1;  // an in-front contact touches one hand only
+        W.slot_hand[lane] = u1 ? 1 : 0;
       }
-      coupled = __any_sync(FULL, coupled);
-      dense[0] = __any_sync(FULL, dense[0]) || coupled;
-      dense[1] = __any_sync(FULL, dense[1]) || coupled;
 
       // per-dof rows: frictionloss (always) and joint limit (when violated)
       float fD[2], faref[2], floss[2], lsg[2], lD[2], laref[2];
@@ -891,27 +866,46 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
         const LimitRow r = pp_limit_row(o, kq_, kv_, 0.f, kt.hi[skey], kt.invw[skey]);
         ssg = r.sgn; sD = r.D; saref = r.aref;
       }
+      __syncwarp();  // a.kin is dead from here on (a.sol aliases it)
 
-      // ================================================================ mj_fwdConstraint (Newton)
-      int el[2];
-#pragma unroll
-      for (int h = 0; h < 2; h++) el[h] = dense[h] ? 25 : lane + L.ni.nsub - 1;
-      float* H = W.u.H;
+      // ================================================================ mj_fwdConstraint + mj_Euler
+      // Newton on the primal cost; every linear solve goes through the multifrontal factorisation of
+      // H_t = M + diagonal rows + in-front contact cliques (one lane per finger-chain front, the
+      // 4x4 root front replicated), cross-front contacts enter as a Woodbury correction. The last
+      // trip of the loop reuses the same code for mj_Euler's (M + h diag(b)) solve.
+      float (*Ht)[9] = W.a.s.Ht;
+      const int posl = lane < 4 ? lane : 4 + lane - L.ni.cs;  // own position in own ancestor list
       float a[2] = {acc[0], acc[1]};  // warm start
       float Ma[2] = {0.f, 0.f}, sMa = 0.f;
       float jar[4] = {0.f, 0.f, 0.f, 0.f};
-      auto build_M = [&](float hdamp) {
-        // H <- M (+ hdamp * damping on the diagonal); zero the widened envelopes first
-        if (L.dof) {
+      const bool con_on = lane < ncon && my_slot != -2;
+      // front lane identity: lane = replica*16 + hand*8 + chain
+      const int frep = lane >> 4, fh = (lane >> 3) & 1, fc = lane & 7;
+      const bool fvalid = fc < 5;
+      const int fce = fc == 0 ? 7 : fc == 1 ? 11 : fc == 2 ? 15 : fc == 3 ? 20 : 25;
+      const int fn = (fc == 3 || fc == 4) ? 5 : 4;
+      const int fcs = fce - fn + 1;
+      const int fg0 = fh * 26;
+
+      // out = M x for x in W.va: ancestors from registers, descendants from the pristine copy Mt
+      auto matvec_M = [&](float out[2]) {
 #pragma unroll
-          for (int h = 0; h < 2; h++) {
-            if (dense[h]) {
-              const int g = h * 26 + lane, gend = coupled ? 51 : h * 26 + 25;
-              for (int gk = g; gk <= gend; gk++) H[hidx(g, gk)] = 0.f;
+        for (int h = 0; h < 2; h++) {
+          float s = 0.f;
+          if (L.dof) {
+#pragma unroll
+            for (int j = 0; j < 9; j++) {
+              const int an = j < 4 ? j : L.ni.cs + j - 4;
+              const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
+              if (valid) s += Mr[h][j] * W.va[h * 26 + an];
             }
+            for (int d = lane + 1; d < lane + L.ni.nsub; d++) s += W.Mt[h * 26 + d][posl] * W.va[h * 26 + d];
           }
+          out[h] = s;
         }
-        __syncwarp();
+      };
+      // H_t <- M (+ hdamp * damping on the diagonal): tree entries only
+      auto build_M = [&](float hdamp) {
         if (L.dof) {
 #pragma unroll
           for (int h = 0; h < 2; h++) {
@@ -919,90 +913,92 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
             for (int j = 0; j < 9; j++) {
               const int an = j < 4 ? j : L.ni.cs + j - 4;
               const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
-              if (valid) H[hidx(h * 26 + an, h * 26 + lane)] = Mr[h][j] + (an == lane ? hdamp * damp[h] : 0.f);
+              if (valid) Ht[h * 26 + lane][j] = Mr[h][j] + (an == lane ? hdamp * damp[h] : 0.f);
             }
           }
         }
         __syncwarp();
       };
       build_M(0.f);
-      // Ma at the warm start: tree entries of M only
+      // Ma at the warm start
 #pragma unroll
       for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = a[h];
       __syncwarp();
-      if (L.dof) {
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-          float s = 0.f;
-          unsigned m = L.ni.anc;
-          while (m) { const int d = __ffs(m) - 1; m &= m - 1; s += H[hidx(h * 26 + d, h * 26 + lane)] * W.va[h * 26 + d]; }
-          for (int d = lane + 1; d < lane + L.ni.nsub; d++) s += H[hidx(h * 26 + lane, h * 26 + d)] * W.va[h * 26 + d];
-          Ma[h] = s;
-        }
-      }
+      matvec_M(Ma);
       if (lane < nslot) { W.va[52 + lane] = sa; sMa = sM * sa; }
       __syncwarp();
-      if (lane < ncon) {
+      if (con_on) {
         const f3 ua = contact_ux(W, lane, my_nent);
         jar[0] = ua.x + cmu * ua.y - caref[0]; jar[1] = ua.x - cmu * ua.y - caref[1];
         jar[2] = ua.x + cmu * ua.z - caref[2]; jar[3] = ua.x - cmu * ua.z - caref[3];
       }
       const float scale = 1.f / (o.meaninertia * (float)PP_NV);
       int iter = 0, ls_total = 0;
-      const int maxit = min(o.iterations, 30);
-      for (; iter < maxit; iter++) {
+      const int maxit = min(o.iterations, 50);
+      bool euler = false;
+      for (;;) {
         // ---- row forces and curvatures at the current point
-        float ff[2], fc[2], lf[2], lc[2]; int fz[2];
+        float ff[2] = {0.f, 0.f}, fc_[2] = {0.f, 0.f}, lf[2] = {0.f, 0.f}, lc[2] = {0.f, 0.f};
+        int fz[2] = {0, 0};
         float cf[4] = {0.f, 0.f, 0.f, 0.f}, cc[4] = {0.f, 0.f, 0.f, 0.f};
         float sf = 0.f, sc = 0.f;
+        float grad[2] = {0.f, 0.f}, sgrad = 0.f;
+        if (!euler) {
 #pragma unroll
-        for (int h = 0; h < 2; h++) {
-          ff[h] = 0.f; fc[h] = 0.f; fz[h] = 0; lf[h] = 0.f; lc[h] = 0.f;
-          if (floss[h] > 0.f) row_fric(fD[h], floss[h], a[h] - faref[h], ff[h], fc[h], fz[h]);
-          if (lsg[h] != 0.f) row_ineq(lD[h], lsg[h] * a[h] - laref[h], lf[h], lc[h]);
-        }
-        if (ssg != 0.f) row_ineq(sD, ssg * sa - saref, sf, sc);
-        if (lane < ncon && my_slot != -2) {
+          for (int h = 0; h < 2; h++) {
+            if (floss[h] > 0.f) row_fric(fD[h], floss[h], a[h] - faref[h], ff[h], fc_[h], fz[h]);
+            if (lsg[h] != 0.f) row_ineq(lD[h], lsg[h] * a[h] - laref[h], lf[h], lc[h]);
+          }
+          if (ssg != 0.f) row_ineq(sD, ssg * sa - saref, sf, sc);
+          if (con_on) {
 #pragma unroll
-          for (int k = 0; k < 4; k++) row_ineq(cD, jar[k], cf[k], cc[k]);
-          const int c = lane;
-          W.c_wf[0][c] = cf[0] + cf[1] + cf[2] + cf[3];
-          W.c_wf[1][c] = cmu * (cf[0] - cf[1]);
-          W.c_wf[2][c] = cmu * (cf[2] - cf[3]);
-          W.c_w[0][c] = cc[0] + cc[1] + cc[2] + cc[3];
-          W.c_w[1][c] = cmu * (cc[0] - cc[1]);
-          W.c_w[2][c] = cmu * cmu * (cc[0] + cc[1]);
-          W.c_w[3][c] = cmu * (cc[2] - cc[3]);
-          W.c_w[4][c] = cmu * cmu * (cc[2] + cc[3]);
-        } else if (lane < ncon) {
-          for (int k = 0; k < 3; k++) W.c_wf[k][lane] = 0.f;
-          for (int k = 0; k < 5; k++) W.c_w[k][lane] = 0.f;
-        }
-        __syncwarp();
-        // ---- gradient
-        float gj[2], gjs;
-        gather_jt(W, ncon, lane, gj, gjs);
-        float grad[2], sgrad = 0.f;
+            for (int k = 0; k < 4; k++) row_ineq(cD, jar[k], cf[k], cc[k]);
+            const int c = lane;
+            W.c_wf[0][c] = cf[0] + cf[1] + cf[2] + cf[3];
+            W.c_wf[1][c] = cmu * (cf[0] - cf[1]);
+            W.c_wf[2][c] = cmu * (cf[2] - cf[3]);
+            W.c_w[0][c] = cc[0] + cc[1] + cc[2] + cc[3];
+            W.c_w[1][c] = cmu * (cc[0] - cc[1]);
+            W.c_w[2][c] = cmu * cmu * (cc[0] + cc[1]);
+            W.c_w[3][c] = cmu * (cc[2] - cc[3]);
+            W.c_w[4][c] = cmu * cmu * (cc[2] + cc[3]);
+          } else if (lane < ncon) {
+            for (int k = 0; k < 3; k++) W.c_wf[k][lane] = 0.f;
+            for (int k = 0; k < 5; k++) W.c_w[k][lane] = 0.f;
+          }
+          __syncwarp();
+          // ---- gradient
+          float gj[2], gjs;
+          gather_jt(W, ncon, lane, gj, gjs);
 #pragma unroll
-        for (int h = 0; h < 2; h++) grad[h] = L.dof ? (Ma[h] - fs[h] - ff[h] - lsg[h] * lf[h] - gj[h]) : 0.f;
-        if (lane < nslot) sgrad = sMa - sfs - ssg * sf - gjs;
-        // ---- Hessian: M + diagonal rows + contact cliques
-        if (iter > 0) build_M(0.f);
-        if (L.dof) {
+          for (int h = 0; h < 2; h++) grad[h] = L.dof ? (Ma[h] - fs[h] - ff[h] - lsg[h] * lf[h] - gj[h]) : 0.f;
+          if (lane < nslot) sgrad = sMa - sfs - ssg * sf - gjs;
+        }
+        int m = 0;
+        float p[2] = {0.f, 0.f}, sp = 0.f;
+        if (dense_mode && !euler) {
+          // ---- dense fallback: full Hessian of the 52 hand dofs, every contact as a clique
+          float* Hd = W.a.s.Hd;
+          for (int i = lane; i < 52 * 53 / 2; i += 32) Hd[i] = 0.f;
+          for (int s = 0; s < nslot; s++) { W.a.s.Kcd[s][lane] = 0.f; if (lane + 32 < 52) W.a.s.Kcd[s][lane + 32] = 0.f; }
+          __syncwarp();
+          if (L.dof) {
 #pragma unroll
-          for (int h = 0; h < 2; h++) H[hidx(h * 26 + lane, h * 26 + lane)] += fc[h] + lc[h];
-        }
-        for (int s = 0; s < nslot; s++) {
-          W.Kc[s][lane] = 0.f;
-          if (lane + 32 < 52) W.Kc[s][lane + 32] = 0.f;
-        }
-        __syncwarp();
-        float shss = sM + sc;  // H(slot, slot), lane < nslot
-        {
+            for (int h = 0; h < 2; h++) {
+#pragma unroll
+              for (int j = 0; j < 9; j++) {
+                const int an = j < 4 ? j : L.ni.cs + j - 4;
+                const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
+                if (valid) Hd[hidx(h * 26 + an, h * 26 + lane)] = Mr[h][j] + (an == lane ? fc_[h] + lc[h] : 0.f);
+              }
+            }
+          }
+          __syncwarp();
+          float shss = sM + sc;
           const unsigned lt = (1u << lane) - 1u;
           for (int c = 0; c < ncon; c++) {
             const float w0 = W.c_w[0][c];
-            if (w0 == 0.f) continue;  // no active row
+            if (w0 == 0.f) continue;
             const float w1 = W.c_w[1][c], w2 = W.c_w[2][c], w3 = W.c_w[3][c], w4 = W.c_w[4][c];
             const unsigned m0 = W.c_mask[0][c], m1 = W.c_mask[1][c];
             const int n0 = __popc(m0), n1_ = __popc(m1), slot = W.c_slot[c];
@@ -1012,15 +1008,14 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
               if (!((mh >> lane) & 1u)) continue;
               const int e0 = (h ? n0 : 0) + __popc(mh & lt);
               const float ux = W.c_u[3 * e0][c], uy = W.c_u[3 * e0 + 1][c], uz = W.c_u[3 * e0 + 2][c];
-              // z = W u (W symmetric 3x3 with zero (t1,t2) entry)
               const float zx = w0 * ux + w1 * uy + w3 * uz, zy = w1 * ux + w2 * uy, zz = w3 * ux + w4 * uz;
               const int g = h * 26 + lane;
               const int etot = n0 + n1_ + (slot >= 0 ? 1 : 0);
               for (int e = e0; e < etot; e++) {
                 const float val = zx * W.c_u[3 * e][c] + zy * W.c_u[3 * e + 1][c] + zz * W.c_u[3 * e + 2][c];
                 const int col = W.c_col[e][c];
-                if (col >= 52) W.Kc[col - 52][g] += val;
-                else H[hidx(g, col)] += val;
+                if (col >= 52) W.a.s.Kcd[col - 52][g] += val;
+                else Hd[hidx(g, col)] += val;
               }
             }
             if (slot == lane) {
@@ -1029,70 +1024,358 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
               shss += ux * (w0 * ux + w1 * uy + w3 * uz) + uy * (w1 * ux + w2 * uy) + uz * (w3 * ux + w4 * uz);
             }
           }
-        }
-        if (lane < nslot) W.hss[lane] = 1.f / shss;
-        __syncwarp();
-        // ---- eliminate the key slots (Schur complement), right-hand side b = -grad
-        float b[2] = {-grad[0], -grad[1]};
-        const float sb = -sgrad;
-        for (int s = 0; s < nslot; s++) {
-          const float ih = W.hss[s];
-          const float bs = __shfl_sync(FULL, sb, s) * ih;
-          if (L.dof) {
+          if (lane < nslot) W.a.s.hss[lane] = 1.f / shss;
+          __syncwarp();
+          float b[2] = {-grad[0], -grad[1]};
+          const float sb = -sgrad;
+          for (int s = 0; s < nslot; s++) {
+            const float ih = W.a.s.hss[s];
+            const float bs = __shfl_sync(FULL, sb, s) * ih;
+            if (L.dof) {
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-              const int g = h * 26 + lane;
-              const float kg = W.Kc[s][g];
-              if (kg != 0.f) {
-                b[h] -= kg * bs;
-                const float cf_ = kg * ih;
-                const int gend = coupled ? 51 : h * 26 + el[h];
-                for (int gk = g; gk <= gend; gk++) H[hidx(g, gk)] -= cf_ * W.Kc[s][gk];
+              for (int h = 0; h < 2; h++) {
+                const int g = h * 26 + lane;
+                const float kg = W.a.s.Kcd[s][g];
+                if (kg != 0.f) {
+                  b[h] -= kg * bs;
+                  const float cf_ = kg * ih;
+                  for (int gk = g; gk < 52; gk++) Hd[hidx(g, gk)] -= cf_ * W.a.s.Kcd[s][gk];
+                }
               }
             }
           }
+          __syncwarp();
+          dense_factor_solve(Hd, lane, L.dof, b);
+          __syncwarp();
+#pragma unroll
+          for (int h = 0; h < 2; h++) { p[h] = L.dof ? b[h] : 0.f; if (L.dof) W.va[h * 26 + lane] = p[h]; }
+          __syncwarp();
+          if (lane < nslot) {
+            float d = 0.f;
+            for (int g = 0; g < 52; g++) d += W.a.s.Kcd[lane][g] * W.va[g];
+            sp = (sb - d) * W.a.s.hss[lane];
+            W.va[52 + lane] = sp;
+          }
+          __syncwarp();
+        } else {
+        // ---- H_t: M + diagonal rows + in-front contact cliques (Euler: M + h diag(b))
+        if (iter > 0 || euler) build_M(euler ? o.h : 0.f);
+        float shss = sM + sc;  // H(slot, slot), lane < nslot
+        if (!euler) {
+          if (L.dof) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) Ht[h * 26 + lane][posl] += fc_[h] + lc[h];
+          }
+          for (int s = 0; s < nslot; s++) {
+            if (lane < 9) W.a.s.Kc[s][lane] = 0.f;
+          }
+          __syncwarp();
+          const unsigned lt = (1u << lane) - 1u;
+          for (int c = 0; c < ncon; c++) {
+            const float w0 = W.c_w[0][c];
+            if (w0 == 0.f || W.c_lr[c]) continue;  // no active row / handled by the low-rank path
+            const float w1 = W.c_w[1][c], w2 = W.c_w[2][c], w3 = W.c_w[3][c], w4 = W.c_w[4][c];
+            const unsigned m0 = W.c_mask[0][c], m1 = W.c_mask[1][c];
+            const int n0 = __popc(m0), n1_ = __popc(m1), slot = W.c_slot[c];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+              const unsigned mh = h ? m1 : m0;
+              if (!((mh >> lane) & 1u)) continue;
+              const int e0 = (h ? n0 : 0) + __popc(mh & lt);
+              const float ux = W.c_u[3 * e0][c], uy = W.c_u[3 * e0 + 1][c], uz = W.c_u[3 * e0 + 2][c];
+              const float zx = w0 * ux + w1 * uy + w3 * uz, zy = w1 * ux + w2 * uy, zz = w3 * ux + w4 * uz;
+              const int g = h * 26 + lane;
+              const int etot = n0 + n1_ + (slot >= 0 ? 1 : 0);
+              for (int e = e0; e < etot; e++) {
+                const float val = zx * W.c_u[3 * e][c] + zy * W.c_u[3 * e + 1][c] + zz * W.c_u[3 * e + 2][c];
+                const int col = W.c_col[e][c];
+                if (col >= 52) W.a.s.Kc[col - 52][posl] += val;
+                else Ht[col][posl] += val;
+              }
+            }
+            if (slot == lane) {
+              const int e0 = n0 + n1_;
+              const float ux = W.c_u[3 * e0][c], uy = W.c_u[3 * e0 + 1][c], uz = W.c_u[3 * e0 + 2][c];
+              shss += ux * (w0 * ux + w1 * uy + w3 * uz) + uy * (w1 * ux + w2 * uy) + uz * (w3 * ux + w4 * uz);
+            }
+          }
+          if (lane < nslot) W.a.s.hss[lane] = 1.f / shss;
+          __syncwarp();
+          // ---- eliminate the key slots from H_t (Schur complement on the owner's root path)
+          if (L.dof) {
+            for (int s = 0; s < nslot; s++) {
+              const int h = W.slot_hand[s];
+              const unsigned sm = W.slot_mask[s];
+              if (!((sm >> lane) & 1u)) continue;
+              const int scs = cs_of(31 - __clz(sm));
+              const float cf_ = W.a.s.Kc[s][posl] * W.a.s.hss[s];
+              unsigned m = sm & ~lt;
+              while (m) { const int d = __ffs(m) - 1; m &= m - 1; Ht[h * 26 + d][posl] -= cf_ * W.a.s.Kc[s][apos(d, scs)]; }
+            }
+          }
+          __syncwarp();
+        }
+        // ---- multifrontal factorisation. Front (hand fh, chain fc): local variables 0..4 = chain dofs
+        // deepest first (a 4-dof chain is padded with an identity pivot), 5..8 = root dofs 3,2,1,0.
+        float F[45], Rt[10];
+        {
+#pragma unroll
+          for (int i = 0; i < 9; i++) {
+#pragma unroll
+            for (int j = 0; j <= i; j++) {
+              float val = 0.f;
+              if (i < 5) {
+                if (fvalid && i < fn) val = Ht[fg0 + fce - j][4 + (fce - i) - fcs];
+                else val = i == j ? 1.f : 0.f;
+              } else if (j < 5) {
+                if (fvalid && j < fn) val = Ht[fg0 + fce - j][8 - i];
+              }
+              F[i * (i + 1) / 2 + j] = val;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j <= i; j++) Rt[i * (i + 1) / 2 + j] = Ht[fg0 + 3 - j][3 - i];
+          // eliminate the 5 chain pivots
+#pragma unroll
+          for (int k = 0; k < 5; k++) {
+            const float inv = rsqrtf(fmaxf(F[k * (k + 1) / 2 + k], 1e-30f));
+            F[k * (k + 1) / 2 + k] = inv;
+#pragma unroll
+            for (int i = k + 1; i < 9; i++) F[i * (i + 1) / 2 + k] *= inv;
+#pragma unroll
+            for (int i = k + 1; i < 9; i++)
+#pragma unroll
+              for (int j = k + 1; j <= i; j++) F[i * (i + 1) / 2 + j] -= F[i * (i + 1) / 2 + k] * F[j * (j + 1) / 2 + k];
+          }
+          // root front = root block of H_t + the update matrices of the hand's 5 chain fronts
+#pragma unroll
+          for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j <= i; j++) {
+              float upd = F[(i + 5) * (i + 6) / 2 + j + 5];
+              upd += __shfl_xor_sync(FULL, upd, 1); upd += __shfl_xor_sync(FULL, upd, 2); upd += __shfl_xor_sync(FULL, upd, 4);
+              Rt[i * (i + 1) / 2 + j] += upd;
+            }
+#pragma unroll
+          for (int k = 0; k < 4; k++) {
+            const float inv = rsqrtf(fmaxf(Rt[k * (k + 1) / 2 + k], 1e-30f));
+            Rt[k * (k + 1) / 2 + k] = inv;
+#pragma unroll
+            for (int i = k + 1; i < 4; i++) Rt[i * (i + 1) / 2 + k] *= inv;
+#pragma unroll
+            for (int i = k + 1; i < 4; i++)
+#pragma unroll
+              for (int j = k + 1; j <= i; j++) Rt[i * (i + 1) / 2 + j] -= Rt[i * (i + 1) / 2 + k] * Rt[j * (j + 1) / 2 + k];
+          }
+        }
+        // ---- right-hand sides. Row 0: -grad (Euler: f_smooth + f_constraint = M qacc); rows 1..m:
+        // sqrt(D) J_r^T of the active rows of the low-rank contacts.
+        float V[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // lower 3x3: (00, 10, 20, 11, 21, 22)
+        int vrow[3] = {0, 0, 0};
+        float (*Z)[52 + KS] = W.a.s.Z;
+        const float sb = -sgrad;
+        {
+          // W = V V^T (3x3 Cholesky of the active pyramid rows' weight, rank <= 3): columns U v_j
+          unsigned bal[3] = {0u, 0u, 0u};
+          if (!euler && nlr > 0) {
+            if (my_lr) {
+              const float w0 = W.c_w[0][lane], w1 = W.c_w[1][lane], w2 = W.c_w[2][lane], w3 = W.c_w[3][lane], w4 = W.c_w[4][lane];
+              if (w0 > 0.f) {
+                const float l00 = sqrtf(w0), l10 = w1 / l00, l20 = w3 / l00;
+                const float d1 = w2 - l10 * l10;
+                const float l11 = d1 > 1e-6f * w2 ? sqrtf(d1) : 0.f;
+                const float l21 = l11 > 0.f ? -l20 * l10 / l11 : 0.f;
+                const float d2 = w4 - l20 * l20 - l21 * l21;
+                const float l22 = d2 > 1e-6f * w4 ? sqrtf(d2) : 0.f;
+                V[0] = l00; V[1] = l10; V[2] = l20; V[3] = l11; V[4] = l21; V[5] = l22;
+              }
+            }
+            bal[0] = __ballot_sync(FULL, V[0] != 0.f); bal[1] = __ballot_sync(FULL, V[3] != 0.f);
+            bal[2] = __ballot_sync(FULL, V[5] != 0.f);
+            m = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2]);
+            for (int i = lane; i < m * (52 + KS); i += 32) Z[1 + i / (52 + KS)][i % (52 + KS)] = 0.f;
+          }
+#pragma unroll
+          for (int h = 0; h < 2; h++) if (L.dof) Z[0][h * 26 + lane] = euler ? Ma[h] : -grad[h];
+          if (lane < nslot) Z[0][52 + lane] = euler ? 0.f : sb;
+          __syncwarp();
+          if (m > 0 && my_lr) {
+            const unsigned ltc = (1u << lane) - 1u;
+            vrow[0] = __popc(bal[0] & ltc);
+            vrow[1] = __popc(bal[0]) + __popc(bal[1] & ltc);
+            vrow[2] = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2] & ltc);
+            for (int e = 0; e < my_nent; e++) {
+              const float ux = W.c_u[3 * e][lane], uy = W.c_u[3 * e + 1][lane], uz = W.c_u[3 * e + 2][lane];
+              const int col = W.c_col[e][lane];
+              if (V[0] != 0.f) Z[1 + vrow[0]][col] = V[0] * ux + V[1] * uy + V[2] * uz;
+              if (V[3] != 0.f) Z[1 + vrow[1]][col] = V[3] * uy + V[4] * uz;
+              if (V[5] != 0.f) Z[1 + vrow[2]][col] = V[5] * uz;
+            }
+          }
+          __syncwarp();
+          // slot elimination applied to every right-hand side: b_g -= Kc[s][g] b_s / H_ss
+          if (!euler && L.dof) {
+            for (int s = 0; s < nslot; s++) {
+              const unsigned sm = W.slot_mask[s];
+              if (!((sm >> lane) & 1u)) continue;
+              const int g = W.slot_hand[s] * 26 + lane;
+              const float cf_ = W.a.s.Kc[s][posl] * W.a.s.hss[s];
+              for (int r = 0; r <= m; r++) Z[r][g] -= cf_ * Z[r][52 + s];
+            }
+          }
+          __syncwarp();
+        }
+        // ---- solves: two right-hand sides per pass (one per replica of the fronts)
+        for (int r0 = 0; r0 <= m; r0 += 2) {
+          const int r = min(r0 + frep, m);  // a replica without work repeats the last row (same values)
+          float y[9];
+#pragma unroll
+          for (int i = 0; i < 5; i++) y[i] = (fvalid && i < fn) ? Z[r][fg0 + fce - i] : 0.f;
+#pragma unroll
+          for (int i = 5; i < 9; i++) y[i] = 0.f;
+          float rr[4];
+#pragma unroll
+          for (int i = 0; i < 4; i++) rr[i] = Z[r][fg0 + 3 - i];
+          __syncwarp();
+#pragma unroll
+          for (int k = 0; k < 5; k++) {
+            y[k] *= F[k * (k + 1) / 2 + k];
+#pragma unroll
+            for (int i = k + 1; i < 9; i++) y[i] -= F[i * (i + 1) / 2 + k] * y[k];
+          }
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            float t = y[5 + i];
+            t += __shfl_xor_sync(FULL, t, 1); t += __shfl_xor_sync(FULL, t, 2); t += __shfl_xor_sync(FULL, t, 4);
+            rr[i] += t;
+          }
+#pragma unroll
+          for (int k = 0; k < 4; k++) {
+            rr[k] *= Rt[k * (k + 1) / 2 + k];
+#pragma unroll
+            for (int i = k + 1; i < 4; i++) rr[i] -= Rt[i * (i + 1) / 2 + k] * rr[k];
+          }
+#pragma unroll
+          for (int k = 3; k >= 0; k--) {
+            float t = rr[k];
+#pragma unroll
+            for (int i = k + 1; i < 4; i++) t -= Rt[i * (i + 1) / 2 + k] * rr[i];
+            rr[k] = t * Rt[k * (k + 1) / 2 + k];
+          }
+#pragma unroll
+          for (int i = 0; i < 4; i++) y[5 + i] = rr[i];
+#pragma unroll
+          for (int k = 4; k >= 0; k--) {
+            float t = y[k];
+#pragma unroll
+            for (int i = k + 1; i < 9; i++) t -= F[i * (i + 1) / 2 + k] * y[i];
+            y[k] = t * F[k * (k + 1) / 2 + k];
+          }
+          if (fvalid && (frep == 0 || r0 + 1 <= m)) {
+#pragma unroll
+            for (int i = 0; i < 5; i++) if (i < fn) Z[r][fg0 + fce - i] = y[i];
+            if (fc == 0) {
+#pragma unroll
+              for (int i = 0; i < 4; i++) Z[r][fg0 + 3 - i] = rr[i];
+            }
+          }
+          __syncwarp();
+        }
+        if (euler) {
+#pragma unroll
+          for (int h = 0; h < 2; h++)
+            if (L.dof) { const float x = Z[0][h * 26 + lane]; v[h] += o.h * x; q[h] += o.h * v[h]; }
+          __syncwarp();
+          break;
+        }
+        // ---- back-substitute the key slots of every solved vector
+        if (lane < nslot) {
+          const int h = W.slot_hand[lane];
+          const unsigned sm = W.slot_mask[lane];
+          const int scs = sm ? cs_of(31 - __clz(sm)) : 0;
+          for (int r = 0; r <= m; r++) {
+            float d = 0.f;
+            unsigned mm = sm;
+            while (mm) { const int dd = __ffs(mm) - 1; mm &= mm - 1; d += W.a.s.Kc[lane][apos(dd, scs)] * Z[r][h * 26 + dd]; }
+            Z[r][52 + lane] = (Z[r][52 + lane] - d) * W.a.s.hss[lane];
+          }
         }
         __syncwarp();
-        // ---- factorise and solve for the search direction
-        float dinv[2] = {1.f, 1.f};
-        if (coupled) { chol_coupled(H, lane, L.dof, dinv); solve_coupled(H, lane, L.dof, dinv, b); }
-        else { chol_uncoupled(H, lane, L.dof, el, dense, dinv); solve_uncoupled(H, lane, L.dof, el, dinv, b); }
-        float p[2] = {L.dof ? b[0] : 0.f, L.dof ? b[1] : 0.f};
+        // ---- Woodbury: p = y0 - Z (I + B^T Z)^-1 B^T y0
+        if (m > 0) {
+          float (*C)[LRR + 1] = W.a.s.C;
+          if (my_lr) {
+            for (int rc = 0; rc <= m; rc++) {  // column rc: Z row rc (0 = y0)
+              f3 uz = mk3(0, 0, 0);
+              for (int e = 0; e < my_nent; e++) {
+                const float x = Z[rc][W.c_col[e][lane]];
+                uz.x += W.c_u[3 * e][lane] * x; uz.y += W.c_u[3 * e + 1][lane] * x; uz.z += W.c_u[3 * e + 2][lane] * x;
+              }
+              // C[r][0..m-1] = I + B^T Z ; C[r][m] = B^T y0
+              const float val[3] = {V[0] * uz.x + V[1] * uz.y + V[2] * uz.z, V[3] * uz.y + V[4] * uz.z, V[5] * uz.z};
+#pragma unroll
+              for (int j = 0; j < 3; j++) {
+                if (V[j == 0 ? 0 : j == 1 ? 3 : 5] != 0.f) {
+                  const int r = vrow[j];
+                  if (rc == 0) C[r][m] = val[j]; else C[r][rc - 1] = val[j] + (rc - 1 == r ? 1.f : 0.f);
+                }
+              }
+            }
+          }
+          __syncwarp();
+          // Cholesky of the SPD capacitance (lane = row) and solve C t = B^T y0
+          for (int j = 0; j < m; j++) {
+            float s = 0.f;
+            if (lane >= j && lane < m) { s = C[lane][j]; for (int k = 0; k < j; k++) s -= C[lane][k] * C[j][k]; }
+            const float inv = rsqrtf(fmaxf(__shfl_sync(FULL, s, j), 1e-30f));
+            if (lane >= j && lane < m) C[lane][j] = lane == j ? inv : s * inv;
+            __syncwarp();
+          }
+          float t = lane < m ? C[lane][m] : 0.f;
+          for (int j = 0; j < m; j++) {  // forward
+            const float yj = __shfl_sync(FULL, t, j) * C[j][j];
+            if (lane == j) t = yj; else if (lane > j && lane < m) t -= C[lane][j] * yj;
+          }
+          for (int j = m - 1; j >= 0; j--) {  // backward
+            const float xj = __shfl_sync(FULL, t, j) * C[j][j];
+            if (lane == j) t = xj; else if (lane < j) t -= C[j][lane] * xj;
+          }
+          if (lane < m) C[lane][m] = t;
+          __syncwarp();
+#pragma unroll
+          for (int h = 0; h < 2; h++)
+            if (L.dof) { float s = Z[0][h * 26 + lane]; for (int r = 0; r < m; r++) s -= Z[1 + r][h * 26 + lane] * C[r][m]; p[h] = s; }
+          if (lane < nslot) { float s = Z[0][52 + lane]; for (int r = 0; r < m; r++) s -= Z[1 + r][52 + lane] * C[r][m]; sp = s; }
+        } else {
+#pragma unroll
+          for (int h = 0; h < 2; h++) if (L.dof) p[h] = Z[0][h * 26 + lane];
+          if (lane < nslot) sp = Z[0][52 + lane];
+        }
         __syncwarp();
 #pragma unroll
         for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = p[h];
+        if (lane < nslot) W.va[52 + lane] = sp;
         __syncwarp();
-        float sp = 0.f;
-        if (lane < nslot) {
-          float d = 0.f;
-          for (int g = 0; g < 52; g++) d += W.Kc[lane][g] * W.va[g];
-          sp = (sb - d) * W.hss[lane];
-          W.va[52 + lane] = sp;
         }
-        __syncwarp();
         // ---- J p for every row
         float jp[4] = {0.f, 0.f, 0.f, 0.f};
-        if (lane < ncon && my_slot != -2) {
+        if (con_on) {
           const f3 up = contact_ux(W, lane, my_nent);
           jp[0] = up.x + cmu * up.y; jp[1] = up.x - cmu * up.y; jp[2] = up.x + cmu * up.z; jp[3] = up.x - cmu * up.z;
-          // curvature-weighted J p, for M p = -grad - J^T C J p
-          W.c_wf[0][lane] = cc[0] * jp[0] + cc[1] * jp[1] + cc[2] * jp[2] + cc[3] * jp[3];
-          W.c_wf[1][lane] = cmu * (cc[0] * jp[0] - cc[1] * jp[1]);
-          W.c_wf[2][lane] = cmu * (cc[2] * jp[2] - cc[3] * jp[3]);
         }
         __syncwarp();
-        float cj[2], cjs;
-        gather_jt(W, ncon, lane, cj, cjs);
+        // ---- M p from the pristine tree entries
         float Mp[2], sMp = 0.f;
-#pragma unroll
-        for (int h = 0; h < 2; h++) Mp[h] = L.dof ? (-grad[h] - (fc[h] + lc[h]) * p[h] - cj[h]) : 0.f;
+        matvec_M(Mp);
         if (lane < nslot) sMp = sM * sp;
         // ---- exact line search on phi(alpha) = cost(a + alpha p)
         float g1 = grad[0] * p[0] + grad[1] * p[1] + sgrad * sp;
         float g2 = p[0] * Mp[0] + p[1] * Mp[1] + sp * sMp;
         float gauss1 = (Ma[0] - fs[0]) * p[0] + (Ma[1] - fs[1]) * p[1] + (sMa - sfs) * sp;
         g1 = wsum(g1); g2 = wsum(g2); gauss1 = wsum(gauss1);
-        if (!(g1 < 0.f) || 0.5f * scale * (-g1) < 1e-10f) break;  // no descent left: converged
+        if (!(g1 < 0.f) || 0.5f * scale * (-g1) < 1e-10f) { euler = true; continue; }  // converged
         float alpha = 0.f, lo = 0.f, hi = -1.f;
         bool changed = false;
         for (int ls = 0; ls < 20; ls++) {
@@ -1117,7 +1400,7 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
             row_ineq(sD, ssg * sa - saref + alpha * jp_, f_, c_);
             dphi -= f_ * jp_; ddphi += c_ * jp_ * jp_; ch |= (c_ != sc);
           }
-          if (lane < ncon && my_slot != -2) {
+          if (con_on) {
 #pragma unroll
             for (int k = 0; k < 4; k++) {
               float f_, c_;
@@ -1142,32 +1425,17 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
         sa += alpha * sp; sMa += alpha * sMp;
 #pragma unroll
         for (int k = 0; k < 4; k++) jar[k] += alpha * jp[k];
+        iter++;
         // piecewise-quadratic cost: a full Newton step that crosses no breakpoint is exact
-        if (!changed && fabsf(alpha - 1.f) < 1e-3f) { iter++; break; }
+        // (the Woodbury direction is only accurate to ~1e-3 in fp32: with low-rank rows the next trip's
+        // decrement test decides instead)
+        if ((m == 0 && !changed && fabsf(alpha - 1.f) < 1e-3f) || iter >= maxit) euler = true;
       }
       // ---- solution: hand dofs, touched keys (slots), untouched keys in closed form
 #pragma unroll
       for (int h = 0; h < 2; h++) acc[h] = a[h];
       if (lane < nslot) W.va[52 + lane] = sa;
       __syncwarp();
-
-      // ================================================================ mj_Euler (implicit damping)
-      {
-        bool nodense[2] = {false, false};
-        int elt[2] = {lane + L.ni.nsub - 1, lane + L.ni.nsub - 1};
-        const bool sv0 = dense[0], sv1 = dense[1], svc = coupled;
-        dense[0] = dense[1] = false; coupled = false;
-        build_M(o.h);
-        dense[0] = sv0; dense[1] = sv1; coupled = svc;
-        float dinv[2] = {1.f, 1.f};
-        chol_uncoupled(H, lane, L.dof, elt, nodense, dinv);
-        float x[2] = {Ma[0], Ma[1]};
-        solve_uncoupled(H, lane, L.dof, elt, dinv, x);
-        __syncwarp();
-#pragma unroll
-        for (int h = 0; h < 2; h++)
-          if (L.dof) { v[h] += o.h * x[h]; q[h] += o.h * v[h]; }
-      }
 #pragma unroll
       for (int i = 0; i < 3; i++) {
         const int k = lane + 32 * i;
@@ -1190,7 +1458,7 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
       }
       __syncwarp();
       cnt_ncon = ncon; cnt_iter = iter; cnt_drop = ndrop;
-      sum_iter += iter; sum_ls += ls_total; sum_dense += (dense[0] || dense[1]) ? 1 : 0; sum_coupled += coupled ? 1 : 0;
+      sum_iter += iter; sum_ls += ls_total; sum_dense += dense_mode ? 1 : 0; sum_coupled += nlr;
       {  // key limit rows count towards nefc (diagnostic)
         int nk = 0;
 #pragma unroll
@@ -1211,16 +1479,16 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
   for (int h = 0; h < 2; h++)
     if (L.dof) {
       const int g = h * 26 + lane;
-      st3(W.xpos[g], K.pos[h]);
-      W.xquat[g][0] = K.quat[h].w; W.xquat[g][1] = K.quat[h].x; W.xquat[g][2] = K.quat[h].y; W.xquat[g][3] = K.quat[h].z;
+      st3(W.a.k.xpos[g], K.pos[h]);
+      W.a.k.xquat[g][0] = K.quat[h].w; W.a.k.xquat[g][1] = K.quat[h].x; W.a.k.xquat[g][2] = K.quat[h].y; W.a.k.xquat[g][3] = K.quat[h].z;
     }
   __syncwarp();
   // fingertip sites: lanes 0..9
   f3 site = mk3(0, 0, 0);
   if (lane < PP_NSITE) {
     const int hb = ht.site_body[lane], h = hb >= PP_HB ? 1 : 0, g = h * 26 + (hb - h * PP_HB) + 1;
-    f4 qq; qq.w = W.xquat[g][0]; qq.x = W.xquat[g][1]; qq.y = W.xquat[g][2]; qq.z = W.xquat[g][3];
-    site = ld3(W.xpos[g]) + qrot(qq, ld3(ht.site_pos[lane]));
+    f4 qq; qq.w = W.a.k.xquat[g][0]; qq.x = W.a.k.xquat[g][1]; qq.y = W.a.k.xquat[g][2]; qq.z = W.a.k.xquat[g][3];
+    site = ld3(W.a.k.xpos[g]) + qrot(qq, ld3(ht.site_pos[lane]));
     st3(A.site_xpos + ((size_t)env * PP_NSITE + lane) * 3, site);
   }
   // forearm-forearm contact (forearm reward): the fixed pair of the two forearm capsules
@@ -1228,10 +1496,10 @@ __global__ void __launch_bounds__(32) pp_hands_step_kernel(HandsArgs A) {
   if (ht.forearm_geom[0] >= 0 && ht.forearm_geom[1] >= 0) {
     const int g1 = ht.forearm_geom[0], g2 = ht.forearm_geom[1];
     const int a1 = ht.geom_body[g1] + 1, a2 = 26 + ht.geom_body[g2] - PP_HB + 1;
-    f4 q1; q1.w = W.xquat[a1][0]; q1.x = W.xquat[a1][1]; q1.y = W.xquat[a1][2]; q1.z = W.xquat[a1][3];
-    f4 q2; q2.w = W.xquat[a2][0]; q2.x = W.xquat[a2][1]; q2.y = W.xquat[a2][2]; q2.z = W.xquat[a2][3];
-    const f3 c1 = ld3(W.xpos[a1]) + qrot(q1, ld3(ht.geom_pos[g1]));
-    const f3 c2 = ld3(W.xpos[a2]) + qrot(q2, ld3(ht.geom_pos[g2]));
+    f4 q1; q1.w = W.a.k.xquat[a1][0]; q1.x = W.a.k.xquat[a1][1]; q1.y = W.a.k.xquat[a1][2]; q1.z = W.a.k.xquat[a1][3];
+    f4 q2; q2.w = W.a.k.xquat[a2][0]; q2.x = W.a.k.xquat[a2][1]; q2.y = W.a.k.xquat[a2][2]; q2.z = W.a.k.xquat[a2][3];
+    const f3 c1 = ld3(W.a.k.xpos[a1]) + qrot(q1, ld3(ht.geom_pos[g1]));
+    const f3 c2 = ld3(W.a.k.xpos[a2]) + qrot(q2, ld3(ht.geom_pos[g2]));
     const Hit hh = capsule_capsule(c1, qrot(q1, mk3(0, 0, 1)), ht.geom_r[g1], ht.geom_hl[g1], c2,
                                    qrot(q2, mk3(0, 0, 1)), ht.geom_r[g2], ht.geom_hl[g2],
                                    o.pair_margin[PP_PAIRCLS_HAND]);

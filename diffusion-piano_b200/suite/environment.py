@@ -20,7 +20,7 @@ from . import specs
 
 class BatchedEnvironment:
     def __init__(self, task, num_envs: int, device: int = 0, canonical_actions: bool = False,
-                 auto_reset: bool = True):
+                 auto_reset: bool = True, max_contacts: int = 0):
         import torch  # device memory + streams only
 
         self._torch = torch
@@ -28,6 +28,7 @@ class BatchedEnvironment:
         self.num_envs = int(num_envs)
         cfg = task.engine_config(num_envs, device, canonical_actions)
         cfg.auto_reset = auto_reset
+        cfg.max_contacts = max_contacts
         self.engine = BatchedPianoEngine(task.model, task.song, cfg)
         self.device = torch.device("cuda", device)
         self.layout = task.observation_layout()

@@ -23,10 +23,10 @@ def relerr(a, b):
     return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-12))
 
 
-def run(name, ctrl_fn, steps, gravcomp=False, dt=0.005, verbose_every=1):
+def run(name, ctrl_fn, steps, gravcomp=False, dt=0.005, verbose_every=1, max_contacts=0):
     task = suite.PianoWithShadowHands(music.load("TwinkleTwinkleRousseau"), trim_silence=True,
                                       n_steps_lookahead=1, control_timestep=dt, gravity_compensation=gravcomp)
-    env = suite.BatchedEnvironment(task, 2, canonical_actions=False, auto_reset=False)
+    env = suite.BatchedEnvironment(task, 2, canonical_actions=False, auto_reset=False, max_contacts=max_contacts)
     ora = PianoWithShadowHandsOracle(task)
     env.reset()
     ora.reset()
@@ -62,9 +62,9 @@ def run(name, ctrl_fn, steps, gravcomp=False, dt=0.005, verbose_every=1):
         e_site = float(np.abs(sx.cpu().numpy()[0] - p.site_xpos).max())
         drift = float(np.abs(qp[1] - p.qpos).max())
         worst["qacc"] = max(worst["qacc"], relerr(qa[0], p.qacc)); worst["qpos"] = max(worst["qpos"], e_qpos)
-        if t % verbose_every == 0 or not np.isfinite(e_qpos):
+        if t % verbose_every == 0 or not np.isfinite(e_qpos) or relerr(qa[0], p.qacc) > 1e-3:
             print(f"{t:5d} | {c[0,0]:3d}/{p.ncon:3d} | {c[0,1]:3d}/{p.nefc:3d} | {c[0,2]:2d}/{p.solver_iter:2d} | {e_hand:9.2e} | {e_key:9.2e} | "
-                  f"{e_qpos:8.1e} | {e_qvel:8.1e} | {e_frc:7.1e} | {e_site:7.1e} | {rew[0]:.5f}/{r_o:.5f} | {drift:8.1e}")
+                  f"{e_qpos:8.1e} | {e_qvel:8.1e} | {e_frc:7.1e} | {e_site:7.1e} | {rew[0]:.5f}/{r_o:.5f} | {drift:8.1e} | drop {c[0,3]} lr {c[0,7]} ls {c[0,5]}")
         if not np.isfinite(qp).all():
             print("non-finite state; worst hand dof:", np.argmax(np.abs(qa[0] - p.qacc)))
             break
@@ -79,7 +79,7 @@ def main():
     if "free" in which:
         run("free fall to zero ctrl", lambda t, o: np.zeros(45), 12)
         run("free, gravcomp", lambda t, o: np.zeros(45), 6, gravcomp=True)
-    if "curl" in which:
+    if "curl" in which or "curl_lr" in which:
         def curl(t, o):
             a = np.zeros(45)
             names = o.model.names["actuator"]
@@ -88,8 +88,13 @@ def main():
             a[22 + names.index("rh_shadow_hand/rh_A_WRJ1")] = 0.45
             a[22 + names.index("rh_shadow_hand/rh_A_MFJ3")] = 1.2
             return a
-        run("curl fingers onto keys", curl, 160, verbose_every=8)
-    if "random" in which:
+        if "curl" in which:
+            run("curl fingers onto keys", curl, 160, verbose_every=8)
+    if "curl_lr" in which:
+        run("curl, all contacts low-rank (test hook)", curl, 160, verbose_every=4, max_contacts=256)
+    for w in which:
+      if w.startswith("random"):
+        rng = np.random.RandomState(int(w[6:].rstrip("g") or 0))
         lo = hi = None
 
         def rnd(t, o):
@@ -99,7 +104,7 @@ def main():
             if t % 10 == 0:
                 rnd.a = lo + rng.uniform(0, 1, 45) * (hi - lo)
             return rnd.a
-        run("random ctrl (held 10 substeps)", rnd, 200, verbose_every=10)
+        run("random ctrl (held 10 substeps) " + w, rnd, 150, verbose_every=10, gravcomp=w.endswith("g"))
 
 
 if __name__ == "__main__":
