@@ -113,6 +113,16 @@ __device__ __forceinline__ f4 qnormalize(f4 q) {
 }
 __device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
 
+// general power-law branch of getimpedance(), kept out of line (powf is ~200 instructions)
+static __device__ __noinline__ float pp_impedance_pow(float x, float mid, float power) {
+  return x <= mid ? powf(x, power) / powf(mid, power - 1.f) : 1.f - powf(1.f - x, power) / powf(1.f - mid, power - 1.f);
+}
+// sin and cos for |x| <= ~2 (joint half angles, key angles): Taylor/Horner, error < 2e-8 for |x| <= 1
+__device__ __forceinline__ void pp_sincos_small(float x, float* s, float* c) {
+  const float x2 = x * x;
+  *s = x * (1.f - x2 * (1.f / 6.f) * (1.f - x2 * (1.f / 20.f) * (1.f - x2 * (1.f / 42.f) * (1.f - x2 * (1.f / 72.f) * (1.f - x2 * (1.f / 110.f) * (1.f - x2 * (1.f / 156.f)))))));
+  *c = 1.f - x2 * 0.5f * (1.f - x2 * (1.f / 12.f) * (1.f - x2 * (1.f / 30.f) * (1.f - x2 * (1.f / 56.f) * (1.f - x2 * (1.f / 90.f) * (1.f - x2 * (1.f / 132.f) * (1.f - x2 * (1.f / 182.f)))))));
+}
 // getimpedance(): MuJoCo's position-dependent impedance d(r) (power-law sigmoid)
 __device__ __forceinline__ float pp_impedance(const float* solimp, float pos, float margin) {
   float dmin = clampf(solimp[0], 1e-4f, 0.9999f), dmax = clampf(solimp[1], 1e-4f, 0.9999f);
@@ -123,8 +133,8 @@ __device__ __forceinline__ float pp_impedance(const float* solimp, float pos, fl
   if (x >= 1.f) return dmax;
   if (x <= 0.f) return dmin;
   if (power == 1.f) y = x;
-  else if (x <= mid) y = powf(x, power) / powf(mid, power - 1.f);
-  else y = 1.f - powf(1.f - x, power) / powf(1.f - mid, power - 1.f);
+  else if (power == 2.f) y = x <= mid ? x * x / mid : 1.f - (1.f - x) * (1.f - x) / (1.f - mid);  // MuJoCo default
+  else y = pp_impedance_pow(x, mid, power);
   return dmin + y * (dmax - dmin);
 }
 // solref -> (K, B), with the refsafe clamp timeconst >= 2*timestep

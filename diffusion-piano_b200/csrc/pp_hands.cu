@@ -167,7 +167,7 @@ __device__ __forceinline__ float seg_box_dgrad(f3 al, f3 dv, f3 h, float t) {
 
 // capsule / sphere (geom1) against a box: contact at the closest segment point, plus one at the
 // far segment end when it also penetrates
-__device__ __forceinline__ void capsule_box(f3 cp, f3 axis, float r, float hl, const Box& b, float margin,
+__device__ __noinline__ void capsule_box(f3 cp, f3 axis, float r, float hl, const Box& b, float margin,
                                             Hit& h0, Hit& h1) {
   h1.ok = false;
   if (hl == 0.f) { h0 = sphere_box(cp, r, b, margin); return; }
@@ -196,7 +196,7 @@ __device__ __forceinline__ void capsule_box(f3 cp, f3 axis, float r, float hl, c
   h1 = sphere_box(t > 0.5f ? a : e, r, b, margin);
 }
 
-__device__ __forceinline__ Hit capsule_capsule(f3 p1, f3 u, float r1, float h1, f3 p2, f3 v, float r2, float h2,
+__device__ __noinline__ Hit capsule_capsule(f3 p1, f3 u, float r1, float h1, f3 p2, f3 v, float r2, float h2,
                                                float margin) {
   Hit o; o.ok = false; o.dist = 0.f; o.n = mk3(0, 0, 1); o.pos = p1;
   const f3 w = p1 - p2;
@@ -375,7 +375,7 @@ __device__ __forceinline__ void forward_kinematics(const HandTables& ht, const O
   }
   float sh[2], ch[2];
 #pragma unroll
-  for (int h = 0; h < 2; h++) sincosf(0.5f * q[h], &sh[h], &ch[h]);
+  for (int h = 0; h < 2; h++) pp_sincos_small(0.5f * q[h], &sh[h], &ch[h]);
   const int par = L.ni.parent;
   for (int d = 2; d <= 8; d++) {
     const bool mine = L.dof && L.ni.depth == d;
@@ -462,8 +462,11 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
     sustain = act[44];
     if (A.canonical) sustain = 0.5f * (sustain + 1.f);
 
-    // ================================================================ substeps
-    for (int sub = 0; sub < A.n_substeps; sub++) {
+  }
+  // ================================================================ substeps (+ the trailing mj_step1)
+  const int nsub = do_reset ? 0 : A.n_substeps;
+  {
+    for (int sub = 0;; sub++) {
       // ---- key state to shared memory
 #pragma unroll
       for (int i = 0; i < 3; i++) {
@@ -486,6 +489,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
           W.a.k.S[g][0] = sa.x; W.a.k.S[g][1] = sa.y; W.a.k.S[g][2] = sa.z; W.a.k.S[g][3] = Sl[h].x; W.a.k.S[g][4] = Sl[h].y; W.a.k.S[g][5] = Sl[h].z;
         }
       }
+      if (sub == nsub) break;  // trailing mj_step1: positions at the integrated state only
       // ---- body spatial inertia about ref + RNE body force (node 0 is massless)
 #pragma unroll
       for (int h = 0; h < 2; h++) {
@@ -664,7 +668,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
               Box b;
               if (key < PP_NKEY) {
                 float sq_, cq_;
-                sincosf(W.kq[key], &sq_, &cq_);
+                pp_sincos_small(W.kq[key], &sq_, &cq_);
                 const float hx = kt.half[key][0];
                 b.p = mk3(kt.pos[key][0] - hx + hx * cq_, kt.pos[key][1], kt.pos[key][2] - hx * sq_);
                 b.cq = cq_; b.sq = sq_; b.h = ld3(kt.half[key]);
@@ -1466,22 +1470,10 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
         cnt_nefc = nefc + (int)wsum((float)nk);
       }
     }  // substeps
-    t_idx += 1;
-  } else {
-    t_idx = 0;
   }
+  t_idx = do_reset ? 0 : t_idx + 1;
 
-  // ================================================================== trailing mj_step1: positions
-  Kin K;
-  forward_kinematics<false>(ht, o, L, q, v, K);
-  __syncwarp();
-#pragma unroll
-  for (int h = 0; h < 2; h++)
-    if (L.dof) {
-      const int g = h * 26 + lane;
-      st3(W.a.k.xpos[g], K.pos[h]);
-      W.a.k.xquat[g][0] = K.quat[h].w; W.a.k.xquat[g][1] = K.quat[h].x; W.a.k.xquat[g][2] = K.quat[h].y; W.a.k.xquat[g][3] = K.quat[h].z;
-    }
+  // ================================================================== sensors at the integrated state
   __syncwarp();
   // fingertip sites: lanes 0..9
   f3 site = mk3(0, 0, 0);
@@ -1565,7 +1557,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
       if (has) {
         const float kqv = (kk >> 5) == 0 ? q0 : (kk >> 5) == 1 ? q1 : q2;
         float sq_, cq_;
-        sincosf(kqv, &sq_, &cq_);
+        pp_sincos_small(kqv, &sq_, &cq_);
         const float hx = kt.half[kk][0];
         // key geom centre (rotated about the hinge) + world-axis offsets (0.35 size_x, 0, 0.5 size_z)
         const f3 kp = mk3(kt.pos[kk][0] - hx + hx * cq_ + 0.35f * hx, kt.pos[kk][1],
