@@ -384,7 +384,7 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     A.discount = discount; A.done = done; A.qacc = e->qacc; A.act_force = e->act_force;
     A.act_vel = e->act_vel; A.site_xpos = e->site_xpos; A.activation = e->activation;
     A.counters = e->counters;
-    pp_launch_hands(A, s);
+    e->launches += pp_launch_hands(A, s) - 1;
   }
   e->launches++;
   cudaError_t err = cudaGetLastError();

@@ -28,6 +28,7 @@ struct HandsArgs {
   int num_envs, mode, n_substeps, n_frames, lookahead, obs_dim, pmax;
   int canonical, has_fingering, disable_forearm_reward, wrong_press_termination, auto_reset;
   int max_contacts;
+  int meet_level;  // 0: warps of a block run free, 1: meet at substep phases, 2: and at every Newton iteration
   float energy_coef;
   const uint8_t* goal;    // [T,89]
   const int16_t* pairs;   // [T,pmax,2]
@@ -50,5 +51,5 @@ struct HandsArgs {
 };
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);
-void pp_launch_hands(const HandsArgs& A, cudaStream_t stream);
+int pp_launch_hands(const HandsArgs& A, cudaStream_t stream);  // returns the number of kernels launched
 size_t pp_hands_smem_bytes();

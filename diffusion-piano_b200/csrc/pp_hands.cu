@@ -24,6 +24,7 @@
 //   contact needs them.
 //   mj_Euler with implicit joint damping.
 #include "../../include/pp_model.h"
+#include <cstdlib>
 #include "pp_env.cuh"
 #include "pp_keys.cuh"
 
@@ -36,11 +37,12 @@ constexpr unsigned FULL = 0xffffffffu;
 constexpr float ZCULL = 0.045f;  // nothing of the piano is above this height
 
 constexpr int LRC = 8;       // contacts that couple two fronts (hand-hand, doubly touched key)
-constexpr int LRR = 3 * LRC; // rank of their Woodbury correction (3 per contact: U V, W = V V^T)
+constexpr int LRR = 3 * LRC;   // rank of their Woodbury correction (3 per contact: U V, W = V V^T)
+constexpr int ZS = 52 + KS + 1;  // row stride of the solved vectors (odd: conflict-free down a column)
 
 // Shared memory of one warp. Two phases of a substep alias each other: `k` (kinematics ..
 // mj_makeConstraint) and `s` (the solver).
-struct WarpShared {
+struct __align__(16) WarpShared {
   union {
     struct {
       float xpos[52][3];   // joint anchor (= body origin) of every hand dof node, world
@@ -54,7 +56,7 @@ struct WarpShared {
     struct {
       union {
         struct {
-          float Z[LRR + 1][52 + KS];  // row 0: -grad -> y0; rows 1..m: low-rank columns B -> H_t^-1 B
+          float Z[LRR + 1][ZS];  // row 0: -grad -> y0; rows 1..m: low-rank columns B -> H_t^-1 B
           float C[LRR][LRR + 1];      // capacitance I + B^T H_t^-1 B | B^T y0
         };
         struct {                      // dense fallback (more than LRC cross-finger contacts)
@@ -83,6 +85,8 @@ struct WarpShared {
   float c_wf[3][NC];      // 3-vector weight of the rows (forces, or curvature * jp)
   int c_ids[NC];          // h1 | node1<<1 | kind<<6 | (key or h2|node2<<1)<<8
 };
+static_assert(sizeof(WarpShared) % 16 == 0, "WarpShared is laid out back to back, one per warp");
+static_assert(10 * sizeof(WarpShared) + 5 * 1024 <= 228 * 1024, "10 warps (5 blocks of 2) per SM must fit the 228 KB of shared memory");
 
 struct NodeInfo { int parent, depth, nsub, cs; unsigned anc; };
 __device__ __forceinline__ NodeInfo node_info(int l) {
@@ -407,12 +411,15 @@ __device__ __forceinline__ void forward_kinematics(const HandTables& ht, const O
 }  // namespace
 
 // ====================================================================== the step kernel
-__global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
+// WPB warps (= envs) per block. With WPB > 1 the warps of a block meet at the phase boundaries
+// of every substep, so that they fetch the same stretch of the (instruction-cache bound) code
+// together; the meeting is skipped for a block in which any env resets (it runs no substeps).
+template <int WPB>
+__global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(HandsArgs A, int env_base) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  WarpShared& W = *reinterpret_cast<WarpShared*>(smem_raw);
+  WarpShared& W = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
-  const int env = blockIdx.x;
-  if (env >= A.num_envs) return;
+  const int env = env_base + blockIdx.x * WPB + (threadIdx.x >> 5);
   const DevModel& dm = *A.dm;
   const Options& o = dm.opt;
   const HandTables& ht = dm.hand;
@@ -424,7 +431,11 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
   int t_idx = A.t_idx[env];
   const bool do_reset = A.mode == PP_MODE_RESET ? (A.reset_mask ? A.reset_mask[env] != 0 : true)
                                                 : (A.auto_reset && A.needs_reset[env]);
+  bool meet = false;
+  if (WPB > 1) meet = __syncthreads_and(A.mode != PP_MODE_RESET && !do_reset) != 0 && A.meet_level > 0;
+  const bool meet_it = meet && A.meet_level > 1;
   if (A.mode == PP_MODE_RESET && !do_reset) return;
+#define PP_MEET() do { if (WPB > 1 && meet) __syncthreads(); } while (0)
 
   // ---- state: lane l holds hand dof l of both hands and keys l, l+32, l+64
   float q[2] = {0.f, 0.f}, v[2] = {0.f, 0.f}, acc[2] = {0.f, 0.f};
@@ -467,6 +478,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
   const int nsub = do_reset ? 0 : A.n_substeps;
   {
     for (int sub = 0;; sub++) {
+      PP_MEET();
       // ---- key state to shared memory
 #pragma unroll
       for (int i = 0; i < 3; i++) {
@@ -620,6 +632,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
         }
       }
 
+      PP_MEET();
       // ================================================================ mj_collision
       int ncon = 0, ndrop = 0;
       {
@@ -724,6 +737,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
       int my_nent = 0; float cD = 0.f, caref[4] = {0.f, 0.f, 0.f, 0.f}; int my_slot = -1;
       unsigned cm[2] = {0u, 0u};
       int ids = 0, kind = 0, key = -1, nlr = 0;
+      unsigned lrb = 0u;
       bool my_lr = false, dense_mode = false;
       if (lane < ncon) { ids = W.c_ids[lane]; kind = (ids >> 6) & 1; key = kind == 0 ? (ids >> 8) : -1; }
       {
@@ -751,7 +765,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
         const int my_front = (ids & 1) * 8 + (n1_ >= 21 ? 4 : n1_ >= 16 ? 3 : n1_ >= 12 ? 2 : n1_ >= 8 ? 1 : 0);
         const int owner = __shfl_sync(FULL, my_front, __ffs(same) - 1);
         my_lr = lane < ncon && my_slot != -2 && (kind == 1 || dbg_all_lr || (wants && owner != my_front));
-        const unsigned lrb = __ballot_sync(FULL, my_lr);
+        lrb = __ballot_sync(FULL, my_lr);
         nlr = __popc(lrb);
         dense_mode = nlr > LRC;  // too many cross-finger contacts for the low-rank path
       }
@@ -832,13 +846,18 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
       const float cmu = (lane < ncon) ? o.pair_friction[kind == 0 ? PP_PAIRCLS_PIANO : PP_PAIRCLS_HAND] : 0.f;
       __syncwarp();
       // slot bookkeeping: the root path (one finger of one hand) that owns each touched key
+      bool slot_lr = false;  // a low-rank contact touches this key: its slot entry is needed in every solved vector
       if (lane < nslot) {
         unsigned u0 = 0u, u1 = 0u;
         for (int c = 0; c < ncon; c++)
-          if (W.c_slot[c] == lane && !W.c_lr[c]) { u0 |= W.c_mask[0][c]; u1 |= W.c_mask[1][c]; }
+          if (W.c_slot[c] == lane) {
+            if (W.c_lr[c]) slot_lr = true;
+            else { u0 |= W.c_mask[0][c]; u1 |= W.c_mask[1][c]; }
+          }
         W.slot_mask[lane] = u0 | u1;  // an in-front contact touches one hand only
         W.slot_hand[lane] = u1 ? 1 : 0;
       }
+      const unsigned slot_lr_mask = __ballot_sync(FULL, slot_lr);
 
       // per-dof rows: frictionloss (always) and joint limit (when violated)
       float fD[2], faref[2], floss[2], lsg[2], lD[2], laref[2];
@@ -872,6 +891,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
       }
       __syncwarp();  // a.kin is dead from here on (a.sol aliases it)
 
+      PP_MEET();
       // ================================================================ mj_fwdConstraint + mj_Euler
       // Newton on the primal cost; every linear solve goes through the multifrontal factorisation of
       // H_t = M + diagonal rows + in-front contact cliques (one lane per finger-chain front, the
@@ -941,6 +961,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
       const int maxit = min(o.iterations, 50);
       bool euler = false;
       for (;;) {
+        if (WPB > 1 && meet_it) __syncthreads_or(1);
         // ---- row forces and curvatures at the current point
         float ff[2] = {0.f, 0.f}, fc_[2] = {0.f, 0.f}, lf[2] = {0.f, 0.f}, lc[2] = {0.f, 0.f};
         int fz[2] = {0, 0};
@@ -1177,12 +1198,12 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
         // ---- right-hand sides. Row 0: -grad (Euler: f_smooth + f_constraint = M qacc); rows 1..m:
         // sqrt(D) J_r^T of the active rows of the low-rank contacts.
         float V[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // lower 3x3: (00, 10, 20, 11, 21, 22)
+        unsigned bal[3] = {0u, 0u, 0u};
         int vrow[3] = {0, 0, 0};
-        float (*Z)[52 + KS] = W.a.s.Z;
+        float (*Z)[ZS] = W.a.s.Z;
         const float sb = -sgrad;
         {
           // W = V V^T (3x3 Cholesky of the active pyramid rows' weight, rank <= 3): columns U v_j
-          unsigned bal[3] = {0u, 0u, 0u};
           if (!euler && nlr > 0) {
             if (my_lr) {
               const float w0 = W.c_w[0][lane], w1 = W.c_w[1][lane], w2 = W.c_w[2][lane], w3 = W.c_w[3][lane], w4 = W.c_w[4][lane];
@@ -1199,7 +1220,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
             bal[0] = __ballot_sync(FULL, V[0] != 0.f); bal[1] = __ballot_sync(FULL, V[3] != 0.f);
             bal[2] = __ballot_sync(FULL, V[5] != 0.f);
             m = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2]);
-            for (int i = lane; i < m * (52 + KS); i += 32) Z[1 + i / (52 + KS)][i % (52 + KS)] = 0.f;
+            for (int i = lane; i < m * ZS; i += 32) (&Z[1][0])[i] = 0.f;
           }
 #pragma unroll
           for (int h = 0; h < 2; h++) if (L.dof) Z[0][h * 26 + lane] = euler ? Ma[h] : -grad[h];
@@ -1226,7 +1247,8 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
               if (!((sm >> lane) & 1u)) continue;
               const int g = W.slot_hand[s] * 26 + lane;
               const float cf_ = W.a.s.Kc[s][posl] * W.a.s.hss[s];
-              for (int r = 0; r <= m; r++) Z[r][g] -= cf_ * Z[r][52 + s];
+              const int rmax = ((slot_lr_mask >> s) & 1u) ? m : 0;  // other slots: zero in rows 1..m
+              for (int r = 0; r <= rmax; r++) Z[r][g] -= cf_ * Z[r][52 + s];
             }
           }
           __syncwarp();
@@ -1294,38 +1316,45 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
           __syncwarp();
           break;
         }
-        // ---- back-substitute the key slots of every solved vector
+        // ---- back-substitute the key slots touched by low-rank contacts in every solved vector
+        int bs_h = 0, bs_cs = 0; unsigned bs_m = 0u;
         if (lane < nslot) {
-          const int h = W.slot_hand[lane];
-          const unsigned sm = W.slot_mask[lane];
-          const int scs = sm ? cs_of(31 - __clz(sm)) : 0;
-          for (int r = 0; r <= m; r++) {
-            float d = 0.f;
-            unsigned mm = sm;
-            while (mm) { const int dd = __ffs(mm) - 1; mm &= mm - 1; d += W.a.s.Kc[lane][apos(dd, scs)] * Z[r][h * 26 + dd]; }
-            Z[r][52 + lane] = (Z[r][52 + lane] - d) * W.a.s.hss[lane];
+          bs_h = W.slot_hand[lane]; bs_m = W.slot_mask[lane];
+          bs_cs = bs_m ? cs_of(31 - __clz(bs_m)) : 0;
+          if (slot_lr) {
+            for (int r = 0; r <= m; r++) {
+              float d = 0.f;
+              unsigned mm = bs_m;
+              while (mm) { const int dd = __ffs(mm) - 1; mm &= mm - 1; d += W.a.s.Kc[lane][apos(dd, bs_cs)] * Z[r][bs_h * 26 + dd]; }
+              Z[r][52 + lane] = (Z[r][52 + lane] - d) * W.a.s.hss[lane];
+            }
           }
         }
         __syncwarp();
         // ---- Woodbury: p = y0 - Z (I + B^T Z)^-1 B^T y0
+        float (*C)[LRR + 1] = W.a.s.C;
         if (m > 0) {
-          float (*C)[LRR + 1] = W.a.s.C;
-          if (my_lr) {
-            for (int rc = 0; rc <= m; rc++) {  // column rc: Z row rc (0 = y0)
+          // capacitance, lane = solved vector (0: y0 -> right-hand side, 1 + r: column r)
+          unsigned lm = lrb;
+          while (lm) {
+            const int c = __ffs(lm) - 1; lm &= lm - 1;
+            const float v0 = __shfl_sync(FULL, V[0], c), v1 = __shfl_sync(FULL, V[1], c), v2 = __shfl_sync(FULL, V[2], c);
+            const float v3 = __shfl_sync(FULL, V[3], c), v4 = __shfl_sync(FULL, V[4], c), v5 = __shfl_sync(FULL, V[5], c);
+            if (v0 == 0.f) continue;
+            const unsigned ltc = (1u << c) - 1u;
+            const int q0 = __popc(bal[0] & ltc), q1 = __popc(bal[0]) + __popc(bal[1] & ltc);
+            const int q2 = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2] & ltc);
+            if (lane <= m) {
+              const int ne = W.c_nent[c];
               f3 uz = mk3(0, 0, 0);
-              for (int e = 0; e < my_nent; e++) {
-                const float x = Z[rc][W.c_col[e][lane]];
-                uz.x += W.c_u[3 * e][lane] * x; uz.y += W.c_u[3 * e + 1][lane] * x; uz.z += W.c_u[3 * e + 2][lane] * x;
+              for (int e = 0; e < ne; e++) {
+                const float x = Z[lane][W.c_col[e][c]];
+                uz.x += W.c_u[3 * e][c] * x; uz.y += W.c_u[3 * e + 1][c] * x; uz.z += W.c_u[3 * e + 2][c] * x;
               }
-              // C[r][0..m-1] = I + B^T Z ; C[r][m] = B^T y0
-              const float val[3] = {V[0] * uz.x + V[1] * uz.y + V[2] * uz.z, V[3] * uz.y + V[4] * uz.z, V[5] * uz.z};
-#pragma unroll
-              for (int j = 0; j < 3; j++) {
-                if (V[j == 0 ? 0 : j == 1 ? 3 : 5] != 0.f) {
-                  const int r = vrow[j];
-                  if (rc == 0) C[r][m] = val[j]; else C[r][rc - 1] = val[j] + (rc - 1 == r ? 1.f : 0.f);
-                }
-              }
+              const int col = lane == 0 ? m : lane - 1;
+              C[q0][col] = v0 * uz.x + v1 * uz.y + v2 * uz.z + (col == q0 ? 1.f : 0.f);
+              if (v3 != 0.f) C[q1][col] = v3 * uz.y + v4 * uz.z + (col == q1 ? 1.f : 0.f);
+              if (v5 != 0.f) C[q2][col] = v5 * uz.z + (col == q2 ? 1.f : 0.f);
             }
           }
           __syncwarp();
@@ -1348,19 +1377,28 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
           }
           if (lane < m) C[lane][m] = t;
           __syncwarp();
-#pragma unroll
-          for (int h = 0; h < 2; h++)
-            if (L.dof) { float s = Z[0][h * 26 + lane]; for (int r = 0; r < m; r++) s -= Z[1 + r][h * 26 + lane] * C[r][m]; p[h] = s; }
-          if (lane < nslot) { float s = Z[0][52 + lane]; for (int r = 0; r < m; r++) s -= Z[1 + r][52 + lane] * C[r][m]; sp = s; }
-        } else {
-#pragma unroll
-          for (int h = 0; h < 2; h++) if (L.dof) p[h] = Z[0][h * 26 + lane];
-          if (lane < nslot) sp = Z[0][52 + lane];
         }
-        __syncwarp();
 #pragma unroll
-        for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = p[h];
-        if (lane < nslot) W.va[52 + lane] = sp;
+        for (int h = 0; h < 2; h++)
+          if (L.dof) {
+            float s = Z[0][h * 26 + lane];
+            for (int r = 0; r < m; r++) s -= Z[1 + r][h * 26 + lane] * C[r][m];
+            p[h] = s; W.va[h * 26 + lane] = s;
+          }
+        __syncwarp();
+        if (lane < nslot) {
+          if (slot_lr) {
+            float s = Z[0][52 + lane];
+            for (int r = 0; r < m; r++) s -= Z[1 + r][52 + lane] * C[r][m];
+            sp = s;
+          } else {  // the slot's row of H p = -grad, from the final hand part of p
+            float d = 0.f;
+            unsigned mm = bs_m;
+            while (mm) { const int dd = __ffs(mm) - 1; mm &= mm - 1; d += W.a.s.Kc[lane][apos(dd, bs_cs)] * W.va[bs_h * 26 + dd]; }
+            sp = (Z[0][52 + lane] - d) * W.a.s.hss[lane];
+          }
+          W.va[52 + lane] = sp;
+        }
         __syncwarp();
         }
         // ---- J p for every row
@@ -1435,6 +1473,7 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
         // decrement test decides instead)
         if ((m == 0 && !changed && fabsf(alpha - 1.f) < 1e-3f) || iter >= maxit) euler = true;
       }
+      if (WPB > 1 && meet_it) while (__syncthreads_or(0)) {}  // keep the other warps' iteration meetings complete
       // ---- solution: hand dofs, touched keys (slots), untouched keys in closed form
 #pragma unroll
       for (int h = 0; h < 2; h++) acc[h] = a[h];
@@ -1663,13 +1702,27 @@ __global__ void __launch_bounds__(32, 10) pp_hands_step_kernel(HandsArgs A) {
   }
 }
 
-void pp_launch_hands(const HandsArgs& A, cudaStream_t stream) {
+template <int WPB>
+static int launch_wpb(const HandsArgs& A, cudaStream_t stream) {
   static bool configured = false;
   const size_t smem = sizeof(WarpShared);
   if (!configured) {
-    cudaFuncSetAttribute(pp_hands_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(pp_hands_step_kernel<WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * WPB));
+    cudaFuncSetAttribute(pp_hands_step_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured = true;
   }
-  pp_hands_step_kernel<<<A.num_envs, 32, smem, stream>>>(A);
+  const int nblk = A.num_envs / WPB, tail = A.num_envs - nblk * WPB;
+  if (nblk) pp_hands_step_kernel<WPB><<<nblk, 32 * WPB, smem * WPB, stream>>>(A, 0);
+  if (WPB > 1 && tail) pp_hands_step_kernel<1><<<tail, 32, smem, stream>>>(A, nblk * WPB);
+  return (nblk ? 1 : 0) + (WPB > 1 && tail ? 1 : 0);
+}
+int pp_launch_hands(const HandsArgs& A_, cudaStream_t stream) {
+  static int wpb = 0, ml = 1;
+  if (!wpb) { const char* e = getenv("PP_WPB"); wpb = e ? atoi(e) : 2; e = getenv("PP_MEET"); ml = e ? atoi(e) : 1; }
+  HandsArgs A = A_;
+  A.meet_level = ml;
+  if (wpb == 1) return launch_wpb<1>(A, stream);
+  if (wpb == 5) return launch_wpb<5>(A, stream);
+  return launch_wpb<2>(A, stream);
 }
 size_t pp_hands_smem_bytes() { return sizeof(WarpShared); }

@@ -6,6 +6,7 @@
 #include "piano_oracle.h"
 
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -773,8 +774,30 @@ static void solve_newton(const pp_model *m, po_data *d, efc_t *e) {
       if (next == alpha) break;
       alpha = next;
     }
+    static int fullstep = -1;
+    if (fullstep < 0) fullstep = getenv("PO_NEWTON_FULLSTEP") ? atoi(getenv("PO_NEWTON_FULLSTEP")) : 0;
+    if (fullstep) {
+      double *t = (double *)malloc(sizeof(double) * nv);
+      for (int j = 0; j < nv; j++) t[j] = a[j] + p[j];
+      double c1 = total_cost(m, d, e, t, NULL, NULL, NULL);
+      for (int j = 0; j < nv; j++) t[j] = a[j] + alpha * p[j];
+      double ca = total_cost(m, d, e, t, NULL, NULL, NULL);
+      if (fullstep == 1 ? (c1 < cost) : (c1 < cost - 0.5 * (cost - ca))) alpha = 1;
+      free(t);
+    }
     for (int j = 0; j < nv; j++) a[j] += alpha * p[j];
+    double *oldcurv = NULL;
+    static int dbg = -1;
+    if (dbg < 0) dbg = getenv("PO_DEBUG_NEWTON") != NULL;
+    if (dbg) { oldcurv = (double *)malloc(sizeof(double) * ne); memcpy(oldcurv, curv, sizeof(double) * ne); }
     double newcost = total_cost(m, d, e, a, grad, force, curv);
+    if (dbg) {
+      int nfr = 0, nin = 0;
+      for (int r = 0; r < ne; r++) if ((oldcurv[r] != 0) != (curv[r] != 0)) { if (e->type[r] == ROW_INEQ) nin++; else nfr++; }
+      fprintf(stderr, "  newton it %d alpha %.6f improvement %.3e changed fric %d ineq %d (nefc %d)\n", iter, alpha,
+              scale * (cost - newcost), nfr, nin, ne);
+      free(oldcurv);
+    }
     double improvement = scale * (cost - newcost), gnorm = 0;
     cost = newcost;
     for (int j = 0; j < nv; j++) gnorm += grad[j] * grad[j];

@@ -1,6 +1,7 @@
 """Aggregates an `ncu --page source --csv` SASS dump by CUDA source line, using nvdisasm line info.
 
-usage: python tools/ncu_lines.py <report.ncu-rep> <libpiano_step.so> <kernel substring> [top N]
+usage: python tools/ncu_lines.py <report.ncu-rep> <libpiano_step.so> <kernel substring> [top N] [bucket]
+Lines are the OUTERMOST call site (nvdisasm -gi inline chains); bucket > 0 sums over ranges of that many lines.
 """
 import csv
 import re
@@ -14,11 +15,12 @@ from pathlib import Path
 def main():
     rep, so, kern = sys.argv[1:4]
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 50
+    bucket = int(sys.argv[5]) if len(sys.argv) > 5 else 0
     tmp = Path(tempfile.mkdtemp())
     subprocess.run(["cuobjdump", "-xelf", "all", str(Path(so).resolve())], cwd=tmp, check=True, capture_output=True)
     lines = None
     for cubin in tmp.glob("*.cubin"):
-        sass = subprocess.run(["nvdisasm", "-g", "-c", str(cubin)], capture_output=True, text=True).stdout.splitlines()
+        sass = subprocess.run(["nvdisasm", "-gi", "-c", str(cubin)], capture_output=True, text=True).stdout.splitlines()
         cur, infunc, out = None, False, []
         for ln in sass:
             if ".section" in ln and ".text." in ln:
@@ -37,6 +39,7 @@ def main():
     agg, samp = defaultdict(float), defaultdict(float)
     for i in range(min(len(rows), len(lines))):
         key = lines[i] or ("?", 0)
+        if bucket: key = (key[0], key[1] // bucket * bucket)
         agg[key] += float(rows[i][5]); samp[key] += float(rows[i][4])
     tot, ts = sum(agg.values()), sum(samp.values())
     print(f"warp instructions executed: {tot:.4g}")
