@@ -234,7 +234,7 @@ def run_product(args) -> None:
     torch.cuda.synchronize(dev)
     cm = cnt.float().mean(0).tolist()
     solver = {"contacts_last_substep": cm[0], "rows_last_substep": cm[1], "newton_iters_per_step": cm[4],
-              "linesearch_iters_per_step": cm[5], "majorised_cross_contacts_per_step": cm[6],
+              "linesearch_iters_per_step": cm[5], "dense_fallback_substeps_per_step": cm[6],
               "lowrank_cross_contacts_per_step": cm[7], "dropped_contacts": cm[3]}
 
     # ---- end to end through the C-ABI with host buffers (pp_step_host)

@@ -101,8 +101,8 @@ int pp_set_qfrc_applied(pp_env *env, const float *qfrc_dev, void *stream);
 /* diagnostics of the LAST substep of the last pp_step (device pointers, any may be NULL):
  * qacc [N,nv]; actuator_force [N,nu]; actuator_velocity [N,nu]; site_xpos [N,nsite,3];
  * activation [N,88] u8; counters [N,8] i32 = {ncon, nefc, newton iterations, dropped contacts} of the last substep, then
- * sums over the substeps of the last step: {newton iterations, line-search iterations, cross-finger
- * contacts majorised inside the fronts, cross-finger contacts solved as a low-rank correction} */
+ * sums over the substeps of the last step: {newton iterations, line-search iterations, substeps
+ * that took the dense fallback solver, cross-finger contacts (low-rank correction or dense)} */
 int pp_get_diag(pp_env *env, float *qacc_dev, float *actuator_force_dev,
                 float *actuator_velocity_dev, float *site_xpos_dev, uint8_t *activation_dev,
                 int32_t *counters_dev, void *stream);
