@@ -341,6 +341,124 @@ __device__ __noinline__ void dense_factor_solve(float* H, int lane, bool dof, fl
   }
 }
 
+// ------------------------------------------------------------------ OT fingering reward
+// _compute_ot_fingering_reward (piano_with_shadow_hands.py:333-369): distances between the 10
+// fingertips (left hand first) and the K keys to press, scipy.optimize.linear_sum_assignment
+// (rectangular shortest-augmenting-path; transposed when K < 10), mean tolerance over the min(10, K)
+// assigned pairs. One warp: column c of the cost matrix lives in lane c % 32, slot c / 32.
+// `sm` is scratch shared memory (>= 1300 floats); once per control step, kept out of line.
+__device__ __noinline__ float ot_fingering_reward(float* sm, int lane, f3 site, const float qk[3],
+                                                  const uint8_t* goal_cur, const KeyTables& kt) {
+  float* cost = sm;              // [10][88]
+  float* kp = sm + 880;          // [88][3] key surface points of the keys to press
+  float* tips = kp + 264;        // [10][3]
+  float* u = tips + 30;          // [10] row duals
+  int* col4row = reinterpret_cast<int*>(u + 10);  // [10]
+  int* inSR = col4row + 10;      // [10]
+  const unsigned lt = (1u << lane) - 1u;
+  int K = 0;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const int k = lane + 32 * i;
+    const bool on = k < PP_NKEY && goal_cur[k] != 0;
+    const unsigned b = __ballot_sync(FULL, on);
+    if (on) {
+      const int idx = K + __popc(b & lt);
+      float sq_, cq_;
+      pp_sincos_small(qk[i], &sq_, &cq_);
+      const float hx = kt.half[k][0];
+      kp[3 * idx] = kt.pos[k][0] - hx + hx * cq_ + 0.35f * hx;
+      kp[3 * idx + 1] = kt.pos[k][1];
+      kp[3 * idx + 2] = kt.pos[k][2] - hx * sq_ + 0.5f * kt.half[k][2];
+    }
+    K += __popc(b);
+  }
+  if (K == 0) return 1.f;
+  if (lane < PP_NSITE) { const int r = lane >= 5 ? lane - 5 : lane + 5; st3(tips + 3 * r, site); }
+  __syncwarp();
+  const bool tr = K < 10;  // rows = keys, columns = fingers
+  const int n = tr ? K : 10, m = tr ? 10 : K;
+  for (int r = 0; r < n; r++)
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      const int c = lane + 32 * i;
+      if (c < m) cost[r * 88 + c] = norm(ld3(kp + 3 * (tr ? r : c)) - ld3(tips + 3 * (tr ? c : r)));
+    }
+  if (lane < 10) { u[lane] = 0.f; col4row[lane] = -1; }
+  __syncwarp();
+  const float INF = 3.0e38f;
+  float v[3] = {0.f, 0.f, 0.f};
+  int row4col[3] = {-1, -1, -1};
+  for (int cur = 0; cur < n; cur++) {
+    float shortest[3] = {INF, INF, INF};
+    int path[3] = {-1, -1, -1};
+    bool inSC[3] = {false, false, false};
+    if (lane < 10) inSR[lane] = 0;
+    __syncwarp();
+    int i = cur, sink = -1;
+    float min_val = 0.f;
+    while (sink < 0) {
+      if (lane == 0) inSR[i] = 1;
+      const float ui = u[i];
+      float best = INF; int bslot = 0;
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const int c = lane + 32 * k;
+        if (c < m && !inSC[k]) {
+          const float r = min_val + cost[i * 88 + c] - ui - v[k];
+          if (r < shortest[k]) { shortest[k] = r; path[k] = i; }
+          // ties prefer a column without a row (as scipy does)
+          if (shortest[k] < best || (shortest[k] == best && row4col[k] < 0)) { best = shortest[k]; bslot = k; }
+        }
+      }
+      float gmin = best;
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) gmin = fminf(gmin, __shfl_xor_sync(FULL, gmin, off));
+      if (!(gmin < INF)) return 0.f;  // infeasible: cannot happen with finite distances
+      const unsigned who = __ballot_sync(FULL, best == gmin);
+      const int wl = __ffs(who) - 1;
+      const int jslot = __shfl_sync(FULL, bslot, wl);
+      const int jrow = __shfl_sync(FULL, bslot == 0 ? row4col[0] : bslot == 1 ? row4col[1] : row4col[2], wl);
+      min_val = gmin;
+      if (lane == wl) {
+        if (jslot == 0) inSC[0] = true; else if (jslot == 1) inSC[1] = true; else inSC[2] = true;
+      }
+      if (jrow < 0) sink = wl + 32 * jslot; else i = jrow;
+      __syncwarp();
+    }
+    // dual updates; shortest[] goes through shared memory (kp is dead once the cost matrix is built)
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const int c = lane + 32 * k;
+      if (c < m) kp[c] = shortest[k];
+    }
+    __syncwarp();
+    if (lane < n && inSR[lane]) {
+      if (lane == cur) u[lane] += min_val;
+      else u[lane] += min_val - kp[col4row[lane]];
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) if (inSC[k]) v[k] -= min_val - shortest[k];
+    __syncwarp();
+    // augment along the alternating path
+    int j = sink;
+    for (;;) {
+      const int jl = j & 31, js = j >> 5;
+      const int pi = __shfl_sync(FULL, js == 0 ? path[0] : js == 1 ? path[1] : path[2], jl);
+      if (lane == jl) { if (js == 0) row4col[0] = pi; else if (js == 1) row4col[1] = pi; else row4col[2] = pi; }
+      const int prev = col4row[pi];
+      __syncwarp();
+      if (lane == 0) col4row[pi] = j;
+      __syncwarp();
+      j = prev;
+      if (pi == cur) break;
+    }
+  }
+  float tot = 0.f;
+  if (lane < n) tot = pp_tolerance(cost[lane * 88 + col4row[lane]], 0.01f, 0.1f);
+  return wsum(tot) / (float)n;
+}
+
 // ------------------------------------------------------------------ kinematics
 struct Kin {
   f3 pos[2];   // node origin (world)
@@ -1608,7 +1726,9 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
     }
     fing = cnt > 0 ? tot / (float)cnt : 0.f;
   } else {
-    fing = n_on == 0 ? 1.f : 0.f;  // OT fingering: exact only for the empty case
+    // unfingered MIDI: optimal-transport fingering reward. The kinematics scratch is dead by now.
+    __syncwarp();
+    fing = do_reset ? 0.f : ot_fingering_reward(&W.a.s.Z[0][0], lane, site, qk, goal_cur, kt);
   }
 
   const bool should_terminate = !do_reset && t_idx == T;

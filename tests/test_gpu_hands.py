@@ -197,3 +197,46 @@ def test_short_song_terminates_and_specs(cuda_lib):
         assert ts.discount == 1.0
     assert n == len(task._notes)
     env.close()
+
+
+def _chord_midi(pitches, dur=1.0):
+    """Unfingered MIDI (every note part 0): `pitches` held together for `dur` seconds."""
+    from diffusion_piano_b200.music import midi_file
+    from diffusion_piano_b200.music.sequence import NoteSequence
+    seq = NoteSequence()
+    for p in pitches:
+        seq.notes.add(start_time=0.0, end_time=dur, velocity=80, pitch=p, part=0)
+    seq.total_time = dur
+    seq.tempos.add(qpm=60)
+    return midi_file.MidiFile(seq=seq)
+
+
+@pytest.mark.parametrize("song", ["CrossingFieldCut10s", "chord3", "chord14"])
+def test_ot_fingering_reward_unfingered_midi(cuda_lib, song):
+    """BASELINE config 4 family: a MIDI without fingering gets the optimal-transport fingering reward
+    (piano_with_shadow_hands.py:333-369, scipy linear_sum_assignment in the oracle) and no `fingering`
+    observation. chord3: fewer keys than fingers (transposed assignment); chord14: more keys than fingers."""
+    from diffusion_piano_b200 import music
+    midi = {"chord3": lambda: _chord_midi([48, 64, 79]),
+            "chord14": lambda: _chord_midi([36, 40, 43, 47, 50, 54, 57, 60, 64, 67, 71, 74, 78, 81])}.get(
+                song, lambda: music.load(song))()
+    task = _task(midi=midi, n_steps_lookahead=1)
+    assert "ot_fingering_reward" in task.reward_names
+    s = _Synced(task)
+    assert "fingering" not in s.env.observation_spec()
+    rng = np.random.RandomState(5)
+    seen = []
+    for t in range(12):
+        a = _spec_random(s.ora, rng)
+        a[:44] = s.ora.act_lo + (0.3 + 0.4 * rng.uniform(0, 1, 44)) * (s.ora.act_hi - s.ora.act_lo)
+        obs, rew, done, obs_o, r_o, d_o = s.step(a)
+        assert set(obs) == set(obs_o)
+        terms = s.env.reward_terms
+        for name, val in s.ora.reward_terms.items():
+            np.testing.assert_allclose(terms[name][0], val, atol=3e-4, err_msg=f"{name} step {t}")
+        seen.append(s.ora.reward_terms["ot_fingering_reward"])
+        np.testing.assert_allclose(rew[0], r_o, atol=5e-4)
+        if d_o:
+            break
+    assert len(set(np.round(seen, 6))) > 1  # the term moves with the hands
+    s.close()
