@@ -177,11 +177,10 @@ def run_product(args) -> None:
     import torch
     import torch.distributed as dist
 
-    from diffusion_piano_b200 import suite
+    from diffusion_piano_b200 import sharding, suite
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    shard = sharding.shard_from_env(args.envs)  # rank r owns global envs [r*B, (r+1)*B): no collective in the step
+    rank, world, local = shard.rank, shard.world_size, shard.local_rank
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product arm has no CPU fallback")
     torch.cuda.set_device(local)
@@ -253,10 +252,7 @@ def run_product(args) -> None:
     h2d = B * 45 * 4
     d2h = B * (env.obs_dim + 1 + 5 + 1) * 4 + B
 
-    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms = float(t[0].item()), float(t[1].item())
+    dev_ms, e2e_ms = sharding.max_over_ranks([dev_ms, e2e_s * 1e3], device=dev)
     if rank == 0:
         peaks_path = ROOT / "MEASURED_PEAKS.json"
         if peaks_path.exists():
@@ -264,9 +260,14 @@ def run_product(args) -> None:
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
         bpe = bytes_per_env_step(env.obs_dim)
+        traffic = None  # dram read + write of one launch from the committed ncu --set full capture
+        tpath = ROOT / "profiles" / "r01_traffic.json"
+        if tpath.exists() and B == 4096:
+            tj = json.loads(tpath.read_text())
+            traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / 1e9  # GB per launch, like achieved * kernel_s
         kern_ms = dev_ms / K  # one kernel launch per step: the step IS the dominant kernel
         achieved = bpe * B / (kern_ms * 1e-3) / 1e9
-        line = {"metric": METRIC, "value": B * world * K / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        line = {"metric": METRIC, "value": sharding.whole_job_throughput(shard, K, dev_ms), "unit": UNIT, "n_gpus": world,
                 "steps": K, "warmup": Wm, "ms_per_step": dev_ms / K, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": workload_config(B, world, task),
@@ -274,7 +275,8 @@ def run_product(args) -> None:
                         "d2h_bytes_per_step": d2h},
                 "gpu_launches": int(launches), "clocks": clocks,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                             "frac": achieved / peak, "traffic": traffic, "traffic_unit": "GB per launch (ncu)",
+                             "algorithmic_gb_per_launch": bpe * B / 1e9, "peak_source": peak_src,
                              "bytes_per_env_step": bpe, "kernel": "pp_hands_step_kernel",
                              "kernel_ms": kern_ms},
                 "wall_ms_per_step_incl_flush": 1e3 * t_wall / K, "mean_reward_last_step": rew_mean, "solver": solver}
