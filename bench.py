@@ -237,10 +237,22 @@ def run_product(args) -> None:
               "lowrank_cross_contacts_per_step": cm[7], "dropped_contacts": cm[3]}
 
     # ---- end to end through the C-ABI with host buffers (pp_step_host)
-    h_act = [np.ascontiguousarray(np.broadcast_to(table[(Wm + K + i) % period], (B, 45))) for i in range(K)]
-    h_obs = np.zeros((B, env.obs_dim), np.float32)
-    h_rew = np.zeros(B, np.float32); h_done = np.zeros(B, np.uint8)
-    h_terms = np.zeros((B, 5), np.float32); h_disc = np.zeros(B, np.float32)
+    # host buffers are page-locked (the contract's "pinned host memory"): the library DMAs to/from them
+    keep = []
+
+    def pinned(shape, dtype):
+        t = torch.zeros(shape, dtype=dtype).pin_memory()
+        keep.append(t)
+        return t.numpy()
+
+    h_act = []
+    for i in range(K):
+        buf = pinned((B, 45), torch.float32)
+        buf[...] = table[(Wm + K + i) % period]
+        h_act.append(buf)
+    h_obs = pinned((B, env.obs_dim), torch.float32)
+    h_rew = pinned((B,), torch.float32); h_done = pinned((B,), torch.uint8)
+    h_terms = pinned((B, 5), torch.float32); h_disc = pinned((B,), torch.float32)
     for i in range(2):
         env.engine.step_host(h_act[i], h_obs, h_rew, h_done, h_terms, h_disc)
     barrier()

@@ -405,27 +405,41 @@ extern "C" int pp_step(pp_env* e, const float* actions_dev, float* obs_dev, floa
                 discount_dev, (cudaStream_t)stream);
 }
 
+// Page-locked caller buffers (cudaHostAlloc / cudaHostRegister / torch pin_memory) are copied to and
+// from directly; pageable ones go through the handle's pinned staging buffers plus a host memcpy.
+static bool is_pinned(const void* p) {
+  if (!p) return false;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+static cudaError_t d2h(void* user, void* staging, const void* dev, size_t bytes, bool direct, cudaStream_t s) {
+  return cudaMemcpyAsync(direct ? user : staging, dev, bytes, cudaMemcpyDeviceToHost, s);
+}
+
 extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* reward, float* terms,
                             uint8_t* done, float* discount) {
   if (!e || !actions || !reward || !done) return fail(PP_ERR_INVALID, "null argument");
   const size_t N = e->cfg.num_envs;
   cudaStream_t s = e->hstream;
-  memcpy(e->h_actions, actions, N * e->action_dim * 4);
-  CUDA_OK(cudaMemcpyAsync(e->d_actions, e->h_actions, N * e->action_dim * 4, cudaMemcpyHostToDevice, s));
+  const bool pa = is_pinned(actions), po = is_pinned(obs), pr = is_pinned(reward), pt = is_pinned(terms),
+             pd = is_pinned(done), pc = is_pinned(discount);
+  if (!pa) memcpy(e->h_actions, actions, N * e->action_dim * 4);
+  CUDA_OK(cudaMemcpyAsync(e->d_actions, pa ? actions : e->h_actions, N * e->action_dim * 4, cudaMemcpyHostToDevice, s));
   int rc = launch(e, PP_MODE_STEP, nullptr, e->d_actions, obs ? e->d_obs : nullptr, e->d_reward,
                   terms ? e->d_terms : nullptr, e->d_done, discount ? e->d_discount : nullptr, s);
   if (rc != PP_OK) return rc;
-  if (obs) CUDA_OK(cudaMemcpyAsync(e->h_obs, e->d_obs, N * e->obs_dim * 4, cudaMemcpyDeviceToHost, s));
-  CUDA_OK(cudaMemcpyAsync(e->h_reward, e->d_reward, N * 4, cudaMemcpyDeviceToHost, s));
-  if (terms) CUDA_OK(cudaMemcpyAsync(e->h_terms, e->d_terms, N * 5 * 4, cudaMemcpyDeviceToHost, s));
-  if (discount) CUDA_OK(cudaMemcpyAsync(e->h_discount, e->d_discount, N * 4, cudaMemcpyDeviceToHost, s));
-  CUDA_OK(cudaMemcpyAsync(e->h_done, e->d_done, N, cudaMemcpyDeviceToHost, s));
+  if (obs) CUDA_OK(d2h(obs, e->h_obs, e->d_obs, N * e->obs_dim * 4, po, s));
+  CUDA_OK(d2h(reward, e->h_reward, e->d_reward, N * 4, pr, s));
+  if (terms) CUDA_OK(d2h(terms, e->h_terms, e->d_terms, N * 5 * 4, pt, s));
+  if (discount) CUDA_OK(d2h(discount, e->h_discount, e->d_discount, N * 4, pc, s));
+  CUDA_OK(d2h(done, e->h_done, e->d_done, N, pd, s));
   CUDA_OK(cudaStreamSynchronize(s));
-  if (obs) memcpy(obs, e->h_obs, N * e->obs_dim * 4);
-  memcpy(reward, e->h_reward, N * 4);
-  if (terms) memcpy(terms, e->h_terms, N * 5 * 4);
-  if (discount) memcpy(discount, e->h_discount, N * 4);
-  memcpy(done, e->h_done, N);
+  if (obs && !po) memcpy(obs, e->h_obs, N * e->obs_dim * 4);
+  if (!pr) memcpy(reward, e->h_reward, N * 4);
+  if (terms && !pt) memcpy(terms, e->h_terms, N * 5 * 4);
+  if (discount && !pc) memcpy(discount, e->h_discount, N * 4);
+  if (!pd) memcpy(done, e->h_done, N);
   return PP_OK;
 }
 
@@ -433,13 +447,14 @@ extern "C" int pp_reset_host(pp_env* e, const uint8_t* mask, float* obs) {
   if (!e) return fail(PP_ERR_INVALID, "null handle");
   const size_t N = e->cfg.num_envs;
   cudaStream_t s = e->hstream;
+  const bool po = is_pinned(obs);
   if (mask) CUDA_OK(cudaMemcpyAsync(e->d_mask, mask, N, cudaMemcpyHostToDevice, s));
   int rc = launch(e, PP_MODE_RESET, mask ? e->d_mask : nullptr, nullptr, obs ? e->d_obs : nullptr, nullptr,
                   nullptr, nullptr, nullptr, s);
   if (rc != PP_OK) return rc;
-  if (obs) CUDA_OK(cudaMemcpyAsync(e->h_obs, e->d_obs, N * e->obs_dim * 4, cudaMemcpyDeviceToHost, s));
+  if (obs) CUDA_OK(d2h(obs, e->h_obs, e->d_obs, N * e->obs_dim * 4, po, s));
   CUDA_OK(cudaStreamSynchronize(s));
-  if (obs) memcpy(obs, e->h_obs, N * e->obs_dim * 4);
+  if (obs && !po) memcpy(obs, e->h_obs, N * e->obs_dim * 4);
   return PP_OK;
 }
 

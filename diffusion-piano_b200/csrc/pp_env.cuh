@@ -28,7 +28,6 @@ struct HandsArgs {
   int num_envs, mode, n_substeps, n_frames, lookahead, obs_dim, pmax;
   int canonical, has_fingering, disable_forearm_reward, wrong_press_termination, auto_reset;
   int max_contacts;
-  int meet_level;  // 0: warps of a block run free, 1: meet at substep phases, 2: and at every Newton iteration
   float energy_coef;
   const uint8_t* goal;    // [T,89]
   const int16_t* pairs;   // [T,pmax,2]

@@ -24,7 +24,6 @@
 //   contact needs them.
 //   mj_Euler with implicit joint damping.
 #include "../../include/pp_model.h"
-#include <cstdlib>
 #include "pp_env.cuh"
 #include "pp_keys.cuh"
 
@@ -550,8 +549,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   const bool do_reset = A.mode == PP_MODE_RESET ? (A.reset_mask ? A.reset_mask[env] != 0 : true)
                                                 : (A.auto_reset && A.needs_reset[env]);
   bool meet = false;
-  if (WPB > 1) meet = __syncthreads_and(A.mode != PP_MODE_RESET && !do_reset) != 0 && A.meet_level > 0;
-  const bool meet_it = meet && A.meet_level > 1;
+  if (WPB > 1) meet = __syncthreads_and(A.mode != PP_MODE_RESET && !do_reset) != 0;
   if (A.mode == PP_MODE_RESET && !do_reset) return;
 #define PP_MEET() do { if (WPB > 1 && meet) __syncthreads(); } while (0)
 
@@ -1079,7 +1077,6 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       const int maxit = min(o.iterations, 50);
       bool euler = false;
       for (;;) {
-        if (WPB > 1 && meet_it) __syncthreads_or(1);
         // ---- row forces and curvatures at the current point
         float ff[2] = {0.f, 0.f}, fc_[2] = {0.f, 0.f}, lf[2] = {0.f, 0.f}, lc[2] = {0.f, 0.f};
         int fz[2] = {0, 0};
@@ -1591,7 +1588,6 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         // decrement test decides instead)
         if ((m == 0 && !changed && fabsf(alpha - 1.f) < 1e-3f) || iter >= maxit) euler = true;
       }
-      if (WPB > 1 && meet_it) while (__syncthreads_or(0)) {}  // keep the other warps' iteration meetings complete
       // ---- solution: hand dofs, touched keys (slots), untouched keys in closed form
 #pragma unroll
       for (int h = 0; h < 2; h++) acc[h] = a[h];
@@ -1836,13 +1832,6 @@ static int launch_wpb(const HandsArgs& A, cudaStream_t stream) {
   if (WPB > 1 && tail) pp_hands_step_kernel<1><<<tail, 32, smem, stream>>>(A, nblk * WPB);
   return (nblk ? 1 : 0) + (WPB > 1 && tail ? 1 : 0);
 }
-int pp_launch_hands(const HandsArgs& A_, cudaStream_t stream) {
-  static int wpb = 0, ml = 1;
-  if (!wpb) { const char* e = getenv("PP_WPB"); wpb = e ? atoi(e) : 2; e = getenv("PP_MEET"); ml = e ? atoi(e) : 1; }
-  HandsArgs A = A_;
-  A.meet_level = ml;
-  if (wpb == 1) return launch_wpb<1>(A, stream);
-  if (wpb == 5) return launch_wpb<5>(A, stream);
-  return launch_wpb<2>(A, stream);
-}
+constexpr int WARPS_PER_BLOCK = 2;  // measured on B200: 1 -> 480 k, 2 -> 549 k, 5 -> 487 k env-steps/s (profiles/)
+int pp_launch_hands(const HandsArgs& A, cudaStream_t stream) { return launch_wpb<WARPS_PER_BLOCK>(A, stream); }
 size_t pp_hands_smem_bytes() { return sizeof(WarpShared); }

@@ -40,12 +40,19 @@ class BatchedEnvironment:
         self._discount = torch.ones(n, dtype=torch.float32, device=self.device)
         self._done = torch.zeros(n, dtype=torch.uint8, device=self.device)
         self._canonical = canonical_actions
-        # host staging for the numpy API
-        self._h_obs = np.zeros((n, self.obs_dim), np.float32)
-        self._h_reward = np.zeros(n, np.float32)
-        self._h_terms = np.zeros((n, 5), np.float32)
-        self._h_discount = np.ones(n, np.float32)
-        self._h_done = np.zeros(n, np.uint8)
+        # host side of the numpy API: page-locked, so pp_step_host copies straight into these arrays
+        def pinned(shape, dtype, fill=0):
+            t = torch.full(shape, fill, dtype=dtype).pin_memory()
+            self._pinned.append(t)  # keeps the allocation alive under the numpy view
+            return t.numpy()
+
+        self._pinned = []
+        self._h_obs = pinned((n, self.obs_dim), torch.float32)
+        self._h_reward = pinned((n,), torch.float32)
+        self._h_terms = pinned((n, 5), torch.float32)
+        self._h_discount = pinned((n,), torch.float32, 1)
+        self._h_done = pinned((n,), torch.uint8)
+        self._h_actions = pinned((n, self.action_dim), torch.float32)
 
     # ---- specs
     def action_spec(self) -> specs.BoundedArray:
@@ -78,10 +85,12 @@ class BatchedEnvironment:
         return self._split(self._h_obs)
 
     def step(self, actions):
-        a = np.ascontiguousarray(actions, np.float32)
+        a = np.asarray(actions)
         if a.shape != (self.num_envs, self.action_dim):
             raise ValueError(f"actions must have shape {(self.num_envs, self.action_dim)}, got {a.shape}")
-        self.engine.step_host(a, self._h_obs, self._h_reward, self._h_done, self._h_terms, self._h_discount)
+        self._h_actions[...] = a  # float64 -> float32 into the page-locked buffer
+        self.engine.step_host(self._h_actions, self._h_obs, self._h_reward, self._h_done, self._h_terms,
+                              self._h_discount)
         return self._split(self._h_obs), self._h_reward.astype(np.float64), self._h_done.astype(bool)
 
     @property

@@ -83,8 +83,10 @@ int pp_reset(pp_env *env, const uint8_t *mask_dev, float *obs_dev, void *stream)
  * discount_dev [N] f32 or NULL. */
 int pp_step(pp_env *env, const float *actions_dev, float *obs_dev, float *reward_dev,
             float *reward_terms_dev, uint8_t *done_dev, float *discount_dev, void *stream);
-/* Host-buffer variant: H2D of actions, step, D2H of obs/reward/done inside the call
- * (pinned staging owned by the handle); returns after the results are on the host. */
+/* Host-buffer variant: H2D of actions, step, D2H of obs/reward/done inside the call; returns
+ * after the results are on the host. Page-locked caller buffers (cudaHostAlloc, cudaHostRegister,
+ * torch pin_memory) are the DMA endpoints themselves; pageable ones go through pinned staging
+ * owned by the handle plus one host memcpy each. */
 int pp_step_host(pp_env *env, const float *actions, float *obs, float *reward,
                  float *reward_terms, uint8_t *done, float *discount);
 int pp_reset_host(pp_env *env, const uint8_t *mask, float *obs);
