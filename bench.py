@@ -83,6 +83,8 @@ class CpuPort:
         a = task.model.a
         self.lo, self.hi = a["act_ctrlrange"][:, 0].copy(), a["act_ctrlrange"][:, 1].copy()
         self.nsub = task.physics_steps_per_control_step
+        # all host cores, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1)
+        op.lib().po_set_num_threads(os.cpu_count() or 1)
 
     def step(self, canonical_action: np.ndarray) -> None:
         ctrl = self.lo + 0.5 * (canonical_action[:44].astype(np.float64) + 1.0) * (self.hi - self.lo)

@@ -57,6 +57,7 @@ def lib():
         _LIB.po_forward_position.argtypes = [ctypes.c_void_p, ctypes.POINTER(_Data), ctypes.c_int]
         _LIB.po_step_batch.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.POINTER(_Data)),
                                        ctypes.c_int, ctypes.c_int]
+        _LIB.po_set_num_threads.argtypes = [ctypes.c_int]
     return _LIB
 
 

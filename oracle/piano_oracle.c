@@ -6,6 +6,9 @@
 #include "piano_oracle.h"
 
 #include <math.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -856,7 +859,14 @@ void po_step(const pp_model *m, po_data *d) {
   actuator_velocity(m, d); /* actuatorvel sensor as refreshed by the trailing mj_step1 */
 }
 
+/* threads of po_step_batch; 0 = OpenMP's default (OMP_NUM_THREADS, which torchrun sets to 1) */
+static int po_threads = 0;
+void po_set_num_threads(int n) { po_threads = n > 0 ? n : 0; }
+
 void po_step_batch(const pp_model *m, po_data **d, int nenv, int nsub) {
+#ifdef _OPENMP
+  if (po_threads > 0) omp_set_num_threads(po_threads);
+#endif
 #pragma omp parallel for schedule(dynamic, 1)
   for (int i = 0; i < nenv; i++)
     for (int s = 0; s < nsub; s++) po_step(m, d[i]);

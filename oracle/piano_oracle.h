@@ -67,6 +67,7 @@ void po_forward_position(const pp_model *m, po_data *d, int with_collision);
 void po_step(const pp_model *m, po_data *d);
 /* n env-independent steps over a batch, OpenMP over envs; for the CPU baseline */
 void po_step_batch(const pp_model *m, po_data **d, int nenv, int nsub);
+void po_set_num_threads(int n); /* threads used by po_step_batch (0 = OpenMP default) */
 
 #ifdef __cplusplus
 }
