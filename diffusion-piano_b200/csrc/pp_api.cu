@@ -31,6 +31,8 @@ struct pp_env {
   uint8_t* goal = nullptr;
   int16_t* pairs = nullptr;
   float *qpos = nullptr, *qvel = nullptr, *warm = nullptr, *sustain = nullptr, *qfrc_applied = nullptr;
+  float *hand_off = nullptr, *hand_off_pending = nullptr;  // per-env y shift of both hands (active / drawn for the next reset)
+  bool use_hand_off = false;
   int* t_idx = nullptr;
   uint8_t* needs_reset = nullptr;
   float *qacc = nullptr, *act_force = nullptr, *act_vel = nullptr, *site_xpos = nullptr;
@@ -296,6 +298,7 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(dalloc(&e->qpos, N * nv)); CUDA_OK(dalloc(&e->qvel, N * nv)); CUDA_OK(dalloc(&e->warm, N * nv));
   CUDA_OK(dalloc(&e->qfrc_applied, N * nv)); CUDA_OK(dalloc(&e->qacc, N * nv));
   CUDA_OK(dalloc(&e->sustain, N)); CUDA_OK(dalloc(&e->t_idx, N)); CUDA_OK(dalloc(&e->needs_reset, N));
+  CUDA_OK(dalloc(&e->hand_off, N)); CUDA_OK(dalloc(&e->hand_off_pending, N));
   CUDA_OK(dalloc(&e->act_force, (size_t)N * (e->nu ? e->nu : 1)));
   CUDA_OK(dalloc(&e->act_vel, (size_t)N * (e->nu ? e->nu : 1)));
   CUDA_OK(dalloc(&e->site_xpos, (size_t)N * 3 * PP_NSITE));
@@ -328,7 +331,7 @@ extern "C" int pp_destroy(pp_env* e) {
   void* dev[] = {e->dm, e->goal, e->pairs, e->qpos, e->qvel, e->warm, e->sustain, e->qfrc_applied, e->t_idx,
                  e->needs_reset, e->qacc, e->act_force, e->act_vel, e->site_xpos, e->activation, e->counters,
                  e->act_min_d, e->act_max_d, e->d_actions, e->d_obs, e->d_reward, e->d_terms, e->d_discount,
-                 e->d_done, e->d_mask};
+                 e->d_done, e->d_mask, e->hand_off, e->hand_off_pending};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -379,6 +382,7 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     A.goal = e->goal; A.pairs = e->pairs; A.reset_mask = mask; A.actions = actions;
     A.act_min = e->act_min_d; A.act_max = e->act_max_d;
     A.qfrc_applied = e->use_applied ? e->qfrc_applied : nullptr;
+    A.hand_off = e->use_hand_off ? e->hand_off : nullptr; A.hand_off_pending = e->hand_off_pending;
     A.qpos = e->qpos; A.qvel = e->qvel; A.warm = e->warm; A.t_idx = e->t_idx; A.sustain = e->sustain;
     A.needs_reset = e->needs_reset; A.obs = obs; A.reward = reward; A.reward_terms = terms;
     A.discount = discount; A.done = done; A.qacc = e->qacc; A.act_force = e->act_force;
@@ -489,6 +493,20 @@ extern "C" int pp_set_qfrc_applied(pp_env* e, const float* qfrc, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   e->use_applied = qfrc != nullptr;
   if (qfrc) COPY_IF(e->qfrc_applied, qfrc, (size_t)e->cfg.num_envs * e->nv * 4);
+  return PP_OK;
+}
+
+extern "C" int pp_set_hand_offsets(pp_env* e, const float* y_off, void* stream) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  if (e->cfg.task != PP_TASK_PIANO_WITH_SHADOW_HANDS) return fail(PP_ERR_INVALID, "task has no hands");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t bytes = (size_t)e->cfg.num_envs * 4;
+  if (y_off) {
+    e->use_hand_off = true;
+    COPY_IF(e->hand_off_pending, y_off, bytes);
+  } else {  // back to the model's own hand positions from the next reset on
+    CUDA_OK(cudaMemsetAsync(e->hand_off_pending, 0, bytes, s));
+  }
   return PP_OK;
 }
 

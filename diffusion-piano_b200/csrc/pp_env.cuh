@@ -36,6 +36,8 @@ struct HandsArgs {
   const float* act_min;   // [45] action spec
   const float* act_max;   // [45]
   const float* qfrc_applied;  // [N,140] or null
+  float* hand_off;                // [N] y shift of both hands in force (null: feature unused)
+  const float* hand_off_pending;  // [N] y shift an env takes at its next reset
   float *qpos, *qvel, *warm;  // [N,140]
   int* t_idx;
   float* sustain;

@@ -469,7 +469,7 @@ struct Kin {
 
 template <bool DYN>
 __device__ __forceinline__ void forward_kinematics(const HandTables& ht, const Options& o, const LaneCtx& L,
-                                                   const float q[2], const float v[2], Kin& K) {
+                                                   const float q[2], const float v[2], float yoff, Kin& K) {
   const int l = L.dof ? L.lane : 25;
   f3 lpos[2], axl[2]; f4 lquat[2];
 #pragma unroll
@@ -484,7 +484,8 @@ __device__ __forceinline__ void forward_kinematics(const HandTables& ht, const O
     const f4 qf = ld4(ht.body_quat[h * PP_HB]);
     const f3 a0 = qrot(qf, ld3(ht.axis[h * PP_HD])), a1 = qrot(qf, ld3(ht.axis[h * PP_HD + 1]));
     const float q0 = __shfl_sync(FULL, q[h], 0), q1 = __shfl_sync(FULL, q[h], 1);
-    const f3 pf = ld3(ht.body_pos[h * PP_HB]) + q0 * a0 + q1 * a1;
+    f3 pf = ld3(ht.body_pos[h * PP_HB]) + q0 * a0 + q1 * a1;
+    pf.y += yoff;  // Entity.shift_pose of the attachment frame (randomize_hand_positions)
     K.ref[h] = pf + qrot(qf, mk3(0.f, 0.f, 0.25f));
     K.pos[h] = pf; K.quat[h] = qf; K.axw[h] = l == 0 ? a0 : a1;
     if (DYN) {
@@ -564,6 +565,12 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   const bool dbg_all_lr = (A.max_contacts & 256) != 0;  // test hook: every contact through the low-rank path
   const int cap = mc_ > 0 && mc_ < NC ? mc_ : NC;
   const int ngh = ht.ngeom >> 1;
+  // _randomize_initial_hand_positions (piano_with_shadow_hands.py:491-499): one y shift of both hands per episode
+  float yoff = 0.f;
+  if (A.hand_off) {
+    if (do_reset) { yoff = A.hand_off_pending[env]; if (lane == 0) A.hand_off[env] = yoff; }
+    else yoff = A.hand_off[env];
+  }
 
   if (!do_reset) {
 #pragma unroll
@@ -603,7 +610,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       }
       // ---- mj_kinematics + RNE forward pass
       Kin K;
-      forward_kinematics<true>(ht, o, L, q, v, K);
+      forward_kinematics<true>(ht, o, L, q, v, yoff, K);
       f3 Sl[2];
 #pragma unroll
       for (int h = 0; h < 2; h++) {

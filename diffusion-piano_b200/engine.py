@@ -114,6 +114,10 @@ class BatchedPianoEngine:
     def set_qfrc_applied(self, qfrc, stream: int = 0):
         _lib.check(self.lib.pp_set_qfrc_applied(self._h, _ptr(qfrc), stream))
 
+    def set_hand_offsets(self, y_off, stream: int = 0):
+        """y shift [N] of both hands that each env takes at its next reset (None: zero again)."""
+        _lib.check(self.lib.pp_set_hand_offsets(self._h, _ptr(y_off), stream))
+
     def get_diag(self, qacc=None, actuator_force=None, actuator_velocity=None, site_xpos=None,
                  activation=None, counters=None, stream: int = 0):
         _lib.check(self.lib.pp_get_diag(self._h, _ptr(qacc), _ptr(actuator_force), _ptr(actuator_velocity),

@@ -20,7 +20,7 @@ from . import specs
 
 class BatchedEnvironment:
     def __init__(self, task, num_envs: int, device: int = 0, canonical_actions: bool = False,
-                 auto_reset: bool = True, max_contacts: int = 0):
+                 auto_reset: bool = True, max_contacts: int = 0, random_state=None):
         import torch  # device memory + streams only
 
         self._torch = torch
@@ -28,6 +28,7 @@ class BatchedEnvironment:
         self.num_envs = int(num_envs)
         cfg = task.engine_config(num_envs, device, canonical_actions)
         cfg.auto_reset = auto_reset
+        self._auto_reset = bool(auto_reset)
         cfg.max_contacts = max_contacts
         self.engine = BatchedPianoEngine(task.model, task.song, cfg)
         self.device = torch.device("cuda", device)
@@ -53,6 +54,29 @@ class BatchedEnvironment:
         self._h_discount = pinned((n,), torch.float32, 1)
         self._h_done = pinned((n,), torch.uint8)
         self._h_actions = pinned((n, self.action_dim), torch.float32)
+        # randomize_hand_positions (piano_with_shadow_hands.py:491-499): a uniform(-0.05, 0.05) y shift of
+        # both hands, drawn per env and per episode from the environment's RandomState
+        self._randomize = bool(getattr(task, "_randomize_hand_positions", False))
+        if self._randomize:
+            if isinstance(random_state, np.random.RandomState):
+                self.random_state = random_state
+            else:
+                self.random_state = np.random.RandomState(random_state)
+            self._h_offsets = pinned((n,), torch.float32)
+            self._d_offsets = torch.zeros(n, dtype=torch.float32, device=self.device)
+
+    _POSITION_OFFSET = 0.05
+
+    def _draw_hand_offsets(self):
+        """Offsets the envs take at their NEXT reset; redrawn before every call that can reset an env."""
+        if not self._randomize:
+            return
+        self._h_offsets[...] = self.random_state.uniform(-self._POSITION_OFFSET, self._POSITION_OFFSET,
+                                                         self.num_envs)
+        self._d_offsets.copy_(self._torch.from_numpy(self._h_offsets), non_blocking=True)
+        stream = self._torch.cuda.current_stream(self.device).cuda_stream
+        self.engine.set_hand_offsets(self._d_offsets, stream)
+        self._torch.cuda.current_stream(self.device).synchronize()
 
     # ---- specs
     def action_spec(self) -> specs.BoundedArray:
@@ -66,12 +90,15 @@ class BatchedEnvironment:
 
     # ---- device API: everything stays in HBM; returned tensors are reused between calls
     def reset_device(self, mask=None):
+        self._draw_hand_offsets()
         stream = self._torch.cuda.current_stream(self.device).cuda_stream
         self.engine.reset(obs=self._obs, mask=mask, stream=stream)
         return self._obs
 
     def step_device(self, actions):
         """actions: float32 CUDA tensor (N, action_dim). Returns (obs, reward, done, terms, discount)."""
+        if self._auto_reset:
+            self._draw_hand_offsets()
         stream = self._torch.cuda.current_stream(self.device).cuda_stream
         self.engine.step(actions, self._obs, self._reward, self._done, self._terms, self._discount, stream)
         return self._obs, self._reward, self._done, self._terms, self._discount
@@ -81,6 +108,7 @@ class BatchedEnvironment:
         return OrderedDict((k, flat[:, o:o + s].astype(np.float64)) for k, (o, s) in self.layout.items())
 
     def reset(self) -> Dict[str, np.ndarray]:
+        self._draw_hand_offsets()
         self.engine.reset_host(obs=self._h_obs)
         return self._split(self._h_obs)
 
@@ -89,6 +117,8 @@ class BatchedEnvironment:
         if a.shape != (self.num_envs, self.action_dim):
             raise ValueError(f"actions must have shape {(self.num_envs, self.action_dim)}, got {a.shape}")
         self._h_actions[...] = a  # float64 -> float32 into the page-locked buffer
+        if self._auto_reset:
+            self._draw_hand_offsets()
         self.engine.step_host(self._h_actions, self._h_obs, self._h_reward, self._h_done, self._h_terms,
                               self._h_discount)
         return self._split(self._h_obs), self._h_reward.astype(np.float64), self._h_done.astype(bool)
@@ -148,11 +178,11 @@ class Environment:
     def __init__(self, task, device: int = 0, canonical_actions: bool = False, random_state=None,
                  strip_singleton_obs_buffer_dim: bool = True, recompile_physics: bool = False,
                  legacy_step: bool = True):
-        del random_state, strip_singleton_obs_buffer_dim, recompile_physics
+        del strip_singleton_obs_buffer_dim, recompile_physics
         if not legacy_step:
             raise NotImplementedError("only dm_control's legacy_step=True ordering is implemented")
         self._b = BatchedEnvironment(task, 1, device=device, canonical_actions=canonical_actions,
-                                     auto_reset=False)
+                                     auto_reset=False, random_state=random_state)
         self.task = task
         self._reset_next_step = True
 

@@ -110,8 +110,7 @@ class PianoWithShadowHands(_PianoTaskBase):
         del primitive_fingertip_collisions
         if reduced_action_space or attachment_yaw != 0 or tuple(forearm_dofs) != ("forearm_tx", "forearm_ty"):
             raise NotImplementedError("only the default hand configuration is built (SURVEY §8f rank 4)")
-        if randomize_hand_positions:
-            raise NotImplementedError("randomize_hand_positions is not built yet (SURVEY §8f rank 4)")
+        self._randomize_hand_positions = bool(randomize_hand_positions)
         if n_seconds_lookahead is not None:
             n_steps_lookahead = int(np.ceil(n_seconds_lookahead / control_timestep))
         super().__init__(midi, n_steps_lookahead, trim_silence, physics_timestep, control_timestep,

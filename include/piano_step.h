@@ -100,6 +100,11 @@ int pp_set_state(pp_env *env, const float *qpos_dev, const float *qvel_dev, cons
 /* generalized force added to every substep (tests use it like physics.bind().qfrc_applied) */
 int pp_set_qfrc_applied(pp_env *env, const float *qfrc_dev, void *stream);
 
+/* randomize_hand_positions (piano_with_shadow_hands.py:491-499, Entity.shift_pose): y_off_dev [N] f32 is
+ * the world-y shift of BOTH hands that env i takes at its NEXT reset (the caller draws it, e.g.
+ * uniform(-0.05, 0.05)); it stays in force until the reset after. NULL: zero shift from the next reset on. */
+int pp_set_hand_offsets(pp_env *env, const float *y_off_dev, void *stream);
+
 /* diagnostics of the LAST substep of the last pp_step (device pointers, any may be NULL):
  * qacc [N,nv]; actuator_force [N,nu]; actuator_velocity [N,nu]; site_xpos [N,nsite,3];
  * activation [N,88] u8; counters [N,8] i32 = {ncon, nefc, newton iterations, dropped contacts} of the last substep, then

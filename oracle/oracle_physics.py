@@ -76,6 +76,10 @@ class OraclePhysics:
 
         self.model = model
         self._cm = to_ctypes(model)
+        # private copy of body_pos: Entity.shift_pose (randomize_hand_positions) edits it per environment
+        self._body_pos0 = np.array(model.a["body_pos"], np.float64, copy=True)
+        self._body_pos = self._body_pos0.copy()
+        self._cm.body_pos = self._body_pos.ctypes.data_as(type(self._cm.body_pos))
         self._mp = ctypes.cast(ctypes.pointer(self._cm), ctypes.c_void_p)
         self._d = lib().po_data_create(self._mp)
         d = self._d.contents
@@ -98,6 +102,13 @@ class OraclePhysics:
 
     def reset(self):
         lib().po_reset(self._mp, self._d)
+
+    def shift_hands(self, y_offset: float):
+        """World-y shift of both hand root bodies relative to the compiled model (0 restores it)."""
+        names = self.model.names["body"]
+        for i, n in enumerate(names):
+            if n.endswith("_forearm"):
+                self._body_pos[i, 1] = self._body_pos0[i, 1] + float(y_offset)
 
     def step(self, nsub: int = 1):
         for _ in range(nsub):

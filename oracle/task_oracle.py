@@ -118,8 +118,11 @@ class PianoWithShadowHandsOracle(_Base):
         self.lh_forearm = set(np.flatnonzero(cls == 5))
         self.reset()
 
-    def reset(self):
+    def reset(self, hand_offset: float = 0.0):
+        """hand_offset: the y shift _randomize_initial_hand_positions would draw for this episode
+        (piano_with_shadow_hands.py:491-499); the caller supplies the draw."""
         p = self.physics
+        p.shift_hands(hand_offset)
         p.reset()
         p.forward_position(True)
         self.t_idx = 0

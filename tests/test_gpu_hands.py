@@ -240,3 +240,48 @@ def test_ot_fingering_reward_unfingered_midi(cuda_lib, song):
             break
     assert len(set(np.round(seen, 6))) > 1  # the term moves with the hands
     s.close()
+
+
+def test_randomize_hand_positions(cuda_lib):
+    """reference piano_with_shadow_hands.py:491-499: a uniform(-0.05, 0.05) y shift of both hands per
+    episode. The façade draws it from its RandomState; the kernel applies the pending shift at the env's
+    reset and keeps it for the episode. Checked against the oracle with the same shift."""
+    import torch
+    from diffusion_piano_b200 import suite
+    from oracle.task_oracle import PianoWithShadowHandsOracle
+    task = _task(randomize_hand_positions=True)
+    n = 4
+    env = suite.BatchedEnvironment(task, n, canonical_actions=False, auto_reset=False, random_state=3)
+    expect = np.random.RandomState(3).uniform(-0.05, 0.05, n).astype(np.float32)
+    env.reset()
+    sx = torch.zeros((n, 10, 3), device="cuda")
+    env.engine.get_diag(site_xpos=sx)
+    torch.cuda.synchronize()
+    sx0 = sx.cpu().numpy()
+    ora = PianoWithShadowHandsOracle(task)
+    for i in range(n):
+        ora.reset(float(expect[i]))
+        np.testing.assert_allclose(sx0[i], ora.physics.site_xpos, atol=2e-6)
+    assert np.ptp(sx0[:, 0, 1]) > 1e-3 and np.abs(expect).max() <= 0.05
+    # a few steps of env 2 against the oracle with that env's shift (free running)
+    ora.reset(float(expect[2]))
+    rng = np.random.RandomState(0)
+    for t in range(4):
+        a = _spec_random(ora, rng)
+        a[:44] = ora.act_lo + (0.4 + 0.2 * rng.uniform(0, 1, 44)) * (ora.act_hi - ora.act_lo)
+        obs, rew, done = env.step(np.stack([a] * n))
+        obs_o, r_o, _ = ora.step(np.asarray(a, np.float32).astype(np.float64))
+        np.testing.assert_allclose(obs["rh_shadow_hand/joints_pos"][2], obs_o["rh_shadow_hand/joints_pos"], atol=2e-4)
+        np.testing.assert_allclose(rew[2], r_o, atol=5e-3)
+    assert np.ptp(rew) > 0  # different shifts, different fingering distances
+    # a second reset draws new shifts; NULL offsets restore the model's own pose at the next reset
+    env.reset()
+    env.engine.get_diag(site_xpos=sx); torch.cuda.synchronize()
+    assert np.abs(sx.cpu().numpy() - sx0).max() > 1e-4
+    env.engine.set_hand_offsets(None)
+    env.engine.reset()
+    env.engine.get_diag(site_xpos=sx); torch.cuda.synchronize()
+    ora.reset(0.0)
+    for i in range(n):
+        np.testing.assert_allclose(sx.cpu().numpy()[i], ora.physics.site_xpos, atol=2e-6)
+    env.close()
