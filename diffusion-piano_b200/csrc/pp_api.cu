@@ -33,6 +33,8 @@ struct pp_env {
   float *qpos = nullptr, *qvel = nullptr, *warm = nullptr, *sustain = nullptr, *qfrc_applied = nullptr;
   float *hand_off = nullptr, *hand_off_pending = nullptr;  // per-env y shift of both hands (active / drawn for the next reset)
   bool use_hand_off = false;
+  float *eval_sum = nullptr, *eval_episode = nullptr;  // musical metrics (MidiEvaluationWrapper)
+  int *eval_steps = nullptr, *eval_count = nullptr;
   int* t_idx = nullptr;
   uint8_t* needs_reset = nullptr;
   float *qacc = nullptr, *act_force = nullptr, *act_vel = nullptr, *site_xpos = nullptr;
@@ -299,6 +301,8 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(dalloc(&e->qfrc_applied, N * nv)); CUDA_OK(dalloc(&e->qacc, N * nv));
   CUDA_OK(dalloc(&e->sustain, N)); CUDA_OK(dalloc(&e->t_idx, N)); CUDA_OK(dalloc(&e->needs_reset, N));
   CUDA_OK(dalloc(&e->hand_off, N)); CUDA_OK(dalloc(&e->hand_off_pending, N));
+  CUDA_OK(dalloc(&e->eval_sum, N * 6)); CUDA_OK(dalloc(&e->eval_episode, N * 6));
+  CUDA_OK(dalloc(&e->eval_steps, N)); CUDA_OK(dalloc(&e->eval_count, N));
   CUDA_OK(dalloc(&e->act_force, (size_t)N * (e->nu ? e->nu : 1)));
   CUDA_OK(dalloc(&e->act_vel, (size_t)N * (e->nu ? e->nu : 1)));
   CUDA_OK(dalloc(&e->site_xpos, (size_t)N * 3 * PP_NSITE));
@@ -331,7 +335,8 @@ extern "C" int pp_destroy(pp_env* e) {
   void* dev[] = {e->dm, e->goal, e->pairs, e->qpos, e->qvel, e->warm, e->sustain, e->qfrc_applied, e->t_idx,
                  e->needs_reset, e->qacc, e->act_force, e->act_vel, e->site_xpos, e->activation, e->counters,
                  e->act_min_d, e->act_max_d, e->d_actions, e->d_obs, e->d_reward, e->d_terms, e->d_discount,
-                 e->d_done, e->d_mask, e->hand_off, e->hand_off_pending};
+                 e->d_done, e->d_mask, e->hand_off, e->hand_off_pending, e->eval_sum, e->eval_episode,
+                 e->eval_steps, e->eval_count};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -369,6 +374,7 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     A.qpos = e->qpos; A.qvel = e->qvel; A.t_idx = e->t_idx; A.sustain = e->sustain;
     A.needs_reset = e->needs_reset; A.obs = obs; A.reward = reward; A.reward_terms = terms;
     A.discount = discount; A.done = done; A.qacc = e->qacc; A.activation = e->activation;
+    A.eval = EvalAccum{e->eval_sum, e->eval_steps, e->eval_episode, e->eval_count};
     pp_launch_piano_only(A, s);
   } else {
     HandsArgs A;
@@ -388,6 +394,7 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     A.discount = discount; A.done = done; A.qacc = e->qacc; A.act_force = e->act_force;
     A.act_vel = e->act_vel; A.site_xpos = e->site_xpos; A.activation = e->activation;
     A.counters = e->counters;
+    A.eval = EvalAccum{e->eval_sum, e->eval_steps, e->eval_episode, e->eval_count};
     e->launches += pp_launch_hands(A, s) - 1;
   }
   e->launches++;
@@ -493,6 +500,15 @@ extern "C" int pp_set_qfrc_applied(pp_env* e, const float* qfrc, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   e->use_applied = qfrc != nullptr;
   if (qfrc) COPY_IF(e->qfrc_applied, qfrc, (size_t)e->cfg.num_envs * e->nv * 4);
+  return PP_OK;
+}
+
+extern "C" int pp_get_metrics(pp_env* e, float* episode_metrics, int32_t* episode_count, void* stream) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t N = e->cfg.num_envs;
+  COPY_IF(episode_metrics, e->eval_episode, N * 6 * 4);
+  COPY_IF(episode_count, e->eval_count, N * 4);
   return PP_OK;
 }
 

@@ -158,3 +158,51 @@ __device__ __forceinline__ float pp_tolerance(float x, float hi, float margin) {
   float t = d * scale;
   return expf(-0.5f * t * t);
 }
+
+// ------------------------------------------------------------------ musical metrics
+// MidiEvaluationWrapper (reference wrappers/evaluation.py:67-177): every step, precision / recall / F1
+// (sklearn precision_recall_fscore_support, average="binary", zero_division=1) of the 88 key
+// activations against the frame's notes, and of the sustain activation against the frame's pedal; the
+// episode's metrics are the means over its steps. Per env: running sums [6] = key P, R, F1, sustain P,
+// R, F1; the finished episode's means; a count of finished episodes.
+struct EvalAccum {
+  float* sum;      // [N,6] running sums of the current episode
+  int* steps;      // [N]
+  float* episode;  // [N,6] means of the last finished episode
+  int* count;      // [N] finished episodes
+};
+__device__ __forceinline__ float pp_prf_div(int num, int den) { return den > 0 ? (float)num / (float)den : 1.f; }
+__device__ __forceinline__ void pp_eval_metrics(const EvalAccum& E, int env, int lane, const bool act[3],
+                                                const uint8_t* goal_cur, bool sustain_on, bool do_reset, bool done) {
+  if (!E.sum) return;
+  if (do_reset) {
+    if (lane < 6) E.sum[(size_t)env * 6 + lane] = 0.f;
+    if (lane == 0) E.steps[env] = 0;
+    return;
+  }
+  int tp = 0, fp = 0, fn = 0;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const int k = lane + 32 * i;
+    const unsigned ba = __ballot_sync(0xffffffffu, k < PP_NKEY && act[i]);
+    const unsigned bg = __ballot_sync(0xffffffffu, k < PP_NKEY && goal_cur[k] != 0);
+    tp += __popc(ba & bg); fp += __popc(ba & ~bg); fn += __popc(~ba & bg);
+  }
+  const bool st = goal_cur[88] != 0;
+  const int stp = (sustain_on && st) ? 1 : 0, sfp = (sustain_on && !st) ? 1 : 0, sfn = (!sustain_on && st) ? 1 : 0;
+  float v = 0.f;
+  if (lane == 0) v = pp_prf_div(tp, tp + fp);
+  else if (lane == 1) v = pp_prf_div(tp, tp + fn);
+  else if (lane == 2) v = pp_prf_div(2 * tp, 2 * tp + fp + fn);
+  else if (lane == 3) v = pp_prf_div(stp, stp + sfp);
+  else if (lane == 4) v = pp_prf_div(stp, stp + sfn);
+  else if (lane == 5) v = pp_prf_div(2 * stp, 2 * stp + sfp + sfn);
+  const int n = E.steps[env] + 1;
+  __syncwarp();
+  if (lane < 6) {
+    const float s = E.sum[(size_t)env * 6 + lane] + v;
+    E.sum[(size_t)env * 6 + lane] = s;
+    if (done) E.episode[(size_t)env * 6 + lane] = s / (float)n;
+  }
+  if (lane == 0) { E.steps[env] = n; if (done) E.count[env] += 1; }
+}

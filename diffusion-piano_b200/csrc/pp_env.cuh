@@ -21,6 +21,7 @@ struct PianoOnlyArgs {
   uint8_t* done;
   float* qacc;                // diag [N,88] or null
   uint8_t* activation;        // diag [N,88] or null
+  EvalAccum eval;             // musical metrics accumulators
 };
 
 struct HandsArgs {
@@ -49,6 +50,7 @@ struct HandsArgs {
   float *qacc, *act_force, *act_vel, *site_xpos;
   uint8_t* activation;
   int* counters;  // [N,8]
+  EvalAccum eval;  // musical metrics accumulators
 };
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);

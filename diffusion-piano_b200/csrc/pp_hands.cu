@@ -1739,6 +1739,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   float discount = 1.f;
   if (!do_reset && A.wrong_press_termination && failure && !should_terminate) { done = true; discount = 0.f; }
 
+  pp_eval_metrics(A.eval, env, lane, active, goal_cur, sustain_on, do_reset, done);
   // ---- write back state
 #pragma unroll
   for (int h = 0; h < 2; h++)

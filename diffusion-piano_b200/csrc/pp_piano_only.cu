@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(128) pp_piano_only_step_kernel(PianoOnlyArgs A
     }
   }
   const bool done = !do_reset && t_idx == T;
+  pp_eval_metrics(A.eval, env, lane, act_on, goal_cur, sustain_on, do_reset, done);
   if (lane == 0) {
     A.t_idx[env] = t_idx;
     A.sustain[env] = sustain;

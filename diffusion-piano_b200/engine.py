@@ -118,6 +118,10 @@ class BatchedPianoEngine:
         """y shift [N] of both hands that each env takes at its next reset (None: zero again)."""
         _lib.check(self.lib.pp_set_hand_offsets(self._h, _ptr(y_off), stream))
 
+    def get_metrics(self, episode_metrics=None, episode_count=None, stream: int = 0):
+        """Musical metrics of every env's last finished episode: [N,6] f32, and [N] i32 episode counts."""
+        _lib.check(self.lib.pp_get_metrics(self._h, _ptr(episode_metrics), _ptr(episode_count), stream))
+
     def get_diag(self, qacc=None, actuator_force=None, actuator_velocity=None, site_xpos=None,
                  activation=None, counters=None, stream: int = 0):
         _lib.check(self.lib.pp_get_diag(self._h, _ptr(qacc), _ptr(actuator_force), _ptr(actuator_velocity),

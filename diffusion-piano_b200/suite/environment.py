@@ -130,6 +130,27 @@ class BatchedEnvironment:
                 "ot_fingering_reward": 3, "forearm_reward": 4}
         return OrderedDict((n, self._h_terms[:, cols[n]].astype(np.float64)) for n in self.task.reward_names)
 
+    # ---- musical metrics (wrappers/evaluation.py:67-177), accumulated by the step on the device
+    def episode_metrics(self):
+        """(metrics [N,6] float64, episodes [N] int): means over the steps of each env's last finished
+        episode {precision, recall, f1, sustain_precision, sustain_recall, sustain_f1} and the number of
+        episodes the env has finished."""
+        torch = self._torch
+        m = torch.zeros((self.num_envs, 6), dtype=torch.float32, device=self.device)
+        c = torch.zeros(self.num_envs, dtype=torch.int32, device=self.device)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        self.engine.get_metrics(m, c, stream)
+        return m.cpu().numpy().astype(np.float64), c.cpu().numpy()
+
+    def get_musical_metrics(self) -> Dict[str, float]:
+        """Batched counterpart of MidiEvaluationWrapper.get_musical_metrics: mean over the envs' last
+        finished episodes."""
+        m, c = self.episode_metrics()
+        if not (c > 0).any():
+            raise ValueError("No episode metrics available yet.")
+        names = ("precision", "recall", "f1", "sustain_precision", "sustain_recall", "sustain_f1")
+        return {n: float(m[c > 0, j].mean()) for j, n in enumerate(names)}
+
     def close(self):
         self.engine.close()
 

@@ -100,6 +100,13 @@ int pp_set_state(pp_env *env, const float *qpos_dev, const float *qvel_dev, cons
 /* generalized force added to every substep (tests use it like physics.bind().qfrc_applied) */
 int pp_set_qfrc_applied(pp_env *env, const float *qfrc_dev, void *stream);
 
+/* MidiEvaluationWrapper (wrappers/evaluation.py:67-177): the step accumulates, per env, the per-step
+ * precision / recall / F1 (sklearn binary, zero_division=1) of key activations against the frame's notes
+ * and of the sustain activation against the pedal. episode_metrics_dev [N,6] f32 = means over the steps of
+ * the env's LAST FINISHED episode {key P, R, F1, sustain P, R, F1}; episode_count_dev [N] i32 = finished
+ * episodes since pp_create. Either pointer may be NULL. */
+int pp_get_metrics(pp_env *env, float *episode_metrics_dev, int32_t *episode_count_dev, void *stream);
+
 /* randomize_hand_positions (piano_with_shadow_hands.py:491-499, Entity.shift_pose): y_off_dev [N] f32 is
  * the world-y shift of BOTH hands that env i takes at its NEXT reset (the caller draws it, e.g.
  * uniform(-0.05, 0.05)); it stays in force until the reset after. NULL: zero shift from the next reset on. */
