@@ -43,6 +43,7 @@ struct HandsArgs {
   int* t_idx;
   float* sustain;
   uint8_t* needs_reset;
+  unsigned* stick_bits;  // [N,2] per hand: dofs whose frictionloss row ended the last solve in its quadratic zone
   float* obs;
   float *reward, *reward_terms, *discount;
   uint8_t* done;

@@ -720,6 +720,25 @@ static void solve_newton(const pp_model *m, po_data *d, efc_t *e) {
   double cw = total_cost(m, d, e, d->qacc_warmstart, NULL, NULL, NULL);
   double cs = total_cost(m, d, e, d->qacc_smooth, NULL, NULL, NULL);
   memcpy(a, cw < cs ? d->qacc_warmstart : d->qacc_smooth, sizeof(double) * nv);
+  /* experiment (PO_WARM_STICK): dofs whose frictionloss row was in its quadratic zone at the previous
+   * solution start at the row's new reference acceleration */
+  static int warm_stick = -1;
+  static unsigned char stick_prev[512];
+  if (warm_stick < 0) { warm_stick = getenv("PO_WARM_STICK") ? atoi(getenv("PO_WARM_STICK")) : 0; memset(stick_prev, 0, sizeof(stick_prev)); }
+  if (warm_stick) {
+    double *t = (double *)malloc(sizeof(double) * nv);
+    memcpy(t, a, sizeof(double) * nv);
+    for (int r = 0; r < ne; r++) {
+      if (e->type[r] != ROW_FRICTION) continue;
+      int j = -1;
+      for (int k = 0; k < nv; k++) if (e->J[(size_t)r * nv + k] != 0) { j = k; break; }
+      if (j >= 0 && stick_prev[j]) t[j] = e->aref[r];
+    }
+    double ct = total_cost(m, d, e, t, NULL, NULL, NULL);
+    double c0 = cw < cs ? cw : cs;
+    if (warm_stick == 2 || ct < c0) memcpy(a, t, sizeof(double) * nv);
+    free(t);
+  }
   d->solver_iter = 0;
   if (ne == 0) { memcpy(a, d->qacc_smooth, sizeof(double) * nv); memset(d->qfrc_constraint, 0, sizeof(double) * nv); return; }
   double *grad = (double *)malloc(sizeof(double) * nv), *p = (double *)malloc(sizeof(double) * nv);
@@ -809,6 +828,13 @@ static void solve_newton(const pp_model *m, po_data *d, efc_t *e) {
     if (improvement < m->tolerance || gnorm < m->tolerance) break;
   }
   d->solver_cost = cost;
+  if (warm_stick) {
+    memset(stick_prev, 0, sizeof(stick_prev));
+    for (int r = 0; r < ne; r++) {
+      if (e->type[r] != ROW_FRICTION) continue;
+      for (int k = 0; k < nv; k++) if (e->J[(size_t)r * nv + k] != 0) { stick_prev[k] = curv[r] != 0; break; }
+    }
+  }
   memset(d->qfrc_constraint, 0, sizeof(double) * nv);
   for (int r = 0; r < ne; r++)
     for (int j = 0; j < nv; j++) d->qfrc_constraint[j] += e->J[(size_t)r * nv + j] * force[r];
