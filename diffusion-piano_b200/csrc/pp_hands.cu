@@ -51,6 +51,7 @@ struct __align__(16) WarpShared {
       float raw[52][16];   // body spatial inertia (10) + RNE force (6)
       float comp[10][16];  // composite sums of the finger chains
       float c_geo[7][NC];  // contact pos, normal, dist
+      float gpos[PP_MAXGEOM][3], gaxis[PP_MAXGEOM][3];  // world centre and axis of every hand collider
     } k;
     struct {
       union {
@@ -777,6 +778,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
             gc[h] = ld3(W.a.k.xpos[g]) + qrot(qq, ld3(ht.geom_pos[h * ngh + lane]));
             gax[h] = qrot(qq, mk3(0, 0, 1));
             ylo[h] = gc[h].y - gr - ghl; yhi[h] = gc[h].y + gr + ghl;
+            st3(W.a.k.gpos[h * ngh + lane], gc[h]); st3(W.a.k.gaxis[h * ngh + lane], gax[h]);
           }
         }
         // -- finger colliders against the keys under them and the base
@@ -797,13 +799,37 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) tmax = max(tmax, __shfl_xor_sync(FULL, tmax, off));
         const float margin_p = o.pair_margin[PP_PAIRCLS_PIANO];
+        // candidate t of the lane's collider: whites i_lo.., the black key on every boundary, the base
+        auto candidate = [&](int h, int t) -> int {
+          if (t < nW[h]) return kt.white_key[i_lo[h] + t];
+          if (t < 2 * nW[h] + 1) return kt.boundary_black[i_lo[h] + t - nW[h]];
+          return (t == 2 * nW[h] + 1 && ntot[h] > 0) ? PP_NKEY : -1;
+        };
+        // conservative cull: bounding sphere of the collider against a box that contains the key at every
+        // angle of its range (the far end sinks by <= 2 hx sin(q_max) < 16 mm); the exact test only runs for
+        // the survivors, compacted so that the warp iterates max-survivors-per-lane times
+        unsigned surv[2] = {0u, 0u};
+        const float Rc = Rb + fmaxf(margin_p, 0.f) + 1e-4f;
         for (int t = 0; t < tmax; t++) {
 #pragma unroll
           for (int h = 0; h < 2; h++) {
+            const int key = candidate(h, t);
+            if (key < 0) continue;
+            f3 bp, bh;
+            if (key < PP_NKEY) {
+              bp = ld3(kt.pos[key]); bh = ld3(kt.half[key]);
+              bp.z -= 0.007f; bh.z += 0.010f; bh.x += 0.002f;
+            } else { bp = ld3(o.base_pos); bh = ld3(o.base_half); }
+            const float dx = fmaxf(fabsf(gc[h].x - bp.x) - bh.x, 0.f), dy = fmaxf(fabsf(gc[h].y - bp.y) - bh.y, 0.f);
+            const float dz = fmaxf(fabsf(gc[h].z - bp.z) - bh.z, 0.f);
+            if (dx * dx + dy * dy + dz * dz < Rc * Rc) surv[h] |= 1u << t;
+          }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          while (__any_sync(FULL, surv[h] != 0u)) {
             int key = -1;
-            if (t < nW[h]) key = kt.white_key[i_lo[h] + t];
-            else if (t < 2 * nW[h] + 1) key = kt.boundary_black[i_lo[h] + t - nW[h]];
-            else if (t == 2 * nW[h] + 1 && ntot[h] > 0) key = PP_NKEY;
+            if (surv[h]) { const int t = __ffs(surv[h]) - 1; surv[h] &= surv[h] - 1u; key = candidate(h, t); }
             Hit h0, h1; h0.ok = false; h1.ok = false;
             if (key >= 0) {
               Box b;
@@ -816,7 +842,6 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
               } else {
                 b.p = ld3(o.base_pos); b.cq = 1.f; b.sq = 0.f; b.h = ld3(o.base_half);
               }
-              // the oracle's bounding-sphere cull is implied by the exact test (margin 0)
               capsule_box(gc[h], gax[h], gr, ghl, b, margin_p, h0, h1);
             }
             const int ids = h | (gnode << 1) | (0 << 6) | (key << 8);
@@ -833,6 +858,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         }
         const bool apart = ymin0 > ymax1 || ymin1 > ymax0;
         const int np = apart ? ht.npair_same : ht.npair;
+        __syncwarp();  // gpos / gaxis of every collider are in shared memory
         const float margin_h = o.pair_margin[PP_PAIRCLS_HAND];
         for (int p0 = 0; p0 < np; p0 += 32) {
           const int p = p0 + lane;
@@ -841,14 +867,10 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
             const int g1 = ht.pair_g1[p], g2 = ht.pair_g2[p];
             const int h1 = g1 >= ngh ? 1 : 0, h2 = g2 >= ngh ? 1 : 0;
             const int n1 = ht.geom_body[g1] - h1 * PP_HB + 1, n2 = ht.geom_body[g2] - h2 * PP_HB + 1;
-            const int a1 = h1 * 26 + n1, a2 = h2 * 26 + n2;
-            f4 q1; q1.w = W.a.k.xquat[a1][0]; q1.x = W.a.k.xquat[a1][1]; q1.y = W.a.k.xquat[a1][2]; q1.z = W.a.k.xquat[a1][3];
-            f4 q2; q2.w = W.a.k.xquat[a2][0]; q2.x = W.a.k.xquat[a2][1]; q2.y = W.a.k.xquat[a2][2]; q2.z = W.a.k.xquat[a2][3];
-            const f3 c1 = ld3(W.a.k.xpos[a1]) + qrot(q1, ld3(ht.geom_pos[g1]));
-            const f3 c2 = ld3(W.a.k.xpos[a2]) + qrot(q2, ld3(ht.geom_pos[g2]));
+            const f3 c1 = ld3(W.a.k.gpos[g1]), c2 = ld3(W.a.k.gpos[g2]);
             const float r1 = ht.geom_r[g1], r2 = ht.geom_r[g2], l1 = ht.geom_hl[g1], l2 = ht.geom_hl[g2];
             if (norm(c1 - c2) <= r1 + l1 + r2 + l2 + margin_h)
-              hh = capsule_capsule(c1, qrot(q1, mk3(0, 0, 1)), r1, l1, c2, qrot(q2, mk3(0, 0, 1)), r2, l2, margin_h);
+              hh = capsule_capsule(c1, ld3(W.a.k.gaxis[g1]), r1, l1, c2, ld3(W.a.k.gaxis[g2]), r2, l2, margin_h);
             ids = h1 | (n1 << 1) | (1 << 6) | ((h2 | (n2 << 1)) << 8);
           }
           push_contact(W, hh.ok, ncon, ndrop, cap, hh, ids);
