@@ -860,17 +860,28 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         const int np = apart ? ht.npair_same : ht.npair;
         __syncwarp();  // gpos / gaxis of every collider are in shared memory
         const float margin_h = o.pair_margin[PP_PAIRCLS_HAND];
-        for (int p0 = 0; p0 < np; p0 += 32) {
-          const int p = p0 + lane;
-          Hit hh; hh.ok = false; int ids = 0;
+        // bounding-sphere pass over the lane's pairs (p = lane + 32 i), then the exact capsule-capsule test
+        // on the survivors only, compacted: the warp iterates max-survivors-per-lane times
+        unsigned near = 0u;
+        for (int i = 0; i * 32 < np; i++) {
+          const int p = i * 32 + lane;
           if (p < np) {
+            const int g1 = ht.pair_g1[p], g2 = ht.pair_g2[p];
+            const f3 dc = ld3(W.a.k.gpos[g1]) - ld3(W.a.k.gpos[g2]);
+            const float reach = ht.geom_r[g1] + ht.geom_hl[g1] + ht.geom_r[g2] + ht.geom_hl[g2] + margin_h;
+            if (dot(dc, dc) <= reach * reach) near |= 1u << i;
+          }
+        }
+        while (__any_sync(FULL, near != 0u)) {
+          Hit hh; hh.ok = false; int ids = 0;
+          if (near) {
+            const int i = __ffs(near) - 1; near &= near - 1u;
+            const int p = i * 32 + lane;
             const int g1 = ht.pair_g1[p], g2 = ht.pair_g2[p];
             const int h1 = g1 >= ngh ? 1 : 0, h2 = g2 >= ngh ? 1 : 0;
             const int n1 = ht.geom_body[g1] - h1 * PP_HB + 1, n2 = ht.geom_body[g2] - h2 * PP_HB + 1;
-            const f3 c1 = ld3(W.a.k.gpos[g1]), c2 = ld3(W.a.k.gpos[g2]);
-            const float r1 = ht.geom_r[g1], r2 = ht.geom_r[g2], l1 = ht.geom_hl[g1], l2 = ht.geom_hl[g2];
-            if (norm(c1 - c2) <= r1 + l1 + r2 + l2 + margin_h)
-              hh = capsule_capsule(c1, ld3(W.a.k.gaxis[g1]), r1, l1, c2, ld3(W.a.k.gaxis[g2]), r2, l2, margin_h);
+            hh = capsule_capsule(ld3(W.a.k.gpos[g1]), ld3(W.a.k.gaxis[g1]), ht.geom_r[g1], ht.geom_hl[g1],
+                                 ld3(W.a.k.gpos[g2]), ld3(W.a.k.gaxis[g2]), ht.geom_r[g2], ht.geom_hl[g2], margin_h);
             ids = h1 | (n1 << 1) | (1 << 6) | ((h2 | (n2 << 1)) << 8);
           }
           push_contact(W, hh.ok, ncon, ndrop, cap, hh, ids);
