@@ -76,6 +76,7 @@ struct __align__(16) WarpShared {
   int8_t slot_hand[KS];
   float Mt[52][9];        // M(ancestor j of dof, dof): j < 4 root dofs 0..3, j >= 4 the dof's chain
   float va[52 + KS];      // vector exchange (acceleration / velocity / search direction)
+  float dg[52];           // diagonal added to M when the fronts are loaded (row curvatures; Euler: h * damping)
   // contacts, SoA over the contact index
   float c_u[NE * 3][NC];  // per entry: (n, t1, t2) . jacobian column
   uint8_t c_col[NE][NC];  // column of the entry: hand dof 0..51 or 52+slot
@@ -1069,6 +1070,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       for (int h = 0; h < 2; h++) a[h] = (stick[h] && floss[h] > 0.f) ? faref[h] : acc[h];
       float Ma[2] = {0.f, 0.f}, sMa = 0.f;
       float jar[4] = {0.f, 0.f, 0.f, 0.f};
+      float cco[4] = {0.f, 0.f, 0.f, 0.f}, sco = 0.f;  // row curvatures H_t was last assembled with
       const bool con_on = lane < ncon && my_slot != -2;
       // front lane identity: lane = replica*16 + hand*8 + chain
       const int frep = lane >> 4, fh = (lane >> 3) & 1, fc = lane & 7;
@@ -1095,8 +1097,8 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
           out[h] = s;
         }
       };
-      // H_t <- M (+ hdamp * damping on the diagonal): tree entries only
-      auto build_M = [&](float hdamp) {
+      // H_t <- M: tree entries only (the diagonal rows are added when the fronts are loaded)
+      auto build_M = [&]() {
         if (L.dof) {
 #pragma unroll
           for (int h = 0; h < 2; h++) {
@@ -1104,13 +1106,12 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
             for (int j = 0; j < 9; j++) {
               const int an = j < 4 ? j : L.ni.cs + j - 4;
               const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
-              if (valid) Ht[h * 26 + lane][j] = Mr[h][j] + (an == lane ? hdamp * damp[h] : 0.f);
+              if (valid) Ht[h * 26 + lane][j] = Mr[h][j];
             }
           }
         }
         __syncwarp();
       };
-      build_M(0.f);
       // Ma at the warm start
 #pragma unroll
       for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = a[h];
@@ -1250,13 +1251,26 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
           __syncwarp();
         } else {
         // ---- H_t: M + diagonal rows + in-front contact cliques (Euler: M + h diag(b))
-        if (iter > 0 || euler) build_M(euler ? o.h : 0.f);
-        float shss = sM + sc;  // H(slot, slot), lane < nslot
-        if (!euler) {
-          if (L.dof) {
+        // diagonal of the dof rows (Euler: h * damping), added to M when the fronts are loaded
+        if (L.dof) {
 #pragma unroll
-            for (int h = 0; h < 2; h++) Ht[h * 26 + lane][posl] += fc_[h] + lc[h];
-          }
+          for (int h = 0; h < 2; h++) W.dg[h * 26 + lane] = euler ? o.h * damp[h] : fc_[h] + lc[h];
+        }
+        // H_t without that diagonal (M + cliques of the in-front contacts - Schur complements of the key
+        // slots) only changes when an in-front contact row or a slot's limit row changes zone: kept otherwise
+        bool redo = false;
+        if (!euler) {
+          bool chg = iter == 0;
+          if (con_on && !my_lr) chg |= cc[0] != cco[0] || cc[1] != cco[1] || cc[2] != cco[2] || cc[3] != cco[3];
+          if (lane < nslot) chg |= sc != sco;
+          redo = __any_sync(FULL, chg);
+#pragma unroll
+          for (int k = 0; k < 4; k++) cco[k] = cc[k];
+          sco = sc;
+        }
+        float shss = sM + sc;  // H(slot, slot), lane < nslot
+        if (redo) {
+          build_M();
           for (int s = 0; s < nslot; s++) {
             if (lane < 9) W.a.s.Kc[s][lane] = 0.f;
           }
@@ -1310,16 +1324,18 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         // deepest first (a 4-dof chain is padded with an identity pivot), 5..8 = root dofs 3,2,1,0.
         float F[45], Rt[10];
         {
+          const float (*Hs)[9] = euler ? W.Mt : Ht;  // Euler: M + h diag(b), no constraint rows
+          __syncwarp();
 #pragma unroll
           for (int i = 0; i < 9; i++) {
 #pragma unroll
             for (int j = 0; j <= i; j++) {
               float val = 0.f;
               if (i < 5) {
-                if (fvalid && i < fn) val = Ht[fg0 + fce - j][4 + (fce - i) - fcs];
+                if (fvalid && i < fn) val = Hs[fg0 + fce - j][4 + (fce - i) - fcs] + (i == j ? W.dg[fg0 + fce - i] : 0.f);
                 else val = i == j ? 1.f : 0.f;
               } else if (j < 5) {
-                if (fvalid && j < fn) val = Ht[fg0 + fce - j][8 - i];
+                if (fvalid && j < fn) val = Hs[fg0 + fce - j][8 - i];
               }
               F[i * (i + 1) / 2 + j] = val;
             }
@@ -1327,7 +1343,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
 #pragma unroll
           for (int i = 0; i < 4; i++)
 #pragma unroll
-            for (int j = 0; j <= i; j++) Rt[i * (i + 1) / 2 + j] = Ht[fg0 + 3 - j][3 - i];
+            for (int j = 0; j <= i; j++) Rt[i * (i + 1) / 2 + j] = Hs[fg0 + 3 - j][3 - i] + (i == j ? W.dg[fg0 + 3 - i] : 0.f);
           // eliminate the 5 chain pivots
 #pragma unroll
           for (int k = 0; k < 5; k++) {
