@@ -705,7 +705,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       }
       __syncwarp();  // u.dyn is dead from here on (H aliases it)
       // ---- CRBA row (ancestors of the dof) and RNE bias
-      float Mr[2][9], bias[2];
+      float bias[2];  // M(ancestor j, dof) goes to shared memory (Mt) only: 18 registers less through the solver
 #pragma unroll
       for (int h = 0; h < 2; h++) {
         const float* cI = comp[h];
@@ -726,7 +726,6 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
             mv = Sa[0] * Fn.x + Sa[1] * Fn.y + Sa[2] * Fn.z + Sa[3] * Ff.x + Sa[4] * Ff.y + Sa[5] * Ff.z;
             if (a == lane) mv += ht.armature[h * PP_HD + l];
           }
-          Mr[h][j] = mv;
           if (L.dof) W.Mt[h * 26 + lane][j] = mv;
         }
       }
@@ -1090,7 +1089,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
             for (int j = 0; j < 9; j++) {
               const int an = j < 4 ? j : L.ni.cs + j - 4;
               const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
-              if (valid) s += Mr[h][j] * W.va[h * 26 + an];
+              if (valid) s += W.Mt[h * 26 + lane][j] * W.va[h * 26 + an];
             }
             for (int d = lane + 1; d < lane + L.ni.nsub; d++) s += W.Mt[h * 26 + d][posl] * W.va[h * 26 + d];
           }
@@ -1106,7 +1105,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
             for (int j = 0; j < 9; j++) {
               const int an = j < 4 ? j : L.ni.cs + j - 4;
               const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
-              if (valid) Ht[h * 26 + lane][j] = Mr[h][j];
+              if (valid) Ht[h * 26 + lane][j] = W.Mt[h * 26 + lane][j];
             }
           }
         }
@@ -1181,7 +1180,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
               for (int j = 0; j < 9; j++) {
                 const int an = j < 4 ? j : L.ni.cs + j - 4;
                 const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
-                if (valid) Hd[hidx(h * 26 + an, h * 26 + lane)] = Mr[h][j] + (an == lane ? fc_[h] + lc[h] : 0.f);
+                if (valid) Hd[hidx(h * 26 + an, h * 26 + lane)] = W.Mt[h * 26 + lane][j] + (an == lane ? fc_[h] + lc[h] : 0.f);
               }
             }
           }
@@ -1910,6 +1909,10 @@ static int launch_wpb(const HandsArgs& A, cudaStream_t stream) {
   if (WPB > 1 && tail) pp_hands_step_kernel<1><<<tail, 32, smem, stream>>>(A, nblk * WPB);
   return (nblk ? 1 : 0) + (WPB > 1 && tail ? 1 : 0);
 }
-constexpr int WARPS_PER_BLOCK = 2;  // measured on B200: 1 -> 480 k, 2 -> 549 k, 5 -> 487 k env-steps/s (profiles/)
+#ifndef PP_WPB
+#define PP_WPB 2
+#endif
+// envs per block; measured on B200 (env-steps/s, profiles/): 2 -> 871 k, 5 -> 665 k, 10 -> 696 k
+constexpr int WARPS_PER_BLOCK = PP_WPB;
 int pp_launch_hands(const HandsArgs& A, cudaStream_t stream) { return launch_wpb<WARPS_PER_BLOCK>(A, stream); }
 size_t pp_hands_smem_bytes() { return sizeof(WarpShared); }
