@@ -730,7 +730,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         }
       }
       // ---- mj_fwdActuation (position servos on joints / 2-joint fixed tendons) + qfrc_smooth
-      float fs[2], damp[2];
+      float fs[2];
 #pragma unroll
       for (int h = 0; h < 2; h++) {
         float f = 0.f;
@@ -746,9 +746,9 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
           act_force[h] = f;
         }
         const float fa = __shfl_sync(FULL, f, ht.dof_act[h * PP_HD + l]);
-        damp[h] = ht.damping[h * PP_HD + l];
+        const float damp_h = ht.damping[h * PP_HD + l];
         const float applied = (A.qfrc_applied && L.dof) ? A.qfrc_applied[sbase + PP_NKEY + h * PP_HD + lane] : 0.f;
-        fs[h] = L.dof ? (-damp[h] * v[h] - bias[h] + fa + applied) : 0.f;
+        fs[h] = L.dof ? (-damp_h * v[h] - bias[h] + fa + applied) : 0.f;
       }
       float fsk[3];
 #pragma unroll
@@ -1069,7 +1069,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       for (int h = 0; h < 2; h++) a[h] = (stick[h] && floss[h] > 0.f) ? faref[h] : acc[h];
       float Ma[2] = {0.f, 0.f}, sMa = 0.f;
       float jar[4] = {0.f, 0.f, 0.f, 0.f};
-      float cco[4] = {0.f, 0.f, 0.f, 0.f}, sco = 0.f;  // row curvatures H_t was last assembled with
+      int zone_old = 0;  // zones (active bits) of the lane's in-front contact rows and slot row H_t was last assembled with
       const bool con_on = lane < ncon && my_slot != -2;
       // front lane identity: lane = replica*16 + hand*8 + chain
       const int frep = lane >> 4, fh = (lane >> 3) & 1, fc = lane & 7;
@@ -1253,19 +1253,19 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         // diagonal of the dof rows (Euler: h * damping), added to M when the fronts are loaded
         if (L.dof) {
 #pragma unroll
-          for (int h = 0; h < 2; h++) W.dg[h * 26 + lane] = euler ? o.h * damp[h] : fc_[h] + lc[h];
+          for (int h = 0; h < 2; h++) W.dg[h * 26 + lane] = euler ? o.h * ht.damping[h * PP_HD + lane] : fc_[h] + lc[h];
         }
         // H_t without that diagonal (M + cliques of the in-front contacts - Schur complements of the key
         // slots) only changes when an in-front contact row or a slot's limit row changes zone: kept otherwise
         bool redo = false;
         if (!euler) {
           bool chg = iter == 0;
-          if (con_on && !my_lr) chg |= cc[0] != cco[0] || cc[1] != cco[1] || cc[2] != cco[2] || cc[3] != cco[3];
-          if (lane < nslot) chg |= sc != sco;
+          int zone = 0;
+          if (con_on && !my_lr) zone = (cc[0] != 0.f ? 1 : 0) | (cc[1] != 0.f ? 2 : 0) | (cc[2] != 0.f ? 4 : 0) | (cc[3] != 0.f ? 8 : 0);
+          if (lane < nslot && sc != 0.f) zone |= 16;
+          chg |= zone != zone_old;
           redo = __any_sync(FULL, chg);
-#pragma unroll
-          for (int k = 0; k < 4; k++) cco[k] = cc[k];
-          sco = sc;
+          zone_old = zone;
         }
         float shss = sM + sc;  // H(slot, slot), lane < nslot
         if (redo) {
