@@ -26,6 +26,12 @@
 #include "../../include/pp_model.h"
 #include "pp_env.cuh"
 #include "pp_keys.cuh"
+#ifndef PP_T2
+#define PP_T2 1
+#endif
+#ifndef PP_T4
+#define PP_T4 1
+#endif
 
 namespace {
 
@@ -1542,7 +1548,13 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
           // Cholesky of the SPD capacitance (lane = row) and solve C t = B^T y0
           for (int j = 0; j < m; j++) {
             float s = 0.f;
-            if (lane >= j && lane < m) { s = C[lane][j]; for (int k = 0; k < j; k++) s -= C[lane][k] * C[j][k]; }
+            if (lane >= j && lane < m) {
+              s = C[lane][j];
+#if PP_T2
+#pragma unroll 4
+#endif
+              for (int k = 0; k < j; k++) s -= C[lane][k] * C[j][k];
+            }
             const float inv = rsqrtf(fmaxf(__shfl_sync(FULL, s, j), 1e-30f));
             if (lane >= j && lane < m) C[lane][j] = lane == j ? inv : s * inv;
             __syncwarp();
@@ -1597,11 +1609,23 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         float g1 = grad[0] * p[0] + grad[1] * p[1] + sgrad * sp;
         float g2 = p[0] * Mp[0] + p[1] * Mp[1] + sp * sMp;
         float gauss1 = (Ma[0] - fs[0]) * p[0] + (Ma[1] - fs[1]) * p[1] + (sMa - sfs) * sp;
+#if PP_T4
+        // phi''(0) = p^T H p from the curvatures already in hand: the first Newton step on phi starts from
+        // alpha = 0 without evaluating the rows there (phi'(0) = g1)
+        float dd0 = (fc_[0] + lc[0]) * p[0] * p[0] + (fc_[1] + lc[1]) * p[1] * p[1] + sc * sp * sp;
+#pragma unroll
+        for (int k = 0; k < 4; k++) dd0 += cc[k] * jp[k] * jp[k];
+        dd0 = wsum(dd0);
+#endif
         g1 = wsum(g1); g2 = wsum(g2); gauss1 = wsum(gauss1);
         if (!(g1 < 0.f) || 0.5f * scale * (-g1) < 1e-10f) { euler = true; continue; }  // converged
         float alpha = 0.f, lo = 0.f, hi = -1.f;
         bool changed = false;
-        for (int ls = 0; ls < 20; ls++) {
+        int ls0 = 0;
+#if PP_T4
+        if (dd0 + g2 > 0.f) { alpha = -g1 / (dd0 + g2); ls0 = 1; ls_total++; }
+#endif
+        for (int ls = ls0; ls < 20; ls++) {
           float dphi = 0.f, ddphi = 0.f;
           bool ch = false;
 #pragma unroll
