@@ -46,7 +46,8 @@ struct pp_env {
   bool use_applied = false;
   long long launches = 0;
   // host-buffer path
-  cudaStream_t hstream = nullptr;
+  cudaStream_t hstream = nullptr, hstream2 = nullptr;  // host-buffer calls: the batch is stepped in two halves
+  cudaEvent_t h_ready = nullptr;                       // so that the first half's D2H overlaps the second half's step
   float *h_actions = nullptr, *h_obs = nullptr, *h_reward = nullptr, *h_terms = nullptr, *h_discount = nullptr;
   uint8_t* h_done = nullptr;
   float *d_actions = nullptr, *d_obs = nullptr, *d_reward = nullptr, *d_terms = nullptr, *d_discount = nullptr;
@@ -313,6 +314,8 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(cudaMemcpy(e->act_max_d, e->act_max.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
   // host-buffer path: pinned staging + device mirrors
   CUDA_OK(cudaStreamCreateWithFlags(&e->hstream, cudaStreamNonBlocking));
+  CUDA_OK(cudaStreamCreateWithFlags(&e->hstream2, cudaStreamNonBlocking));
+  CUDA_OK(cudaEventCreateWithFlags(&e->h_ready, cudaEventDisableTiming));
   CUDA_OK(cudaMallocHost((void**)&e->h_actions, (size_t)N * e->action_dim * 4));
   CUDA_OK(cudaMallocHost((void**)&e->h_obs, (size_t)N * e->obs_dim * 4));
   CUDA_OK(cudaMallocHost((void**)&e->h_reward, (size_t)N * 4));
@@ -342,6 +345,8 @@ extern "C" int pp_destroy(pp_env* e) {
   void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
   for (void* p : host) if (p) cudaFreeHost(p);
   if (e->hstream) cudaStreamDestroy(e->hstream);
+  if (e->hstream2) cudaStreamDestroy(e->hstream2);
+  if (e->h_ready) cudaEventDestroy(e->h_ready);
   delete e;
   return PP_OK;
 }
@@ -362,7 +367,8 @@ extern "C" int pp_action_bounds(const pp_env* e, float* lo, float* hi) {
 
 // ------------------------------------------------------------------ launches
 static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions, float* obs, float* reward,
-                  float* terms, uint8_t* done, float* discount, cudaStream_t s) {
+                  float* terms, uint8_t* done, float* discount, cudaStream_t s, int env_begin = 0,
+                  int env_count = -1) {
   const pp_config& c = e->cfg;
   if (c.task == PP_TASK_SELF_ACTUATED_PIANO) {
     PianoOnlyArgs A;
@@ -397,7 +403,7 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     A.act_vel = e->act_vel; A.site_xpos = e->site_xpos; A.activation = e->activation;
     A.counters = e->counters;
     A.eval = EvalAccum{e->eval_sum, e->eval_steps, e->eval_episode, e->eval_count};
-    e->launches += pp_launch_hands(A, s) - 1;
+    e->launches += pp_launch_hands(A, s, env_begin, env_count) - 1;
   }
   e->launches++;
   cudaError_t err = cudaGetLastError();
@@ -439,14 +445,24 @@ extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* 
              pd = is_pinned(done), pc = is_pinned(discount);
   if (!pa) memcpy(e->h_actions, actions, N * e->action_dim * 4);
   CUDA_OK(cudaMemcpyAsync(e->d_actions, pa ? actions : e->h_actions, N * e->action_dim * 4, cudaMemcpyHostToDevice, s));
-  int rc = launch(e, PP_MODE_STEP, nullptr, e->d_actions, obs ? e->d_obs : nullptr, e->d_reward,
-                  terms ? e->d_terms : nullptr, e->d_done, discount ? e->d_discount : nullptr, s);
-  if (rc != PP_OK) return rc;
-  if (obs) CUDA_OK(d2h(obs, e->h_obs, e->d_obs, N * e->obs_dim * 4, po, s));
-  CUDA_OK(d2h(reward, e->h_reward, e->d_reward, N * 4, pr, s));
-  if (terms) CUDA_OK(d2h(terms, e->h_terms, e->d_terms, N * 5 * 4, pt, s));
-  if (discount) CUDA_OK(d2h(discount, e->h_discount, e->d_discount, N * 4, pc, s));
-  CUDA_OK(d2h(done, e->h_done, e->d_done, N, pd, s));
+  // two halves on two streams (hands task, large batches): the first half's results travel to the host while
+  // the second half is still stepping. Both grids are resident together, so the device does the same work.
+  const bool split = e->cfg.task == PP_TASK_PIANO_WITH_SHADOW_HANDS && N >= 1024;
+  const size_t n0 = split ? ((N / 2) & ~(size_t)1) : N;
+  if (split) { CUDA_OK(cudaEventRecord(e->h_ready, s)); CUDA_OK(cudaStreamWaitEvent(e->hstream2, e->h_ready, 0)); }
+  for (int half = 0; half < (split ? 2 : 1); half++) {
+    cudaStream_t hs = half ? e->hstream2 : s;
+    const size_t b = half ? n0 : 0, n = half ? N - n0 : n0;
+    int rc = launch(e, PP_MODE_STEP, nullptr, e->d_actions, obs ? e->d_obs : nullptr, e->d_reward,
+                    terms ? e->d_terms : nullptr, e->d_done, discount ? e->d_discount : nullptr, hs, (int)b, (int)n);
+    if (rc != PP_OK) return rc;
+    if (obs) CUDA_OK(d2h(obs + b * e->obs_dim, e->h_obs + b * e->obs_dim, e->d_obs + b * e->obs_dim, n * e->obs_dim * 4, po, hs));
+    CUDA_OK(d2h(reward + b, e->h_reward + b, e->d_reward + b, n * 4, pr, hs));
+    if (terms) CUDA_OK(d2h(terms + b * 5, e->h_terms + b * 5, e->d_terms + b * 5, n * 5 * 4, pt, hs));
+    if (discount) CUDA_OK(d2h(discount + b, e->h_discount + b, e->d_discount + b, n * 4, pc, hs));
+    CUDA_OK(d2h(done + b, e->h_done + b, e->d_done + b, n, pd, hs));
+  }
+  if (split) CUDA_OK(cudaStreamSynchronize(e->hstream2));
   CUDA_OK(cudaStreamSynchronize(s));
   if (obs && !po) memcpy(obs, e->h_obs, N * e->obs_dim * 4);
   if (!pr) memcpy(reward, e->h_reward, N * 4);

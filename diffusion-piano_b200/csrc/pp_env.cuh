@@ -55,5 +55,6 @@ struct HandsArgs {
 };
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);
-int pp_launch_hands(const HandsArgs& A, cudaStream_t stream);  // returns the number of kernels launched
+// launches the step for envs [env_begin, env_begin + env_count) (env_count < 0: to the end); returns the number of kernels
+int pp_launch_hands(const HandsArgs& A, cudaStream_t stream, int env_begin = 0, int env_count = -1);
 size_t pp_hands_smem_bytes();

@@ -1921,7 +1921,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
 }
 
 template <int WPB>
-static int launch_wpb(const HandsArgs& A, cudaStream_t stream) {
+static int launch_wpb(const HandsArgs& A, cudaStream_t stream, int env_begin, int env_count) {
   static bool configured = false;
   const size_t smem = sizeof(WarpShared);
   if (!configured) {
@@ -1929,9 +1929,9 @@ static int launch_wpb(const HandsArgs& A, cudaStream_t stream) {
     cudaFuncSetAttribute(pp_hands_step_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured = true;
   }
-  const int nblk = A.num_envs / WPB, tail = A.num_envs - nblk * WPB;
-  if (nblk) pp_hands_step_kernel<WPB><<<nblk, 32 * WPB, smem * WPB, stream>>>(A, 0);
-  if (WPB > 1 && tail) pp_hands_step_kernel<1><<<tail, 32, smem, stream>>>(A, nblk * WPB);
+  const int nblk = env_count / WPB, tail = env_count - nblk * WPB;
+  if (nblk) pp_hands_step_kernel<WPB><<<nblk, 32 * WPB, smem * WPB, stream>>>(A, env_begin);
+  if (WPB > 1 && tail) pp_hands_step_kernel<1><<<tail, 32, smem, stream>>>(A, env_begin + nblk * WPB);
   return (nblk ? 1 : 0) + (WPB > 1 && tail ? 1 : 0);
 }
 #ifndef PP_WPB
@@ -1939,5 +1939,8 @@ static int launch_wpb(const HandsArgs& A, cudaStream_t stream) {
 #endif
 // envs per block; measured on B200 (env-steps/s, profiles/): 2 -> 871 k, 5 -> 665 k, 10 -> 696 k
 constexpr int WARPS_PER_BLOCK = PP_WPB;
-int pp_launch_hands(const HandsArgs& A, cudaStream_t stream) { return launch_wpb<WARPS_PER_BLOCK>(A, stream); }
+int pp_launch_hands(const HandsArgs& A, cudaStream_t stream, int env_begin, int env_count) {
+  if (env_count < 0) env_count = A.num_envs - env_begin;
+  return launch_wpb<WARPS_PER_BLOCK>(A, stream, env_begin, env_count);
+}
 size_t pp_hands_smem_bytes() { return sizeof(WarpShared); }

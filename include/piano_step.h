@@ -86,7 +86,8 @@ int pp_step(pp_env *env, const float *actions_dev, float *obs_dev, float *reward
 /* Host-buffer variant: H2D of actions, step, D2H of obs/reward/done inside the call; returns
  * after the results are on the host. Page-locked caller buffers (cudaHostAlloc, cudaHostRegister,
  * torch pin_memory) are the DMA endpoints themselves; pageable ones go through pinned staging
- * owned by the handle plus one host memcpy each. */
+ * owned by the handle plus one host memcpy each. Large two-hand batches are stepped as two halves on
+ * two internal streams so that the first half's D2H overlaps the second half's step (same results). */
 int pp_step_host(pp_env *env, const float *actions, float *obs, float *reward,
                  float *reward_terms, uint8_t *done, float *discount);
 int pp_reset_host(pp_env *env, const uint8_t *mask, float *obs);

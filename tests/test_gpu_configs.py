@@ -177,3 +177,26 @@ def test_full_size_batch_order_and_shard_invariance(cuda_lib, config, B, steps):
     assert torch.equal(a, b)
     env_s.close()
     del o_a
+
+
+def test_host_buffer_step_equals_device_step(cuda_lib):
+    """pp_step_host steps large batches as two halves on two streams (D2H of the first half overlaps the
+    second half's step): same rows as the device-pointer call, bit for bit."""
+    import torch
+    from diffusion_piano_b200 import suite
+    task = _guren_task()
+    B = 2050  # even split point, odd-sized halves exercise the tail launch too
+    rng = np.random.RandomState(11)
+    acts = [rng.uniform(-1, 1, (B, 45)).astype(np.float32) for _ in range(3)]
+    env_d = suite.BatchedEnvironment(task, B, canonical_actions=True, auto_reset=True)
+    env_h = suite.BatchedEnvironment(task, B, canonical_actions=True, auto_reset=True)
+    env_d.reset_device(); obs_h0 = env_h.reset()
+    for a in acts:
+        obs_d, rew_d, done_d, terms_d, disc_d = env_d.step_device(torch.from_numpy(a).cuda())
+        torch.cuda.synchronize()
+        obs_h, rew_h, done_h = env_h.step(a)
+        flat = np.concatenate([obs_h[k] for k, _ in sorted(env_h.layout.items(), key=lambda kv: kv[1][0])], axis=1)
+        np.testing.assert_array_equal(flat.astype(np.float32), obs_d.cpu().numpy())
+        np.testing.assert_array_equal(rew_h.astype(np.float32), rew_d.cpu().numpy())
+        np.testing.assert_array_equal(done_h, done_d.cpu().numpy().astype(bool))
+    env_d.close(); env_h.close()
