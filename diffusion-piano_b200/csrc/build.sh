@@ -1,5 +1,5 @@
 #!/bin/bash
-# Builds libpiano_step.so (sm_100a) in-tree. Usage: csrc/build.sh [extra nvcc flags]
+# Builds libpiano_step.so and libppo_kernels.so (sm_100a) in-tree. Usage: csrc/build.sh [extra nvcc flags]
 set -e
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
@@ -13,3 +13,4 @@ $NVCC $COMMON "$@" -c pp_api.cu -o "$OBJ/pp_api.o" 2>&1
 $NVCC $COMMON "$@" -c pp_piano_only.cu -o "$OBJ/pp_piano_only.o" 2>&1
 $NVCC $COMMON -prec-div=false -prec-sqrt=false "$@" -c pp_hands.cu -o "$OBJ/pp_hands.o" 2>&1
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o ../libpiano_step.so "$OBJ/pp_api.o" "$OBJ/pp_piano_only.o" "$OBJ/pp_hands.o" 2>&1
+$NVCC $COMMON "$@" -shared ppo_kernels.cu -o ../libppo_kernels.so 2>&1

@@ -1,0 +1,714 @@
+// ppo_kernels.cu - device side of the PPO v2 update (include/ppo_kernels.h). sm_100a.
+//
+// Everything here is small-batch work (128-row minibatches, 256-wide layers): the kernels are sized so that
+// one minibatch update is a short chain of launches inside a CUDA graph, every reduction has a fixed order
+// (bit-reproducible runs), and all loop state lives in `ppo_ctrl` on the device.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/ppo_kernels.h"
+
+namespace {
+
+thread_local char g_err[256] = "";
+
+int fail(const char* what, cudaError_t e) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+  return -2;
+}
+int invalid(const char* what) {
+  snprintf(g_err, sizeof(g_err), "invalid argument: %s", what);
+  return -1;
+}
+#define PPO_LAUNCH_CHECK(name)                 \
+  do {                                         \
+    cudaError_t e_ = cudaGetLastError();       \
+    if (e_ != cudaSuccess) return fail(name, e_); \
+    return 0;                                  \
+  } while (0)
+
+constexpr float kLnEps = 1e-5f;
+constexpr float kHalfLog2Pi = 0.91893853320467274178f;
+
+// ---------------------------------------------------------------- Philox4x32-10 (counter-based RNG)
+__device__ __forceinline__ uint4 philox4x32(uint4 c, uint2 k) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+__device__ __forceinline__ uint4 rng4(const ppo_ctrl* ctrl, uint32_t stream_id, uint32_t idx) {
+  uint64_t ctr = ctrl->rng_counter, seed = ctrl->seed;
+  return philox4x32(make_uint4(idx, stream_id, (uint32_t)ctr, (uint32_t)(ctr >> 32)),
+                    make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+}
+__device__ __forceinline__ float u01(uint32_t x) { return ((x >> 8) + 0.5f) * (1.0f / 16777216.0f); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---------------------------------------------------------------- Linear epilogue: bias, ReLU, LayerNorm, dropout
+// One warp per row, lane l owns columns l, l+32, ... (coalesced 128-byte rows of the GEMM output).
+__global__ void __launch_bounds__(256) relu_ln_fwd_kernel(
+    const float* y /* may alias h_save */, const float* __restrict__ bias, const float* __restrict__ gamma,
+    const float* __restrict__ beta, float* __restrict__ out, float* h_save, float* __restrict__ stats, int rows,
+    int H, float p, const uint8_t* __restrict__ mask_in, uint8_t* __restrict__ mask_out, const ppo_ctrl* ctrl,
+    uint32_t rng_stream) {
+  const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int vpt = H >> 5;
+  float h[8];
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j < vpt) {
+      const int c = lane + 32 * j;
+      h[j] = fmaxf(y[(size_t)row * H + c] + bias[c], 0.f);
+      s += h[j];
+    }
+  const float mu = warp_sum(s) / H;
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j < vpt) q += (h[j] - mu) * (h[j] - mu);
+  const float rstd = rsqrtf(warp_sum(q) / H + kLnEps);
+  if (stats != nullptr && lane == 0) {
+    stats[2 * row] = mu;
+    stats[2 * row + 1] = rstd;
+  }
+  uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
+  if (p > 0.f && mask_in == nullptr) {
+    r0 = rng4(ctrl, rng_stream, (uint32_t)(row * 64 + lane * 2));
+    r1 = rng4(ctrl, rng_stream, (uint32_t)(row * 64 + lane * 2 + 1));
+  }
+  const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+  const float keep_scale = 1.f / (1.f - p);
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j < vpt) {
+      const int c = lane + 32 * j;
+      const size_t i = (size_t)row * H + c;
+      float o = (h[j] - mu) * rstd * gamma[c] + beta[c];
+      if (p > 0.f) {
+        const bool keep = mask_in != nullptr ? mask_in[i] != 0 : u01(rr[j]) >= p;
+        if (mask_out != nullptr) mask_out[i] = keep;
+        o = keep ? o * keep_scale : 0.f;
+      }
+      out[i] = o;
+      if (h_save != nullptr) h_save[i] = h[j];
+    }
+}
+
+// Backward of the block: 32 rows per CTA (one per warp), column sums staged through shared memory, per-CTA
+// partials to scratch, the last CTA (ticket) adds the partials in CTA order.
+__global__ void __launch_bounds__(1024) relu_ln_bwd_kernel(
+    const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
+    const float* __restrict__ gamma, const uint8_t* __restrict__ mask, float p, float* __restrict__ dy,
+    float* __restrict__ dbias, float* __restrict__ dgamma, float* __restrict__ dbeta, float* scratch,
+    uint32_t* ticket, int rows, int H) {
+  __shared__ float col[32][257];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, row = blockIdx.x * 32 + warp;
+  const int vpt = H >> 5;
+  const bool live = row < rows;
+  float d_o[8], xh[8], dyv[8];
+  float s1 = 0.f, s2 = 0.f, mu = 0.f, rstd = 0.f;
+  const float keep_scale = 1.f / (1.f - p);
+  if (live) {
+    mu = stats[2 * row];
+    rstd = stats[2 * row + 1];
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    d_o[j] = xh[j] = dyv[j] = 0.f;
+    if (j < vpt && live) {
+      const int c = lane + 32 * j;
+      const size_t i = (size_t)row * H + c;
+      float g = dout[i];
+      if (p > 0.f) g = mask[i] ? g * keep_scale : 0.f;
+      d_o[j] = g;
+      xh[j] = (hbuf[i] - mu) * rstd;
+      const float dx = g * gamma[c];
+      s1 += dx;
+      s2 += dx * xh[j];
+    }
+  }
+  s1 = warp_sum(s1) / H;
+  s2 = warp_sum(s2) / H;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j < vpt && live) {
+      const int c = lane + 32 * j;
+      const size_t i = (size_t)row * H + c;
+      const float dh = rstd * (d_o[j] * gamma[c] - s1 - xh[j] * s2);
+      dyv[j] = hbuf[i] > 0.f ? dh : 0.f;
+      dy[i] = dyv[j];
+    }
+  // three column sums over this CTA's 32 rows: dbias (dy), dgamma (dout * xhat), dbeta (dout)
+  float* part = scratch + (size_t)blockIdx.x * 3 * H;
+  for (int which = 0; which < 3; ++which) {
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (j < vpt) col[warp][lane + 32 * j] = which == 0 ? dyv[j] : which == 1 ? d_o[j] * xh[j] : d_o[j];
+    __syncthreads();
+    if (threadIdx.x < H) {
+      float a = 0.f;
+#pragma unroll 8
+      for (int w = 0; w < 32; ++w) a += col[w][threadIdx.x];
+      part[which * H + threadIdx.x] = a;
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  for (int i = threadIdx.x; i < 3 * H; i += blockDim.x) {
+    float a = 0.f;
+    for (int b = 0; b < (int)gridDim.x; ++b) a += scratch[(size_t)b * 3 * H + i];
+    float* dst = i < H ? dbias : i < 2 * H ? dgamma : dbeta;
+    dst[i % H] = a;
+  }
+  if (threadIdx.x == 0) *ticket = 0;
+}
+
+// ---------------------------------------------------------------- heads
+// Policy head, one CTA of 32 warps, warp per row (rows w, w+32, ...), lane owns action dims lane and lane+32.
+__global__ void __launch_bounds__(1024) policy_head_kernel(
+    const float* __restrict__ y4, const float* __restrict__ b4, const float* __restrict__ log_std,
+    const float* __restrict__ actions, const float* __restrict__ old_logp, const float* __restrict__ adv,
+    float clip_eps, float entropy_coef, float* __restrict__ dz, float* __restrict__ db4,
+    float* __restrict__ dlog_std, float* __restrict__ logp_out, ppo_ctrl* ctrl, int B, int A) {
+  __shared__ float col_b[32][65], col_s[32][65], red[32][2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float ls[2], inv_var[2], bb[2];
+  bool has[2];
+  float ent_row = 0.f;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int c = lane + 32 * j;
+    has[j] = c < A;
+    ls[j] = has[j] ? fminf(fmaxf(log_std[c], -20.f), 2.f) : 0.f;
+    inv_var[j] = expf(-2.f * ls[j]);
+    bb[j] = has[j] ? b4[c] : 0.f;
+    if (has[j]) ent_row += 0.5f + kHalfLog2Pi + ls[j];
+  }
+  const float entropy = warp_sum(ent_row) / A;  // mean over [B, A] of a row-constant
+  float acc_b[2] = {0.f, 0.f}, acc_s[2] = {0.f, 0.f}, acc_surr = 0.f, acc_ratio = 0.f;
+  for (int row = warp; row < B; row += 32) {
+    float mu[2], diff[2], lp = 0.f;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      mu[j] = diff[j] = 0.f;
+      if (has[j]) {
+        const size_t i = (size_t)row * A + lane + 32 * j;
+        mu[j] = tanhf(y4[i] + bb[j]);
+        diff[j] = actions[i] - mu[j];
+        lp += -0.5f * diff[j] * diff[j] * inv_var[j] - ls[j] - kHalfLog2Pi;
+      }
+    }
+    lp = warp_sum(lp);
+    const float a = adv[row], ratio = expf(lp - old_logp[row]);
+    const float surr1 = ratio * a, surr2 = fminf(fmaxf(ratio, 1.f - clip_eps), 1.f + clip_eps) * a;
+    const bool inside = ratio >= 1.f - clip_eps && ratio <= 1.f + clip_eps;
+    // torch.min sends the gradient to the smaller argument and splits it on ties
+    const float w1 = surr1 < surr2 ? 1.f : surr1 == surr2 ? 0.5f : 0.f;
+    const float w2 = surr2 < surr1 ? 1.f : surr1 == surr2 ? 0.5f : 0.f;
+    const float dlogp = -(w1 + (inside ? w2 : 0.f)) * a * ratio / B;
+    if (lane == 0) {
+      acc_surr += fminf(surr1, surr2);
+      acc_ratio += ratio;
+      if (logp_out != nullptr) logp_out[row] = lp;
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+      if (has[j]) {
+        const float dmu = dlogp * diff[j] * inv_var[j];
+        const float g = dmu * (1.f - mu[j] * mu[j]);
+        dz[(size_t)row * A + lane + 32 * j] = g;
+        acc_b[j] += g;
+        acc_s[j] += dlogp * (diff[j] * diff[j] * inv_var[j] - 1.f);
+      }
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    col_b[warp][lane + 32 * j] = acc_b[j];
+    col_s[warp][lane + 32 * j] = acc_s[j];
+  }
+  if (lane == 0) {
+    red[warp][0] = acc_surr;
+    red[warp][1] = acc_ratio;
+  }
+  __syncthreads();
+  if (threadIdx.x < A) {
+    float sb = 0.f, ss = 0.f;
+    for (int w = 0; w < 32; ++w) {
+      sb += col_b[w][threadIdx.x];
+      ss += col_s[w][threadIdx.x];
+    }
+    db4[threadIdx.x] = sb;
+    const float raw = log_std[threadIdx.x];
+    dlog_std[threadIdx.x] = (raw >= -20.f && raw <= 2.f) ? ss - entropy_coef / A : 0.f;
+  }
+  if (threadIdx.x == 0) {
+    float s = 0.f, r = 0.f;
+    for (int w = 0; w < 32; ++w) {
+      s += red[w][0];
+      r += red[w][1];
+    }
+    ctrl->actor_loss = -s / B - entropy_coef * entropy;
+    ctrl->entropy = entropy;
+    ctrl->mean_ratio = r / B;
+  }
+}
+
+__global__ void __launch_bounds__(1024) value_head_kernel(const float* __restrict__ y4, const float* __restrict__ b4,
+                                                          const float* __restrict__ returns, float* __restrict__ dv,
+                                                          float* __restrict__ db4, ppo_ctrl* ctrl, int B) {
+  __shared__ float red[32][3];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float sq = 0.f, sv = 0.f, sd = 0.f;
+  const float b = b4[0];
+  for (int i = threadIdx.x; i < B; i += blockDim.x) {
+    const float v = y4[i] + b, e = v - returns[i], g = 2.f * e / B;
+    dv[i] = g;
+    sq += e * e;
+    sv += v;
+    sd += g;
+  }
+  sq = warp_sum(sq);
+  sv = warp_sum(sv);
+  sd = warp_sum(sd);
+  if (lane == 0) red[warp][0] = sq, red[warp][1] = sv, red[warp][2] = sd;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, c = 0.f, d = 0.f;
+    for (int w = 0; w < 32; ++w) a += red[w][0], c += red[w][1], d += red[w][2];
+    ctrl->critic_loss = a / B;
+    ctrl->mean_value = c / B;
+    db4[0] = d;
+  }
+}
+
+__global__ void add_bias_kernel(const float* __restrict__ y, const float* __restrict__ b, float* __restrict__ out,
+                                int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = y[i] + b[0];
+}
+
+// select_actions: warp per env.
+__global__ void __launch_bounds__(256) sample_actions_kernel(
+    const float* __restrict__ y4, const float* __restrict__ b4, const float* __restrict__ log_std,
+    const float* __restrict__ noise_in, float* __restrict__ actions, float* __restrict__ logp,
+    const ppo_ctrl* ctrl, int N, int A) {
+  const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= N) return;
+  float lp = 0.f;
+  uint4 r = make_uint4(0, 0, 0, 0);
+  if (noise_in == nullptr) r = rng4(ctrl, 0x5a3711u, (uint32_t)(row * 32 + lane));
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int c = lane + 32 * j;
+    if (c < A) {
+      const size_t i = (size_t)row * A + c;
+      float eps;
+      if (noise_in != nullptr) {
+        eps = noise_in[i];
+      } else {  // Box-Muller, one pair of uniforms per normal
+        const float u1 = u01(j == 0 ? r.x : r.z), u2 = u01(j == 0 ? r.y : r.w);
+        eps = sqrtf(-2.f * logf(u1)) * cospif(2.f * u2);
+      }
+      const float ls = fminf(fmaxf(log_std[c], -20.f), 2.f);
+      actions[i] = tanhf(y4[i] + b4[c]) + expf(ls) * eps;
+      lp += -0.5f * eps * eps - ls - kHalfLog2Pi;  // (a - mu)/sigma is eps by construction
+    }
+  }
+  lp = warp_sum(lp);
+  if (lane == 0) logp[row] = lp;
+}
+
+// ---------------------------------------------------------------- batch preparation (one CTA)
+__device__ double block_sum_d(double v, double* sh) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  double t = 0.0;
+  for (int w = 0; w < 32; ++w) t += sh[w];
+  return t;
+}
+
+__global__ void __launch_bounds__(1024) prepare_batch_kernel(
+    const float* __restrict__ rewards, const float* __restrict__ dones, const float* __restrict__ values,
+    const float* __restrict__ next_values, float gamma, float lam, float* __restrict__ rewards_n,
+    float* __restrict__ returns, float* __restrict__ adv_raw, float* __restrict__ adv, ppo_ctrl* ctrl, int N) {
+  __shared__ double shd[32];
+  __shared__ float sA[1024], sB[1024];
+  const int tid = threadIdx.x;
+  // RunningMeanStd (ppo_v2.py:113-131), float64 as numpy: batch mean, batch var = mean((x - mean)^2)
+  double s = 0.0;
+  for (int i = tid; i < N; i += 1024) s += (double)rewards[i];
+  const double bmean = block_sum_d(s, shd) / N;
+  s = 0.0;
+  for (int i = tid; i < N; i += 1024) {
+    const double d = (double)rewards[i] - bmean;
+    s += d * d;
+  }
+  const double bvar = block_sum_d(s, shd) / N;
+  const double mean0 = ctrl->rms_mean, var0 = ctrl->rms_var, cnt0 = ctrl->rms_count;
+  const double delta = bmean - mean0, tot = cnt0 + (double)N;
+  const double mean1 = mean0 + delta * (double)N / tot;
+  const double var1 = (var0 * cnt0 + bvar * (double)N + delta * delta * cnt0 * (double)N / tot) / tot;
+  const double inv_std = 1.0 / sqrt(var1 + 1e-8);
+  __syncthreads();
+  if (tid == 0) {
+    ctrl->rms_mean = mean1;
+    ctrl->rms_var = var1;
+    ctrl->rms_count = tot;
+  }
+  s = 0.0;
+  for (int i = tid; i < N; i += 1024) {
+    const float rn = (float)(((double)rewards[i] - mean1) * inv_std);
+    rewards_n[i] = rn;
+    returns[i] = rn + gamma * (next_values[i] * (1.f - dones[i]));
+    s += (double)rn;
+  }
+  const double mean_rn = block_sum_d(s, shd) / N;
+  if (tid == 0) ctrl->mean_reward_n = (float)mean_rn;
+  __syncthreads();  // rewards_n visible to the whole CTA
+  // the index-wise recursion g_t = delta_t + c_t g_{t+1} (ppo_v2.py:236-246) as a right-to-left scan of the
+  // affine maps x -> b + a x: chunk summaries, a 1024-wide suffix scan, then a re-walk of each chunk
+  const int chunk = (N + 1023) / 1024, lo = tid * chunk, hi = min(lo + chunk, N);
+  float a = 1.f, b = 0.f;
+  for (int t = hi - 1; t >= lo; --t) {
+    const float nd = 1.f - dones[t], nv = t == N - 1 ? next_values[t] : values[t + 1];
+    const float dlt = rewards_n[t] + gamma * nv * nd - values[t], c = gamma * lam * nd;
+    b = dlt + c * b;
+    a = c * a;
+  }
+  sA[tid] = a;
+  sB[tid] = b;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {
+    float a2 = 1.f, b2 = 0.f;
+    const bool on = tid + off < 1024;
+    if (on) a2 = sA[tid + off], b2 = sB[tid + off];
+    __syncthreads();
+    if (on) {  // this chunk's map applied after everything to its right
+      sB[tid] = sB[tid] + sA[tid] * b2;
+      sA[tid] = sA[tid] * a2;
+    }
+    __syncthreads();
+  }
+  float g = tid + 1 < 1024 ? sB[tid + 1] : 0.f;  // gae entering this chunk from the right (0 after the end)
+  double sum = 0.0;
+  for (int t = hi - 1; t >= lo; --t) {
+    const float nd = 1.f - dones[t], nv = t == N - 1 ? next_values[t] : values[t + 1];
+    const float dlt = rewards_n[t] + gamma * nv * nd - values[t];
+    g = dlt + gamma * lam * nd * g;
+    adv[t] = g;
+    if (adv_raw != nullptr) adv_raw[t] = g;
+    sum += (double)g;
+  }
+  const double amean = block_sum_d(sum, shd) / N;
+  sum = 0.0;
+  for (int t = lo; t < hi; ++t) {
+    const double d = (double)adv[t] - amean;
+    sum += d * d;
+  }
+  const double astd = sqrt(block_sum_d(sum, shd) / (double)(N - 1));  // torch .std(): unbiased
+  const float fm = (float)amean, finv = (float)(1.0 / (astd + 1e-8));
+  for (int t = lo; t < hi; ++t) adv[t] = (adv[t] - fm) * finv;
+}
+
+// ---------------------------------------------------------------- minibatch selection
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16;
+  x *= 0x85EBCA6Bu;
+  x ^= x >> 13;
+  x *= 0xC2B2AE35u;
+  x ^= x >> 16;
+  return x;
+}
+// Keyed bijection of [0, n): balanced Feistel network on 2*hb bits with cycle walking.
+__device__ uint32_t feistel_perm(uint32_t i, uint32_t n, uint32_t key) {
+  int bits = 32 - __clz(max(n - 1u, 1u));
+  const int hb = (bits + 1) >> 1;
+  const uint32_t mask = (1u << hb) - 1u;
+  uint32_t x = i;
+  do {
+    uint32_t l = x >> hb, r = x & mask;
+#pragma unroll
+    for (int round = 0; round < 6; ++round) {
+      const uint32_t f = mix32(r ^ (key + 0x9E3779B9u * (round + 1))) & mask;
+      const uint32_t nl = r;
+      r = l ^ f;
+      l = nl;
+    }
+    x = (l << hb) | r;
+  } while (x >= n);
+  return x;
+}
+__device__ __forceinline__ uint32_t perm_key(const ppo_ctrl* ctrl, uint32_t salt) {
+  return mix32((uint32_t)ctrl->seed ^ mix32((uint32_t)ctrl->epoch + 0x632BE5ABu) ^ mix32(salt + 77u));
+}
+
+__global__ void __launch_bounds__(128) gather_minibatch_kernel(
+    const float* __restrict__ states, const float* __restrict__ actions, const float* __restrict__ old_logp,
+    const float* __restrict__ adv, const float* __restrict__ returns, const int32_t* __restrict__ perm,
+    int perm_epochs, const ppo_ctrl* ctrl, uint32_t salt, int N, int S, int A, float* __restrict__ b_states,
+    float* __restrict__ b_actions, float* __restrict__ b_logp, float* __restrict__ b_adv,
+    float* __restrict__ b_returns) {
+  const int r = blockIdx.x, pos = ctrl->cursor + r;
+  int src;
+  if (perm != nullptr)
+    src = perm[(size_t)(ctrl->epoch % perm_epochs) * N + pos];
+  else
+    src = (int)feistel_perm((uint32_t)pos, (uint32_t)N, perm_key(ctrl, salt));
+  for (int c = threadIdx.x; c < S; c += blockDim.x) b_states[(size_t)r * S + c] = states[(size_t)src * S + c];
+  for (int c = threadIdx.x; c < A; c += blockDim.x) b_actions[(size_t)r * A + c] = actions[(size_t)src * A + c];
+  if (threadIdx.x == 0) {
+    b_logp[r] = old_logp[src];
+    b_adv[r] = adv[src];
+    b_returns[r] = returns[src];
+  }
+}
+__global__ void permutation_kernel(const ppo_ctrl* ctrl, uint32_t salt, int N, int32_t* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) out[i] = (int32_t)feistel_perm((uint32_t)i, (uint32_t)N, perm_key(ctrl, salt));
+}
+
+// ---------------------------------------------------------------- clip_grad_norm_ + Adam
+__global__ void __launch_bounds__(1024) grad_sumsq_kernel(const float* __restrict__ grad, int n, float* scratch,
+                                                          uint32_t* ticket, ppo_ctrl* ctrl, int which) {
+  __shared__ float red[32];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float s = 0.f;
+  for (int i = blockIdx.x * 1024 + threadIdx.x; i < n; i += gridDim.x * 1024) s += grad[i] * grad[i];
+  s = warp_sum(s);
+  if (lane == 0) red[warp] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < 32; ++w) t += red[w];
+    scratch[blockIdx.x] = t;
+    __threadfence();
+    is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last || threadIdx.x != 0) return;
+  __threadfence();
+  float t = 0.f;
+  for (int b = 0; b < (int)gridDim.x; ++b) t += ((volatile float*)scratch)[b];
+  ctrl->norm2[which] = t;
+  ctrl->adam_t[which] += 1;
+  *ticket = 0;
+}
+
+__global__ void __launch_bounds__(256) clip_adam_kernel(float* __restrict__ theta, const float* __restrict__ grad,
+                                                        float* __restrict__ m, float* __restrict__ v, int n,
+                                                        const ppo_ctrl* ctrl, int which, float max_norm,
+                                                        float grad_scale, float b1, float b2, float eps) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float total = sqrtf(ctrl->norm2[which]) * grad_scale;
+  const float coef = fminf(max_norm / (total + 1e-6f), 1.f) * grad_scale;
+  const float t = (float)ctrl->adam_t[which];
+  const float bc1 = 1.f - powf(b1, t), bc2 = 1.f - powf(b2, t);
+  const float g = grad[i] * coef;
+  const float mi = b1 * m[i] + (1.f - b1) * g, vi = b2 * v[i] + (1.f - b2) * g * g;
+  m[i] = mi;
+  v[i] = vi;
+  theta[i] -= (ctrl->lr[which] / bc1) * mi / (sqrtf(vi) / sqrtf(bc2) + eps);
+}
+
+// ---------------------------------------------------------------- control block
+__global__ void ctrl_init_kernel(ppo_ctrl* c, uint64_t seed, float lr_a, float lr_c) {
+  ppo_ctrl z = {};
+  z.seed = seed;
+  z.lr[0] = lr_a;
+  z.lr[1] = lr_c;
+  z.best[0] = -INFINITY;  // actor scheduler: mode "max"
+  z.best[1] = INFINITY;   // critic scheduler: mode "min"
+  z.rms_mean = 0.0;
+  z.rms_var = 1.0;
+  z.rms_count = 1e-4;
+  *c = z;
+}
+__global__ void advance_kernel(ppo_ctrl* c, int N, int B) {
+  c->rng_counter += 1;
+  if (B > 0) {
+    c->cursor += B;
+    if (c->cursor >= N) {
+      c->cursor = 0;
+      c->epoch += 1;
+    }
+  }
+}
+__global__ void begin_update_kernel(ppo_ctrl* c) { c->cursor = 0; }
+
+__global__ void plateau_kernel(ppo_ctrl* c, float factor, int patience) {
+  for (int which = 0; which < 2; ++which) {
+    const float metric = which == 0 ? c->mean_reward_n : c->critic_loss;
+    const float best = c->best[which];
+    // threshold 1e-4, threshold_mode "rel"
+    const bool better = which == 0 ? metric > best * (1.f + 1e-4f) : metric < best * (1.f - 1e-4f);
+    if (better) {
+      c->best[which] = metric;
+      c->num_bad[which] = 0;
+    } else {
+      c->num_bad[which] += 1;
+    }
+    if (c->num_bad[which] > patience) {
+      const float lr = c->lr[which], nlr = lr * factor;
+      if (lr - nlr > 1e-8f) c->lr[which] = nlr;
+      c->num_bad[which] = 0;
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* ppo_last_error(void) { return g_err; }
+const char* ppo_version(void) { return "ppo_kernels 0.1 (sm_100a)"; }
+int ppo_ctrl_size(void) { return (int)sizeof(ppo_ctrl); }
+
+int ppo_ctrl_init(ppo_ctrl* c, uint64_t seed, float lr_actor, float lr_critic, void* stream) {
+  if (c == nullptr) return invalid("ctrl");
+  ctrl_init_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(c, seed, lr_actor, lr_critic);
+  PPO_LAUNCH_CHECK("ppo_ctrl_init");
+}
+
+int ppo_relu_ln_fwd(const float* y, const float* bias, const float* gamma, const float* beta, float* out,
+                    float* h_save, float* stats, int rows, int H, float dropout_p, const uint8_t* mask_in,
+                    uint8_t* mask_out, const ppo_ctrl* ctrl, uint32_t rng_stream, void* stream) {
+  if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
+  if (rows <= 0) return invalid("rows");
+  if (dropout_p > 0.f && mask_in == nullptr && ctrl == nullptr) return invalid("dropout needs ctrl or mask_in");
+  relu_ln_fwd_kernel<<<(rows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(y, bias, gamma, beta, out, h_save, stats, rows,
+                                                                      H, dropout_p, mask_in, mask_out, ctrl,
+                                                                      rng_stream);
+  PPO_LAUNCH_CHECK("ppo_relu_ln_fwd");
+}
+
+int ppo_relu_ln_bwd(const float* dout, const float* h, const float* stats, const float* gamma, const uint8_t* mask,
+                    float dropout_p, float* dy, float* dbias, float* dgamma, float* dbeta, float* scratch,
+                    uint32_t* ticket, int rows, int H, void* stream) {
+  if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
+  if (rows <= 0 || rows > 2048) return invalid("rows must be in 1..2048 (scratch holds 64 CTA partials)");
+  if (dropout_p > 0.f && mask == nullptr) return invalid("dropout backward needs the mask");
+  relu_ln_bwd_kernel<<<(rows + 31) / 32, 1024, 0, (cudaStream_t)stream>>>(dout, h, stats, gamma, mask, dropout_p, dy,
+                                                                         dbias, dgamma, dbeta, scratch, ticket, rows,
+                                                                         H);
+  PPO_LAUNCH_CHECK("ppo_relu_ln_bwd");
+}
+
+int ppo_policy_head(const float* y4, const float* b4, const float* log_std, const float* actions,
+                    const float* old_logp, const float* adv, float clip_eps, float entropy_coef, float* dz,
+                    float* db4, float* dlog_std, float* logp_out, ppo_ctrl* ctrl, int B, int A, void* stream) {
+  if (A <= 0 || A > 64) return invalid("action dim must be in 1..64");
+  if (B <= 0) return invalid("B");
+  policy_head_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(y4, b4, log_std, actions, old_logp, adv, clip_eps,
+                                                          entropy_coef, dz, db4, dlog_std, logp_out, ctrl, B, A);
+  PPO_LAUNCH_CHECK("ppo_policy_head");
+}
+
+int ppo_value_head(const float* y4, const float* b4, const float* returns, float* dv, float* db4, ppo_ctrl* ctrl,
+                   int B, void* stream) {
+  if (B <= 0) return invalid("B");
+  value_head_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(y4, b4, returns, dv, db4, ctrl, B);
+  PPO_LAUNCH_CHECK("ppo_value_head");
+}
+
+int ppo_add_bias(const float* y4, const float* b4, float* out, int n, void* stream) {
+  if (n <= 0) return invalid("n");
+  add_bias_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(y4, b4, out, n);
+  PPO_LAUNCH_CHECK("ppo_add_bias");
+}
+
+int ppo_sample_actions(const float* y4, const float* b4, const float* log_std, const float* noise_in, float* actions,
+                       float* logp, const ppo_ctrl* ctrl, int N, int A, void* stream) {
+  if (A <= 0 || A > 64) return invalid("action dim must be in 1..64");
+  if (N <= 0) return invalid("N");
+  sample_actions_kernel<<<(N + 7) / 8, 256, 0, (cudaStream_t)stream>>>(y4, b4, log_std, noise_in, actions, logp, ctrl,
+                                                                      N, A);
+  PPO_LAUNCH_CHECK("ppo_sample_actions");
+}
+
+int ppo_prepare_batch(const float* rewards, const float* dones, const float* values, const float* next_values,
+                      float gamma, float lam, float* rewards_n, float* returns, float* adv_raw, float* adv,
+                      ppo_ctrl* ctrl, int N, void* stream) {
+  if (N < 2) return invalid("N must be >= 2 (unbiased std)");
+  prepare_batch_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(rewards, dones, values, next_values, gamma, lam,
+                                                            rewards_n, returns, adv_raw, adv, ctrl, N);
+  PPO_LAUNCH_CHECK("ppo_prepare_batch");
+}
+
+int ppo_gather_minibatch(const float* states, const float* actions, const float* old_logp, const float* adv,
+                         const float* returns, const int32_t* perm, int perm_epochs, const ppo_ctrl* ctrl,
+                         uint32_t perm_salt, int N, int S, int A, int B, float* b_states, float* b_actions,
+                         float* b_logp, float* b_adv, float* b_returns, void* stream) {
+  if (B <= 0 || N <= 0) return invalid("sizes");
+  if (perm != nullptr && perm_epochs <= 0) return invalid("perm_epochs");
+  gather_minibatch_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(states, actions, old_logp, adv, returns, perm,
+                                                              perm_epochs, ctrl, perm_salt, N, S, A, b_states,
+                                                              b_actions, b_logp, b_adv, b_returns);
+  PPO_LAUNCH_CHECK("ppo_gather_minibatch");
+}
+
+int ppo_permutation(const ppo_ctrl* ctrl, uint32_t perm_salt, int N, int32_t* out, void* stream) {
+  if (N <= 0) return invalid("N");
+  permutation_kernel<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(ctrl, perm_salt, N, out);
+  PPO_LAUNCH_CHECK("ppo_permutation");
+}
+
+int ppo_grad_sumsq(const float* grad, int n, float* scratch, uint32_t* ticket, ppo_ctrl* ctrl, int which,
+                   void* stream) {
+  if (n <= 0 || (which != 0 && which != 1)) return invalid("n / which");
+  int blocks = (n + 4095) / 4096;
+  if (blocks > 1024) blocks = 1024;
+  grad_sumsq_kernel<<<blocks, 1024, 0, (cudaStream_t)stream>>>(grad, n, scratch, ticket, ctrl, which);
+  PPO_LAUNCH_CHECK("ppo_grad_sumsq");
+}
+
+int ppo_clip_adam(float* theta, const float* grad, float* m, float* v, int n, const ppo_ctrl* ctrl, int which,
+                  float max_norm, float grad_scale, float beta1, float beta2, float eps, void* stream) {
+  if (n <= 0 || (which != 0 && which != 1)) return invalid("n / which");
+  clip_adam_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(theta, grad, m, v, n, ctrl, which, max_norm,
+                                                                     grad_scale, beta1, beta2, eps);
+  PPO_LAUNCH_CHECK("ppo_clip_adam");
+}
+
+int ppo_advance(ppo_ctrl* ctrl, int N, int B, void* stream) {
+  advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, N, B);
+  PPO_LAUNCH_CHECK("ppo_advance");
+}
+
+int ppo_begin_update(ppo_ctrl* ctrl, void* stream) {
+  begin_update_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl);
+  PPO_LAUNCH_CHECK("ppo_begin_update");
+}
+
+int ppo_plateau_step(ppo_ctrl* ctrl, float factor, int patience, void* stream) {
+  plateau_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, factor, patience);
+  PPO_LAUNCH_CHECK("ppo_plateau_step");
+}
+
+}  // extern "C"

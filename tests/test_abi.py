@@ -54,3 +54,26 @@ def test_product_does_not_import_oracle():
     for path in (ROOT / "diffusion-piano_b200" / "csrc").iterdir():
         if path.suffix in (".cu", ".cuh"):
             assert "oracle/" not in path.read_text(), path
+
+
+def test_ppo_library_exports_all_declared_symbols():
+    """libppo_kernels.so (include/ppo_kernels.h): every declared entry point is exported and bound, and the
+    control-block layout of the binding matches the library's."""
+    header = (ROOT / "include" / "ppo_kernels.h").read_text()
+    declared = set(re.findall(r"\b(ppo_[a-z_]+)\s*\(", header))
+    from diffusion_piano_b200.ppo import _kernels
+    assert declared == set(_kernels.EXPORTED_SYMBOLS)
+    lib = _kernels.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert b"sm_100a" in lib.ppo_version()
+    assert lib.ppo_ctrl_size() == ctypes.sizeof(_kernels.PPOCtrl)
+
+
+def test_ppo_agent_without_gpu_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from diffusion_piano_b200.ppo import PPOAgent, _kernels
+    with pytest.raises(_kernels.PPOKernelError, match="no CPU fallback"):
+        PPOAgent(329, 45)

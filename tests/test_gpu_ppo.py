@@ -1,0 +1,385 @@
+"""PPO v2 on the device against the oracle (oracle/ppo_oracle.py, itself pinned against a
+recorded run of the reference's ppo_v2.PPOAgent.update) and against the reference's recorded results directly.
+Every kernel is called through the C-ABI of libppo_kernels.so."""
+import ctypes
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tools"))
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch
+
+
+def _agent(torch, state_dim, action_dim, actor=None, critic=None, **kw):
+    from diffusion_piano_b200.ppo import PPOAgent
+
+    ag = PPOAgent(state_dim, action_dim, device="cuda:0", **kw)
+    if actor is not None:
+        ag.actor.load(actor)
+        ag.critic.load(critic)
+    return ag
+
+
+def _stream(torch):
+    return torch.cuda.current_stream().cuda_stream
+
+
+def test_block_forward_backward_matches_oracle(torch_cuda):
+    torch = torch_cuda
+    from diffusion_piano_b200.ppo import _kernels
+    from oracle import ppo_oracle as po
+
+    lib = _kernels.load()
+    rs = np.random.RandomState(0)
+    for rows, H, p in ((128, 256, 0.1), (44, 128, 0.0), (300, 256, 0.1)):
+        y = rs.randn(rows, H).astype(np.float32)
+        bias, gamma, beta = (0.1 * rs.randn(H)).astype(np.float32), (1 + 0.1 * rs.randn(H)).astype(np.float32), \
+            (0.1 * rs.randn(H)).astype(np.float32)
+        mask = (rs.rand(rows, H) >= p).astype(np.uint8)
+        dout = rs.randn(rows, H).astype(np.float32)
+        d = lambda a: torch.as_tensor(a, device="cuda")  # noqa: E731
+        ty, tb, tg, tbe, tm, tdo = d(y), d(bias), d(gamma), d(beta), d(mask), d(dout)
+        out, h, stats = torch.empty_like(ty), torch.empty_like(ty), torch.empty(rows, 2, device="cuda")
+        mask_out = torch.zeros_like(tm)
+        _kernels.check(lib.ppo_relu_ln_fwd(ty.data_ptr(), tb.data_ptr(), tg.data_ptr(), tbe.data_ptr(), out.data_ptr(),
+                                           h.data_ptr(), stats.data_ptr(), rows, H, p, tm.data_ptr() if p > 0 else None,
+                                           mask_out.data_ptr() if p > 0 else None, None, 0, _stream(torch)))
+        # oracle: the block with W = I so that y is the pre-bias Linear output
+        o_ref, cache = po._block_forward(y.astype(np.float64), np.eye(H), bias.astype(np.float64),
+                                         gamma.astype(np.float64), beta.astype(np.float64))
+        if p > 0:
+            o_ref = o_ref * mask / (1 - p)
+            np.testing.assert_array_equal(mask_out.cpu().numpy(), mask)
+        np.testing.assert_allclose(out.cpu().numpy(), o_ref, atol=2e-5)
+        dy, db, dg, dbe = torch.empty_like(ty), torch.empty(H, device="cuda"), torch.empty(H, device="cuda"), \
+            torch.empty(H, device="cuda")
+        scratch = torch.zeros(3 * H * ((rows + 31) // 32), device="cuda")
+        ticket = torch.zeros(1, dtype=torch.int32, device="cuda")
+        for _ in range(2):  # twice: the ticket must be left at zero
+            _kernels.check(lib.ppo_relu_ln_bwd(tdo.data_ptr(), h.data_ptr(), stats.data_ptr(), tg.data_ptr(),
+                                               tm.data_ptr() if p > 0 else None, p, dy.data_ptr(), db.data_ptr(),
+                                               dg.data_ptr(), dbe.data_ptr(), scratch.data_ptr(), ticket.data_ptr(),
+                                               rows, H, _stream(torch)))
+        d_in = dout.astype(np.float64) * (mask / (1 - p) if p > 0 else 1.0)
+        dx_ref, _, db_ref, dg_ref, dbe_ref = po._block_backward(d_in, cache, np.eye(H), gamma.astype(np.float64))
+        np.testing.assert_allclose(dy.cpu().numpy(), dx_ref, atol=3e-5)
+        np.testing.assert_allclose(db.cpu().numpy(), db_ref, atol=2e-4)
+        np.testing.assert_allclose(dg.cpu().numpy(), dg_ref, atol=2e-4)
+        np.testing.assert_allclose(dbe.cpu().numpy(), dbe_ref, atol=2e-4)
+        assert int(ticket.item()) == 0
+
+
+def test_policy_head_matches_oracle(torch_cuda):
+    torch = torch_cuda
+    from diffusion_piano_b200.ppo import _kernels
+    from oracle import ppo_oracle as po
+
+    lib = _kernels.load()
+    rs = np.random.RandomState(1)
+    B, A = 128, 45
+    z = rs.randn(B, A).astype(np.float32)
+    b4 = (0.1 * rs.randn(A)).astype(np.float32)
+    log_std = (-1 + 0.3 * rs.randn(A)).astype(np.float32)
+    log_std[3], log_std[7] = 2.5, -21.0  # outside the clamp: no gradient
+    actions = (np.tanh(z + b4) + 0.4 * rs.randn(B, A)).astype(np.float32)
+    adv = rs.randn(B).astype(np.float32)
+    zz = (z + b4).astype(np.float64)
+    _, _, logp0, _, _ = po.policy_head(zz, actions.astype(np.float64), np.zeros(B), adv.astype(np.float64),
+                                       log_std.astype(np.float64), 0.2, 0.01)
+    old = (logp0 + 0.15 * rs.randn(B)).astype(np.float32)  # ratios on both sides of the clip range
+    loss, ent, logp, dz_ref, dls_ref = po.policy_head(zz, actions.astype(np.float64), old.astype(np.float64),
+                                                      adv.astype(np.float64), log_std.astype(np.float64), 0.2, 0.01)
+    d = lambda a: torch.as_tensor(a, device="cuda")  # noqa: E731
+    ctrl = torch.zeros(ctypes.sizeof(_kernels.PPOCtrl), dtype=torch.uint8, device="cuda")
+    dz, db4, dls, lp = torch.empty(B, A, device="cuda"), torch.empty(A, device="cuda"), torch.empty(A, device="cuda"), \
+        torch.empty(B, device="cuda")
+    tz, tb, tl, ta, to, tadv = d(z), d(b4), d(log_std), d(actions), d(old), d(adv)
+    _kernels.check(lib.ppo_policy_head(tz.data_ptr(), tb.data_ptr(), tl.data_ptr(), ta.data_ptr(), to.data_ptr(),
+                                       tadv.data_ptr(), 0.2, 0.01, dz.data_ptr(), db4.data_ptr(), dls.data_ptr(),
+                                       lp.data_ptr(), ctrl.data_ptr(), B, A, _stream(torch)))
+    c = _kernels.PPOCtrl.from_buffer_copy(ctrl.cpu().numpy().tobytes())
+    np.testing.assert_allclose(lp.cpu().numpy(), logp, rtol=2e-5, atol=2e-4)
+    # a ratio within float32 rounding of the clip edge may fall on the other side: compare all but those rows
+    ratio = np.exp(logp - old)
+    safe = (np.abs(ratio - 0.8) > 1e-3) & (np.abs(ratio - 1.2) > 1e-3)
+    np.testing.assert_allclose(dz.cpu().numpy()[safe], dz_ref[safe], atol=2e-5 * np.abs(dz_ref).max() + 1e-7)
+    if safe.all():
+        np.testing.assert_allclose(db4.cpu().numpy(), dz_ref.sum(0), atol=1e-4 * np.abs(dz_ref.sum(0)).max())
+        np.testing.assert_allclose(dls.cpu().numpy(), dls_ref, atol=1e-4 * np.abs(dls_ref).max())
+        assert abs(c.actor_loss - loss) < 1e-4 * max(1.0, abs(loss))
+    assert dls.cpu().numpy()[3] == 0.0 and dls.cpu().numpy()[7] == 0.0
+    assert abs(c.entropy - ent) < 1e-5
+
+
+@pytest.mark.parametrize("n", [2, 300, 4096, 70001])
+def test_prepare_batch_matches_oracle(torch_cuda, n):
+    torch = torch_cuda
+    from diffusion_piano_b200.ppo import _kernels
+    from oracle import ppo_oracle as po
+
+    lib = _kernels.load()
+    rs = np.random.RandomState(n)
+    ctrl = torch.zeros(ctypes.sizeof(_kernels.PPOCtrl), dtype=torch.uint8, device="cuda")
+    _kernels.check(lib.ppo_ctrl_init(ctrl.data_ptr(), 5, 1e-4, 2e-4, _stream(torch)))
+    rms = po.RunningMeanStd()
+    for it in range(2):  # twice: the running statistics carry over
+        rewards = (2.0 + rs.randn(n)).astype(np.float32)
+        dones = (rs.rand(n) < 0.05).astype(np.float32)
+        values, next_values = rs.randn(n).astype(np.float32), rs.randn(n).astype(np.float32)
+        d = lambda a: torch.as_tensor(a, device="cuda")  # noqa: E731
+        tr, td, tv, tnv = d(rewards), d(dones), d(values), d(next_values)
+        rn, ret, araw, adv = (torch.empty(n, device="cuda") for _ in range(4))
+        _kernels.check(lib.ppo_prepare_batch(tr.data_ptr(), td.data_ptr(), tv.data_ptr(), tnv.data_ptr(), 0.99, 0.95,
+                                             rn.data_ptr(), ret.data_ptr(), araw.data_ptr(), adv.data_ptr(),
+                                             ctrl.data_ptr(), n, _stream(torch)))
+        rn_ref = rms(rewards.astype(np.float64)).astype(np.float32).astype(np.float64)
+        ret_ref, araw_ref, adv_ref = po.prepare_batch(rn_ref, dones.astype(np.float64), values.astype(np.float64),
+                                                      next_values.astype(np.float64), 0.99)
+        c = _kernels.PPOCtrl.from_buffer_copy(ctrl.cpu().numpy().tobytes())
+        np.testing.assert_allclose([c.rms_mean, c.rms_var, c.rms_count], [rms.mean, rms.var, rms.count], rtol=1e-10)
+        np.testing.assert_allclose(rn.cpu().numpy(), rn_ref, atol=1e-6)
+        np.testing.assert_allclose(ret.cpu().numpy(), ret_ref, atol=1e-5)
+        scale = np.abs(araw_ref).max()
+        np.testing.assert_allclose(araw.cpu().numpy(), araw_ref, atol=2e-6 * scale + 1e-6)
+        np.testing.assert_allclose(adv.cpu().numpy(), adv_ref, atol=2e-5)
+        assert abs(c.mean_reward_n - rn_ref.mean()) < 1e-5
+
+
+def test_sampling_and_permutation(torch_cuda):
+    torch = torch_cuda
+    from oracle import ppo_oracle as po
+
+    ag = _agent(torch, 40, 45, seed=3)
+    from diffusion_piano_b200.ppo import _kernels
+
+    rs = np.random.RandomState(2)
+    n = 4096
+    states = torch.as_tensor(rs.randn(n, 40).astype(np.float32), device="cuda")
+    ora = po.PPOOracle({k: v.numpy() for k, v in ag.actor_state_dict().items()},
+                       {k: v.numpy() for k, v in ag.critic_state_dict().items()})
+    mu, sigma = ora.act_mean_std(states.cpu().numpy())
+    # explicit noise: exact formula
+    noise = rs.randn(n, 45).astype(np.float32)
+    a, lp = ag.select_actions(states, noise=torch.as_tensor(noise, device="cuda"))
+    np.testing.assert_allclose(a.cpu().numpy(), mu + sigma * noise, atol=2e-5)
+    np.testing.assert_allclose(lp.cpu().numpy(), ora.log_prob(states.cpu().numpy(), a.cpu().numpy().astype(np.float64)),
+                               rtol=1e-4, atol=2e-3)
+    # Philox noise: standard normal, fresh on every call, log-prob consistent with the drawn action
+    a1, lp1 = ag.select_actions(states)
+    a1, lp1 = a1.cpu().numpy().copy(), lp1.cpu().numpy().copy()
+    a2, _ = ag.select_actions(states)
+    eps = (a1 - mu) / sigma
+    assert abs(eps.mean()) < 0.01 and abs(eps.std() - 1.0) < 0.01
+    assert abs(((eps ** 3).mean())) < 0.05 and abs((eps ** 4).mean() - 3.0) < 0.1
+    assert np.abs(a2.cpu().numpy() - a1).max() > 0.1
+    np.testing.assert_allclose(lp1, ora.log_prob(states.cpu().numpy(), a1.astype(np.float64)), rtol=1e-4, atol=2e-3)
+    # the minibatch permutation is a bijection of [0, N) and changes with the epoch
+    lib = _kernels.load()
+    perms = []
+    for epoch in (0, 1):
+        c = ag.read_ctrl()
+        c.epoch = epoch
+        tmp = torch.as_tensor(np.frombuffer(bytes(c), dtype=np.uint8).copy(), device="cuda")
+        for nn in (300, 4096, 5000):
+            out = torch.empty(nn, dtype=torch.int32, device="cuda")
+            _kernels.check(lib.ppo_permutation(tmp.data_ptr(), 0, nn, out.data_ptr(), _stream(torch)))
+            o = out.cpu().numpy()
+            assert sorted(o.tolist()) == list(range(nn))
+            if nn == 4096:
+                perms.append(o)
+                assert np.mean(o == np.arange(nn)) < 0.01
+                # adjacent outputs are not adjacent inputs
+                assert np.mean(np.abs(np.diff(o)) == 1) < 0.01
+    assert np.mean(perms[0] == perms[1]) < 0.01
+
+
+def _golden():
+    from make_ppo_golden import ppo_fixture_inputs
+
+    z = np.load(ROOT / "tests" / "golden" / "ppo_update.npz")
+    state_dim, action_dim, n, batch, epochs, seed, stride = (int(v) for v in z["meta"])
+    masks, i = [], 0
+    while f"mask_{i}" in z:
+        shp = tuple(z[f"mask_{i}_shape"])
+        masks.append(np.unpackbits(z[f"mask_{i}"])[: shp[0] * shp[1]].reshape(shp))
+        i += 1
+    actor, critic, b = ppo_fixture_inputs(seed, state_dim, action_dim, n)
+    return z, (state_dim, action_dim, n, batch, epochs, stride), masks, actor, critic, b
+
+
+def test_update_matches_reference_and_oracle(torch_cuda):
+    """The full update on the reference's recorded permutations and dropout masks: against the reference's own
+    parameters after the update (golden) and against the oracle's intermediate quantities."""
+    torch = torch_cuda
+    from oracle import ppo_oracle as po
+
+    z, (sd, ad, n, batch, epochs, stride), masks, actor, critic, b = _golden()
+    ag = _agent(torch, sd, ad, actor, critic, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch, ppo_epochs=epochs)
+    n_mb = epochs * ((n + batch - 1) // batch)
+    dm = lambda m: torch.as_tensor(m.astype(np.uint8), device="cuda")  # noqa: E731
+    bb = ag.update(b["states"], b["actions"], b["rewards"].astype(np.float32), z["log_probs"], b["next_states"],
+                   b["dones"], perms=z["perms"], value_masks=[dm(m) for m in masks[0:2]],
+                   next_value_masks=[dm(m) for m in masks[2:4]],
+                   minibatch_masks=[[dm(m) for m in masks[4 + 2 * i: 6 + 2 * i]] for i in range(n_mb)])
+    ora = po.PPOOracle(actor, critic, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch, ppo_epochs=epochs)
+    f = [m.astype(np.float64) for m in masks]
+    inter = ora.update(b["states"], b["actions"], b["rewards"].astype(np.float32), z["log_probs"], b["next_states"],
+                       b["dones"], perms=z["perms"], value_masks=f[0:2], next_value_masks=f[2:4],
+                       minibatch_masks=[f[4 + 2 * i: 6 + 2 * i] for i in range(n_mb)])
+    np.testing.assert_allclose(bb["packed"][2].cpu().numpy(), inter["values"], atol=2e-5)
+    np.testing.assert_allclose(bb["packed"][3].cpu().numpy(), inter["next_values"], atol=2e-5)
+    np.testing.assert_allclose(bb["returns"].cpu().numpy(), inter["returns"], atol=2e-5)
+    np.testing.assert_allclose(bb["adv"].cpu().numpy(), inter["advantages"], atol=1e-4)
+    for name, before, mine, theirs in (("actor", actor, ag.actor_state_dict(), ora.actor_state()),
+                                       ("critic", critic, ag.critic_state_dict(), ora.critic_state())):
+        for k, v in mine.items():
+            v = v.numpy().astype(np.float64)
+            b0 = before[k].astype(np.float64)
+            # against the oracle, every element
+            np.testing.assert_allclose(v - b0, theirs[k] - b0, atol=4e-6, err_msg=f"oracle {name}/{k}")
+            # against the reference's own result
+            ref = z[f"{name}/{k}/sample"].astype(np.float64)
+            np.testing.assert_allclose((v - b0).ravel()[::stride], ref - b0.ravel()[::stride], atol=4e-6,
+                                       err_msg=f"reference {name}/{k}")
+    c = ag.read_ctrl()
+    np.testing.assert_allclose([c.rms_mean, c.rms_var, c.rms_count], z["rms"], rtol=1e-6)
+    assert c.adam_t[0] == n_mb and c.adam_t[1] == n_mb
+    al, cl, ent = ora.log[-1]
+    assert abs(c.critic_loss - cl) < 1e-4 * max(1.0, cl) and abs(c.entropy - ent) < 1e-5
+    assert abs(c.actor_loss - al) < 2e-4 * max(1.0, abs(al))
+
+
+def test_graph_update_matches_oracle(torch_cuda):
+    """The CUDA-graph path (device-side permutation, no dropout so that the oracle can follow): parameters after
+    two updates against the oracle fed the materialised permutations."""
+    torch = torch_cuda
+    from diffusion_piano_b200.ppo import _kernels
+    from make_ppo_golden import ppo_fixture_inputs
+    from oracle import ppo_oracle as po
+
+    lib = _kernels.load()
+    sd, ad, n, batch, epochs = 57, 45, 600, 128, 3
+    actor, critic, b = ppo_fixture_inputs(11, sd, ad, n)
+    ag = _agent(torch, sd, ad, actor, critic, batch_size=batch, ppo_epochs=epochs, dropout_p=0.0, seed=5)
+    ora = po.PPOOracle(actor, critic, batch_size=batch, ppo_epochs=epochs)
+    logp = ora.log_prob(b["states"], b["actions"].astype(np.float64)).astype(np.float32)
+    rs = np.random.RandomState(3)
+    for it in range(2):
+        lp = (logp + 0.1 * rs.randn(n)).astype(np.float32)
+        rewards = (1.0 + rs.randn(n)).astype(np.float32)
+        perms = []
+        c = ag.read_ctrl()
+        for e in range(epochs):
+            c.epoch = it * epochs + e
+            tmp = torch.as_tensor(np.frombuffer(bytes(c), dtype=np.uint8).copy(), device="cuda")
+            out = torch.empty(n, dtype=torch.int32, device="cuda")
+            _kernels.check(lib.ppo_permutation(tmp.data_ptr(), 0, n, out.data_ptr(), _stream(torch)))
+            perms.append(out.cpu().numpy())
+        launches0 = ag.kernel_launches
+        ag.update(b["states"], b["actions"], rewards, lp, b["next_states"], b["dones"])
+        assert ag.kernel_launches - launches0 > epochs * 5 * 20  # the graph replays are counted
+        ora.update(b["states"], b["actions"], rewards, lp, b["next_states"], b["dones"], perms=perms)
+        torch.cuda.synchronize()
+        assert ag.read_ctrl().epoch == (it + 1) * epochs
+    for name, before, mine, theirs in (("actor", actor, ag.actor_state_dict(), ora.actor_state()),
+                                       ("critic", critic, ag.critic_state_dict(), ora.critic_state())):
+        for k, v in mine.items():
+            b0 = before[k].astype(np.float64)
+            np.testing.assert_allclose(v.numpy().astype(np.float64) - b0, theirs[k] - b0, atol=1.5e-5,
+                                       err_msg=f"{name}/{k}")
+
+
+def test_dropout_statistics_and_determinism(torch_cuda):
+    torch = torch_cuda
+    from diffusion_piano_b200.ppo import _kernels
+
+    lib = _kernels.load()
+    ctrl = torch.zeros(ctypes.sizeof(_kernels.PPOCtrl), dtype=torch.uint8, device="cuda")
+    _kernels.check(lib.ppo_ctrl_init(ctrl.data_ptr(), 9, 1e-4, 2e-4, _stream(torch)))
+    rows, H = 4096, 256
+    y = torch.randn(rows, H, device="cuda")
+    ones, zeros = torch.ones(H, device="cuda"), torch.zeros(H, device="cuda")
+    out, m1, m2, m3 = torch.empty_like(y), *(torch.empty(rows, H, dtype=torch.uint8, device="cuda") for _ in range(3))
+
+    def run(mask, stream_id):
+        _kernels.check(lib.ppo_relu_ln_fwd(y.data_ptr(), zeros.data_ptr(), ones.data_ptr(), zeros.data_ptr(),
+                                           out.data_ptr(), None, None, rows, H, 0.1, None, mask.data_ptr(),
+                                           ctrl.data_ptr(), stream_id, _stream(torch)))
+
+    run(m1, 1)
+    run(m2, 1)
+    assert torch.equal(m1, m2)  # same (seed, counter, stream): same mask
+    keep = m1.float().mean().item()
+    assert abs(keep - 0.9) < 2e-3
+    assert (out[m1 == 0] == 0).all()
+    run(m3, 2)
+    assert 0.75 < (m1 == m3).float().mean().item() < 0.9  # independent streams agree with probability 0.82
+    _kernels.check(lib.ppo_advance(ctrl.data_ptr(), 0, 0, _stream(torch)))
+    run(m2, 1)
+    assert 0.75 < (m1 == m2).float().mean().item() < 0.9  # new counter: new mask
+
+
+def test_plateau_kernel_matches_torch(torch_cuda):
+    torch = torch_cuda
+    from diffusion_piano_b200.ppo import _kernels
+    from oracle import ppo_oracle as po
+
+    lib = _kernels.load()
+    ctrl = torch.zeros(ctypes.sizeof(_kernels.PPOCtrl), dtype=torch.uint8, device="cuda")
+    _kernels.check(lib.ppo_ctrl_init(ctrl.data_ptr(), 0, 1e-4, 2e-4, _stream(torch)))
+    sa, sc = po.ReduceLROnPlateau("max", 0.5, 3), po.ReduceLROnPlateau("min", 0.5, 3)
+    lra, lrc = 1e-4, 2e-4
+    rs = np.random.RandomState(4)
+    for i in range(40):
+        c = _kernels.PPOCtrl.from_buffer_copy(ctrl.cpu().numpy().tobytes())
+        c.mean_reward_n = float(np.float32(-1.0 / (1 + i // 8) + 0.01 * rs.rand()))
+        c.critic_loss = float(np.float32(1.0 / (1 + i // 12) + 0.01 * rs.rand()))
+        ctrl.copy_(torch.as_tensor(np.frombuffer(bytes(c), dtype=np.uint8).copy()))
+        _kernels.check(lib.ppo_plateau_step(ctrl.data_ptr(), 0.5, 3, _stream(torch)))
+        lra, lrc = sa.step(c.mean_reward_n, lra), sc.step(c.critic_loss, lrc)
+        got = _kernels.PPOCtrl.from_buffer_copy(ctrl.cpu().numpy().tobytes())
+        np.testing.assert_allclose([got.lr[0], got.lr[1]], [lra, lrc], rtol=1e-6)
+    assert lra < 1e-4 and lrc < 2e-4  # both schedulers fired
+
+
+def test_train_loop_config4_smoke(torch_cuda):
+    """Config 4 in small: 'Crossing Field Cut 10s' (no usable fingering -> OT reward, obs without the fingering
+    block), the reference's loop for a few control steps; rewards stay finite, parameters move, and the
+    checkpoint round-trips."""
+    torch = torch_cuda
+    from diffusion_piano_b200 import music, suite
+    from diffusion_piano_b200.ppo import TrainConfig, train
+
+    task = suite.PianoWithShadowHands(music.load("CrossingFieldCut10s"), n_steps_lookahead=1, trim_silence=True)
+    env = suite.BatchedEnvironment(task, 256, canonical_actions=True, auto_reset=True)
+    cfg = TrainConfig(num_envs=256, num_episodes=1, batch_size=128, ppo_epochs=2, max_steps_per_episode=4)
+    agent, hist = train(env, cfg, log=lambda s: None)
+    st = agent.stats()
+    assert st["adam_steps"] == 4 * 2 * 2
+    assert np.isfinite(hist["mean_rewards"][0]) and np.isfinite(st["actor_loss"]) and np.isfinite(st["critic_loss"])
+    import tempfile
+
+    with tempfile.TemporaryDirectory() as d:
+        agent.checkpoint_dir = Path(d)
+        path = agent.save_checkpoint(0, hist)
+        from diffusion_piano_b200.ppo import PPOAgent
+
+        other = PPOAgent(env.obs_dim, env.action_dim, device="cuda:0", seed=99, checkpoint_dir=d)
+        other.load_checkpoint(path)
+        assert torch.equal(other.actor.theta, agent.actor.theta) and torch.equal(other.critic.m, agent.critic.m)
+        assert bytes(other.read_ctrl()) == bytes(agent.read_ctrl())
+    env.close()

@@ -1,0 +1,87 @@
+"""Config 4 timing (BASELINE.json configs[3]): 'Crossing Field Cut 10s', the reference's loop of
+select_actions -> env step -> PPO v2 update on the batch of that control step, all on the device.
+Prints one JSON line per phase breakdown; `python tools/bench_ppo.py --envs 4096 --steps 10`.
+Under torchrun every rank owns `--envs` envs and the gradients are all-reduced (NCCL)."""
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--envs", type=int, default=4096)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--epochs", type=int, default=10)
+    ap.add_argument("--batch-size", type=int, default=128)
+    ap.add_argument("--eager", action="store_true", help="no CUDA graphs (launch-bound comparison)")
+    args = ap.parse_args()
+    import torch
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    pg = None
+    if world > 1:
+        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
+        pg = torch.distributed.group.WORLD
+    from diffusion_piano_b200 import music, suite
+    from diffusion_piano_b200.ppo import PPOAgent
+
+    task = suite.PianoWithShadowHands(music.load("CrossingFieldCut10s"), n_steps_lookahead=1, trim_silence=True)
+    env = suite.BatchedEnvironment(task, args.envs, device=local, canonical_actions=True, auto_reset=True)
+    agent = PPOAgent(env.obs_dim, env.action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=args.batch_size,
+                     ppo_epochs=args.epochs, device=f"cuda:{local}", seed=0, process_group=pg,
+                     use_graphs=not args.eager)
+    n = args.envs
+    states = torch.empty((n, env.obs_dim), dtype=torch.float32, device=env.device)
+    obs = env.reset_device()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+    launches0 = 0
+    for it in range(args.warmup + args.steps):
+        if it == args.warmup:
+            if pg is not None:
+                torch.distributed.barrier()
+            torch.cuda.synchronize()
+            launches0 = agent.kernel_launches + env.engine.launch_count
+        e = ev[it - args.warmup] if it >= args.warmup else None
+        states.copy_(obs)
+        if e: e[0].record()
+        actions, logp = agent.select_actions(states)
+        if e: e[1].record()
+        obs, rewards, dones, _, _ = env.step_device(actions)
+        if e: e[2].record()
+        agent.update(states, actions, rewards, logp, obs, dones)
+        if e: e[3].record()
+    torch.cuda.synchronize()
+    launches = agent.kernel_launches + env.engine.launch_count - launches0
+    act = sum(a[0].elapsed_time(a[1]) for a in ev) / args.steps
+    step = sum(a[1].elapsed_time(a[2]) for a in ev) / args.steps
+    upd = sum(a[2].elapsed_time(a[3]) for a in ev) / args.steps
+    total = torch.tensor([ev[0][0].elapsed_time(ev[-1][3])], device=env.device)
+    if pg is not None:
+        torch.distributed.all_reduce(total, op=torch.distributed.ReduceOp.MAX)
+    total_ms = float(total.item())
+    mbs = args.epochs * ((n + args.batch_size - 1) // args.batch_size)
+    if rank == 0:
+        print(json.dumps({
+            "metric": "PPO v2 rollout+update env steps/sec (config 4)", "value": n * world * args.steps / (total_ms * 1e-3),
+            "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "phases_ms": {"select_actions": act, "env_step": step, "update": upd},
+            "minibatches_per_update": mbs, "us_per_minibatch": 1e3 * upd / mbs, "gpu_launches": launches,
+            "graphs": not args.eager, "stats": agent.stats(),
+            "config": {"workload": "PianoWithShadowHands 'Crossing Field Cut 10s', ppo_v2 update every control step",
+                       "envs_per_gpu": n, "batch_size": args.batch_size, "ppo_epochs": args.epochs,
+                       "obs_dim": env.obs_dim, "parallelism": f"env-sharded x{world}, gradient all-reduce per minibatch"}}))
+    if pg is not None:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
