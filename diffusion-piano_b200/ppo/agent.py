@@ -93,6 +93,7 @@ class _Net:
         self.device = device
         self.scratch = torch.zeros(3 * HIDDEN * 64 + 1024, dtype=torch.float32, device=device)
         self.ticket = torch.zeros(4, dtype=torch.int32, device=device)
+        self.wstream = torch.cuda.Stream(device=device)
         self.train: Dict[int, dict] = {}
 
     def _view(self, flat, k):
@@ -132,6 +133,7 @@ class PPOAgent:
         if not torch.cuda.is_available():
             raise _kernels.PPOKernelError("the PPO update runs on a CUDA device only (no CPU fallback)")
         self.lib = _kernels.load()
+        self.kernel_launches = 0  # launches of this library's kernels issued or replayed (bench accounting)
         self.device = torch.device(device if str(device) != "cuda" else f"cuda:{torch.cuda.current_device()}")
         self.state_dim, self.action_dim = int(state_dim), int(action_dim)
         self.gamma, self.epsilon, self.entropy_coef, self.value_coef = gamma, epsilon, entropy_coef, value_coef
@@ -158,7 +160,6 @@ class PPOAgent:
         self._side = torch.cuda.Stream(device=self.device)
         self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
         self._batch: Dict[int, dict] = {}
-        self.kernel_launches = 0  # launches of this library's kernels issued or replayed (bench accounting)
         self._launches_per_graph: Dict[tuple, int] = {}
 
     # ------------------------------------------------------------------ helpers
@@ -193,8 +194,12 @@ class PPOAgent:
 
     def _backward(self, net: _Net, x, buf, dz, p: float):
         """dz = gradient with respect to the last Linear's output; fills net.grad (except the head's bias)."""
+        chain = torch.cuda.current_stream(self.device)
+        wstream = net.wstream  # weight-gradient GEMMs leave the dependent chain dA -> LN backward -> dA ...
         li = net.linears[3]
-        torch.mm(dz.t(), buf["a"][2], out=net.g[f"network.{li}.weight"])
+        wstream.wait_stream(chain)
+        with torch.cuda.stream(wstream):
+            torch.mm(dz.t(), buf["a"][2], out=net.g[f"network.{li}.weight"])
         torch.mm(dz, net.p[f"network.{li}.weight"], out=buf["da"][2])
         for blk in (2, 1, 0):
             li, ni = net.linears[blk], net.norms[blk]
@@ -203,10 +208,14 @@ class PPOAgent:
                     net.p[f"network.{ni}.weight"], buf["mask"][blk] if use_p > 0 else None, use_p, buf["dy"][blk],
                     net.g[f"network.{li}.bias"], net.g[f"network.{ni}.weight"], net.g[f"network.{ni}.bias"],
                     net.scratch, net.ticket, x.shape[0], net.dims[blk + 1])
-            a_prev = x if blk == 0 else buf["a"][blk - 1]
-            torch.mm(buf["dy"][blk].t(), a_prev, out=net.g[f"network.{li}.weight"])
             if blk > 0:
+                wstream.wait_stream(chain)
+                with torch.cuda.stream(wstream):
+                    torch.mm(buf["dy"][blk].t(), buf["a"][blk - 1], out=net.g[f"network.{li}.weight"])
                 torch.mm(buf["dy"][blk], net.p[f"network.{li}.weight"], out=buf["da"][blk - 1])
+            else:
+                torch.mm(buf["dy"][blk].t(), x, out=net.g[f"network.{li}.weight"])
+        chain.wait_stream(wstream)
 
     def _optim_step(self, net: _Net, which: int):
         if self.world > 1:
@@ -246,6 +255,9 @@ class PPOAgent:
         with torch.cuda.stream(side):
             net = self.critic
             y4, buf = self._forward(net, mb["states"], True, self.dropout_p, masks, rng_stream=1)
+            # cursor / epoch / RNG counter were last read by the gather and the dropout above: bump them here,
+            # off the actor's (longer) chain
+            self._k(self.lib.ppo_advance, self.ctrl, n, B)
             self._k(self.lib.ppo_value_head, y4, net.p["network.11.bias"], mb["ret"], mb["dv"],
                     net.g["network.11.bias"], self.ctrl, B)
             self._backward(net, mb["states"], buf, mb["dv"], self.dropout_p)
@@ -258,7 +270,6 @@ class PPOAgent:
         self._backward(net, mb["states"], buf, mb["dz"], 0.0)
         self._optim_step(net, 0)
         main.wait_stream(side)
-        self._k(self.lib.ppo_advance, self.ctrl, n, B)
 
     def _replay_minibatch(self, bb, n, B, adv, returns):
         key = (n, B, adv.data_ptr(), returns.data_ptr())

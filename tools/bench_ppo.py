@@ -20,6 +20,9 @@ def main():
     ap.add_argument("--epochs", type=int, default=10)
     ap.add_argument("--batch-size", type=int, default=128)
     ap.add_argument("--eager", action="store_true", help="no CUDA graphs (launch-bound comparison)")
+    ap.add_argument("--impl", default="product", choices=["product", "torch", "torch-hostgae"],
+                    help="torch: plain-PyTorch restatement of ppo_v2.update (tools/torch_ppo_baseline.py) on the same env")
+    ap.add_argument("--blas", default=None, help="torch.backends.cuda.preferred_blas_library (cublas / cublaslt)")
     args = ap.parse_args()
     import torch
 
@@ -27,6 +30,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    if args.blas:
+        torch.backends.cuda.preferred_blas_library(args.blas)
     pg = None
     if world > 1:
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -36,9 +41,19 @@ def main():
 
     task = suite.PianoWithShadowHands(music.load("CrossingFieldCut10s"), n_steps_lookahead=1, trim_silence=True)
     env = suite.BatchedEnvironment(task, args.envs, device=local, canonical_actions=True, auto_reset=True)
-    agent = PPOAgent(env.obs_dim, env.action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=args.batch_size,
-                     ppo_epochs=args.epochs, device=f"cuda:{local}", seed=0, process_group=pg,
-                     use_graphs=not args.eager)
+    if args.impl == "product":
+        agent = PPOAgent(env.obs_dim, env.action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=args.batch_size,
+                         ppo_epochs=args.epochs, device=f"cuda:{local}", seed=0, process_group=pg,
+                         use_graphs=not args.eager)
+    else:
+        sys.path.insert(0, str(ROOT / "tools"))
+        from torch_ppo_baseline import TorchPPO
+
+        torch.manual_seed(0)
+        agent = TorchPPO(env.obs_dim, env.action_dim, batch_size=args.batch_size, ppo_epochs=args.epochs,
+                         device=f"cuda:{local}", python_gae=args.impl == "torch")
+        agent.kernel_launches = 0
+        agent.stats = lambda: {}
     n = args.envs
     states = torch.empty((n, env.obs_dim), dtype=torch.float32, device=env.device)
     obs = env.reset_device()
@@ -75,7 +90,7 @@ def main():
             "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "phases_ms": {"select_actions": act, "env_step": step, "update": upd},
             "minibatches_per_update": mbs, "us_per_minibatch": 1e3 * upd / mbs, "gpu_launches": launches,
-            "graphs": not args.eager, "stats": agent.stats(),
+            "impl": args.impl, "graphs": not args.eager, "stats": agent.stats(),
             "config": {"workload": "PianoWithShadowHands 'Crossing Field Cut 10s', ppo_v2 update every control step",
                        "envs_per_gpu": n, "batch_size": args.batch_size, "ppo_epochs": args.epochs,
                        "obs_dim": env.obs_dim, "parallelism": f"env-sharded x{world}, gradient all-reduce per minibatch"}}))
