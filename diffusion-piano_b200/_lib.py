@@ -9,8 +9,11 @@ from __future__ import annotations
 import ctypes
 from pathlib import Path
 
+import os
+
 _HERE = Path(__file__).resolve().parent
-LIB_PATH = _HERE / "libpiano_step.so"
+# PIANO_STEP_LIB: an alternative build of the same library (A/B measurements of kernel variants)
+LIB_PATH = Path(os.environ.get("PIANO_STEP_LIB") or _HERE / "libpiano_step.so")
 _lib = None
 
 c_void_p, c_int, c_float_p = ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_float)
@@ -27,6 +30,7 @@ class PPConfig(ctypes.Structure):
 TASK_SELF_ACTUATED_PIANO, TASK_PIANO_WITH_SHADOW_HANDS = 0, 1
 REWARD_NEGATIVE_L2, REWARD_NEGATIVE_XENT = 0, 1
 NUM_TERMS = 5
+SCHED_AUTO, SCHED_LOCKSTEP, SCHED_DIVERGENT = 0, 1, 2
 
 _SIGNATURES = {
     "pp_create": (c_int, [c_void_p, ctypes.POINTER(PPConfig), ctypes.POINTER(c_void_p)]),
@@ -47,6 +51,8 @@ _SIGNATURES = {
     "pp_get_metrics": (c_int, [c_void_p] * 4),
     "pp_get_diag": (c_int, [c_void_p] * 8),
     "pp_launch_count": (ctypes.c_longlong, [c_void_p]),
+    "pp_set_schedule": (c_int, [c_void_p, c_int]),
+    "pp_get_schedule": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "pp_last_error": (ctypes.c_char_p, []),
     "pp_version": (ctypes.c_char_p, []),
 }

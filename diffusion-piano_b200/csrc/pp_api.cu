@@ -24,6 +24,9 @@ static int fail(int code, const char* fmt, ...) {
     if (e_ != cudaSuccess) return fail(PP_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
   } while (0)
 
+// auto-tuning of the launch shape: full-batch steps SKIP .. SKIP+STEPS-1 alternate the two shapes under CUDA events
+constexpr int PP_TUNE_SKIP = 4, PP_TUNE_STEPS = 12;
+
 struct pp_env {
   pp_config cfg;
   int nv, nu, action_dim, obs_dim, nsite;
@@ -45,6 +48,11 @@ struct pp_env {
   std::vector<float> act_min, act_max;
   bool use_applied = false;
   long long launches = 0;
+  // launch shape (pp_set_schedule): envs per block and whether the envs are ordered by expected work
+  int sched_mode = PP_SCHED_AUTO, block_envs = 2, tune_calls = 0;
+  bool sort_work = false, tuned = false;
+  int* order = nullptr;  // [N]
+  cudaEvent_t tune_ev[2 * PP_TUNE_STEPS] = {};
   // host-buffer path
   cudaStream_t hstream = nullptr, hstream2 = nullptr;  // host-buffer calls: the batch is stepped in two halves
   cudaEvent_t h_ready = nullptr;                       // so that the first half's D2H overlaps the second half's step
@@ -309,6 +317,7 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(dalloc(&e->act_vel, (size_t)N * (e->nu ? e->nu : 1)));
   CUDA_OK(dalloc(&e->site_xpos, (size_t)N * 3 * PP_NSITE));
   CUDA_OK(dalloc(&e->activation, (size_t)N * 88)); CUDA_OK(dalloc(&e->counters, (size_t)N * 8));
+  CUDA_OK(dalloc(&e->order, (size_t)N));
   CUDA_OK(dalloc(&e->act_min_d, e->action_dim)); CUDA_OK(dalloc(&e->act_max_d, e->action_dim));
   CUDA_OK(cudaMemcpy(e->act_min_d, e->act_min.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
   CUDA_OK(cudaMemcpy(e->act_max_d, e->act_max.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
@@ -340,13 +349,14 @@ extern "C" int pp_destroy(pp_env* e) {
                  e->needs_reset, e->qacc, e->act_force, e->act_vel, e->site_xpos, e->activation, e->counters,
                  e->act_min_d, e->act_max_d, e->d_actions, e->d_obs, e->d_reward, e->d_terms, e->d_discount,
                  e->d_done, e->d_mask, e->hand_off, e->hand_off_pending, e->eval_sum, e->eval_episode,
-                 e->eval_steps, e->eval_count, e->stick_bits};
+                 e->eval_steps, e->eval_count, e->stick_bits, e->order};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
   for (void* p : host) if (p) cudaFreeHost(p);
   if (e->hstream) cudaStreamDestroy(e->hstream);
   if (e->hstream2) cudaStreamDestroy(e->hstream2);
   if (e->h_ready) cudaEventDestroy(e->h_ready);
+  for (auto ev : e->tune_ev) if (ev) cudaEventDestroy(ev);
   delete e;
   return PP_OK;
 }
@@ -356,6 +366,24 @@ extern "C" int pp_nv(const pp_env* e) { return e ? e->nv : 0; }
 extern "C" int pp_action_dim(const pp_env* e) { return e ? e->action_dim : 0; }
 extern "C" int pp_obs_dim(const pp_env* e) { return e ? e->obs_dim : 0; }
 extern "C" long long pp_launch_count(const pp_env* e) { return e ? e->launches : 0; }
+extern "C" int pp_set_schedule(pp_env* e, int mode) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  if (mode != PP_SCHED_AUTO && mode != PP_SCHED_LOCKSTEP && mode != PP_SCHED_DIVERGENT)
+    return fail(PP_ERR_INVALID, "schedule mode %d", mode);
+  e->sched_mode = mode;
+  e->tuned = mode != PP_SCHED_AUTO;
+  e->tune_calls = 0;
+  e->block_envs = mode == PP_SCHED_DIVERGENT ? 10 : 2;
+  e->sort_work = mode == PP_SCHED_DIVERGENT;
+  return PP_OK;
+}
+extern "C" int pp_get_schedule(const pp_env* e, int* mode, int* block_envs, int* sorted_by_work) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  if (mode) *mode = e->sched_mode;
+  if (block_envs) *block_envs = e->block_envs;
+  if (sorted_by_work) *sorted_by_work = e->sort_work ? 1 : 0;
+  return PP_OK;
+}
 extern "C" const char* pp_last_error(void) { return g_err.c_str(); }
 extern "C" const char* pp_version(void) { return "piano_step 0.1 (sm_100a)"; }
 extern "C" int pp_action_bounds(const pp_env* e, float* lo, float* hi) {
@@ -403,7 +431,42 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     A.act_vel = e->act_vel; A.site_xpos = e->site_xpos; A.activation = e->activation;
     A.counters = e->counters;
     A.eval = EvalAccum{e->eval_sum, e->eval_steps, e->eval_episode, e->eval_count};
-    e->launches += pp_launch_hands(A, s, env_begin, env_count) - 1;
+    const bool full = env_begin == 0 && (env_count < 0 || env_count == c.num_envs);
+    int block_envs = e->block_envs;
+    bool sort = e->sort_work && full && mode == PP_MODE_STEP;
+    int tune_slot = -1;
+    if (e->sched_mode == PP_SCHED_AUTO && !e->tuned && full && mode == PP_MODE_STEP) {
+      const int k = e->tune_calls++;
+      if (k >= PP_TUNE_SKIP && k < PP_TUNE_SKIP + PP_TUNE_STEPS) {
+        tune_slot = k - PP_TUNE_SKIP;
+        const bool divergent = tune_slot & 1;
+        block_envs = divergent ? 10 : 2;
+        sort = divergent;
+        if (!e->tune_ev[0])
+          for (auto& ev : e->tune_ev) cudaEventCreate(&ev);
+        cudaEventRecord(e->tune_ev[2 * tune_slot], s);
+      } else if (k == PP_TUNE_SKIP + PP_TUNE_STEPS) {
+        float t[2] = {0.f, 0.f};
+        cudaEventSynchronize(e->tune_ev[2 * PP_TUNE_STEPS - 1]);
+        for (int i = 0; i < PP_TUNE_STEPS; i++) {
+          float ms = 0.f;
+          cudaEventElapsedTime(&ms, e->tune_ev[2 * i], e->tune_ev[2 * i + 1]);
+          t[i & 1] += ms;
+        }
+        const bool divergent = t[1] < 0.97f * t[0];
+        e->block_envs = block_envs = divergent ? 10 : 2;
+        e->sort_work = divergent;
+        sort = divergent;
+        e->tuned = true;
+      }
+    }
+    if (sort) {
+      pp_launch_work_order(e->counters, e->order, c.num_envs, s);
+      e->launches++;
+      A.order = e->order;
+    }
+    e->launches += pp_launch_hands(A, s, env_begin, env_count, block_envs) - 1;
+    if (tune_slot >= 0) cudaEventRecord(e->tune_ev[2 * tune_slot + 1], s);
   }
   e->launches++;
   cudaError_t err = cudaGetLastError();

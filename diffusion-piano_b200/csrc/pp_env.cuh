@@ -51,10 +51,14 @@ struct HandsArgs {
   float *qacc, *act_force, *act_vel, *site_xpos;
   uint8_t* activation;
   int* counters;  // [N,8]
+  const int* order;  // [N] launch slot -> env (null: identity); envs of similar expected work share a block
   EvalAccum eval;  // musical metrics accumulators
 };
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);
 // launches the step for envs [env_begin, env_begin + env_count) (env_count < 0: to the end); returns the number of kernels
-int pp_launch_hands(const HandsArgs& A, cudaStream_t stream, int env_begin = 0, int env_count = -1);
+// block_envs: 2 (envs that do the same work at the same time) or 10 (envs that diverge: see pp_set_schedule)
+int pp_launch_hands(const HandsArgs& A, cudaStream_t stream, int env_begin = 0, int env_count = -1, int block_envs = 2);
+// order[slot] = env, by decreasing counters[env*8+4] (Newton iterations of the env's previous control step)
+void pp_launch_work_order(const int* counters, int* order, int num_envs, cudaStream_t stream);
 size_t pp_hands_smem_bytes();

@@ -545,7 +545,8 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WarpShared& W = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
-  const int env = env_base + blockIdx.x * WPB + (threadIdx.x >> 5);
+  const int slot_ = env_base + blockIdx.x * WPB + (threadIdx.x >> 5);
+  const int env = A.order ? A.order[slot_] : slot_;
   const DevModel& dm = *A.dm;
   const Options& o = dm.opt;
   const HandTables& ht = dm.hand;
@@ -1133,7 +1134,19 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       int iter = 0, ls_total = 0;
       const int maxit = min(o.iterations, 50);
       bool euler = false;
+#ifndef PP_TRIP_MEET
+#define PP_TRIP_MEET 1
+#endif
+      // The envs of a block also meet at the top of every trip (a finished env keeps arriving until all are):
+      // with different actions per env the warps of an SM would otherwise spread over the whole loop body and
+      // miss the instruction cache on most fetches (ncu, random actions: 51 % hit rate, 57 % of the stall
+      // samples "no instruction"; with the meeting the warps fetch the same stretch of code together).
+      bool fin = false;
       for (;;) {
+        if (PP_TRIP_MEET && WPB > 1 && meet) {
+          if (__syncthreads_and(fin)) break;
+          if (fin) continue;
+        }
         // ---- row forces and curvatures at the current point
         float ff[2] = {0.f, 0.f}, fc_[2] = {0.f, 0.f}, lf[2] = {0.f, 0.f}, lc[2] = {0.f, 0.f};
         int fz[2] = {0, 0};
@@ -1501,6 +1514,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
           for (int h = 0; h < 2; h++)
             if (L.dof) { const float x = Z[0][h * 26 + lane]; v[h] += o.h * x; q[h] += o.h * v[h]; }
           __syncwarp();
+          if (PP_TRIP_MEET && WPB > 1 && meet) { fin = true; continue; }
           break;
         }
         // ---- back-substitute the key slots touched by low-rank contacts in every solved vector
@@ -1937,10 +1951,40 @@ static int launch_wpb(const HandsArgs& A, cudaStream_t stream, int env_begin, in
 #ifndef PP_WPB
 #define PP_WPB 2
 #endif
-// envs per block; measured on B200 (env-steps/s, profiles/): 2 -> 871 k, 5 -> 665 k, 10 -> 696 k
+// envs per block, measured on B200 (profiles/):
+//   every env doing the same work (config 2 replay, env-steps/s): 2 -> 1 175 k, 5 -> 893 k, 10 -> 885 k
+//   different actions per env (config 3, B = 16384, ms per step):  2 -> 45.8, 5 -> 33.4, 10 -> 31.8
+// so both shapes are built and pp_set_schedule (or its auto-tuner) picks one per handle.
 constexpr int WARPS_PER_BLOCK = PP_WPB;
-int pp_launch_hands(const HandsArgs& A, cudaStream_t stream, int env_begin, int env_count) {
+constexpr int WARPS_PER_BLOCK_DIVERGENT = 10;
+int pp_launch_hands(const HandsArgs& A, cudaStream_t stream, int env_begin, int env_count, int block_envs) {
   if (env_count < 0) env_count = A.num_envs - env_begin;
+  if (block_envs >= WARPS_PER_BLOCK_DIVERGENT)
+    return launch_wpb<WARPS_PER_BLOCK_DIVERGENT>(A, stream, env_begin, env_count);
   return launch_wpb<WARPS_PER_BLOCK>(A, stream, env_begin, env_count);
+}
+
+// Counting sort of the envs by the Newton iterations of their previous control step, heaviest first: the envs of
+// a block then need similar numbers of trips (less waiting at the meetings) and the longest blocks start first.
+// The order only changes which block computes an env, never its result. One block; N up to a few 100 k.
+__global__ void __launch_bounds__(1024) pp_work_order_kernel(const int* __restrict__ counters, int* __restrict__ order,
+                                                            int n) {
+  __shared__ int hist[256], base[256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+  __syncthreads();
+  for (int e = threadIdx.x; e < n; e += blockDim.x) atomicAdd(&hist[min(max(counters[(size_t)e * 8 + 4], 0), 255)], 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int acc = 0;
+    for (int k = 255; k >= 0; k--) { base[k] = acc; acc += hist[k]; }
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < n; e += blockDim.x) {
+    const int k = min(max(counters[(size_t)e * 8 + 4], 0), 255);
+    order[atomicAdd(&base[k], 1)] = e;
+  }
+}
+void pp_launch_work_order(const int* counters, int* order, int num_envs, cudaStream_t stream) {
+  pp_work_order_kernel<<<1, 1024, 0, stream>>>(counters, order, num_envs);
 }
 size_t pp_hands_smem_bytes() { return sizeof(WarpShared); }

@@ -142,6 +142,12 @@ class PPOAgent:
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
+        # the two networks' gradient all-reduces sit on concurrent branches of the minibatch graph: each gets its
+        # own communicator so that neither can be ordered behind the other differently on different ranks
+        self.pg_nets = [process_group, process_group]
+        if self.world > 1:
+            ranks = torch.distributed.get_process_group_ranks(process_group)
+            self.pg_nets = [torch.distributed.new_group(ranks), torch.distributed.new_group(ranks)]
         h = HIDDEN
         self.actor = _Net((state_dim, h, h, h, action_dim), ACTOR_LINEARS, ACTOR_NORMS, (False, False, False),
                           {"log_std": action_dim}, self.device)
@@ -219,7 +225,7 @@ class PPOAgent:
 
     def _optim_step(self, net: _Net, which: int):
         if self.world > 1:
-            torch.distributed.all_reduce(net.grad, group=self.pg)
+            torch.distributed.all_reduce(net.grad, group=self.pg_nets[which])
         self._k(self.lib.ppo_grad_sumsq, net.grad, net.size, net.scratch, net.ticket[1:], self.ctrl, which)
         self._k(self.lib.ppo_clip_adam, net.theta, net.grad, net.m, net.v, net.size, self.ctrl, which,
                 self.max_grad_norm, 1.0 / self.world, 0.9, 0.999, 1e-5)
@@ -288,7 +294,8 @@ class PPOAgent:
                 t.copy_(v)
             before = self.kernel_launches
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            # thread_local: the NCCL watchdog thread may query events while this thread captures
+            with torch.cuda.graph(g, capture_error_mode="thread_local" if self.world > 1 else "global"):
                 self._minibatch(bb, n, B, adv, returns)
             self._launches_per_graph[key] = self.kernel_launches - before
             self.kernel_launches = before
@@ -363,6 +370,11 @@ class PPOAgent:
                 mb_index += 1
         self._k(self.lib.ppo_plateau_step, self.ctrl, 0.5, 100)
         return bb
+
+    def close(self):
+        """Drops the captured graphs (they hold NCCL kernels: release them before destroying the process group)."""
+        torch.cuda.synchronize(self.device)
+        self._graphs.clear()
 
     # ------------------------------------------------------------------ introspection / checkpoints
     def read_ctrl(self) -> _kernels.PPOCtrl:

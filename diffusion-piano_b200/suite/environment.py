@@ -20,7 +20,7 @@ from . import specs
 
 class BatchedEnvironment:
     def __init__(self, task, num_envs: int, device: int = 0, canonical_actions: bool = False,
-                 auto_reset: bool = True, max_contacts: int = 0, random_state=None):
+                 auto_reset: bool = True, max_contacts: int = 0, random_state=None, schedule: str = "auto"):
         import torch  # device memory + streams only
 
         self._torch = torch
@@ -31,6 +31,8 @@ class BatchedEnvironment:
         self._auto_reset = bool(auto_reset)
         cfg.max_contacts = max_contacts
         self.engine = BatchedPianoEngine(task.model, task.song, cfg)
+        if schedule != "auto":  # launch shape of the two-hands step (engine.set_schedule); never changes results
+            self.engine.set_schedule(schedule)
         self.device = torch.device("cuda", device)
         self.layout = task.observation_layout()
         self.obs_dim, self.action_dim = self.engine.obs_dim, self.engine.action_dim

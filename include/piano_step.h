@@ -122,6 +122,18 @@ int pp_get_diag(pp_env *env, float *qacc_dev, float *actuator_force_dev,
                 float *actuator_velocity_dev, float *site_xpos_dev, uint8_t *activation_dev,
                 int32_t *counters_dev, void *stream);
 
+/* Launch shape of the two-hands step. The step is one warp per env; how many envs share a thread block decides
+ * whether the warps of an SM walk through the (large) kernel together:
+ *   PP_SCHED_LOCKSTEP   2 envs per block - best when every env does the same work (replaying one action table);
+ *   PP_SCHED_DIVERGENT  10 envs per block, envs ordered by the Newton iterations of their previous step so that a
+ *                       block's envs need similar work - best when the actions differ per env (training, random
+ *                       actions; the reference's loop, parallelized_base_v2.py:116-166, is this case);
+ *   PP_SCHED_AUTO       (default) times both on full-batch steps 4..15 of the handle (CUDA events) and keeps the
+ *                       faster. Results are identical in every mode: an env's result never depends on its block. */
+enum { PP_SCHED_AUTO = 0, PP_SCHED_LOCKSTEP = 1, PP_SCHED_DIVERGENT = 2 };
+int pp_set_schedule(pp_env *env, int mode);
+int pp_get_schedule(const pp_env *env, int *mode, int *block_envs, int *sorted_by_work);
+
 /* number of kernels launched by this handle since creation (for bench's gpu_launches) */
 long long pp_launch_count(const pp_env *env);
 const char *pp_last_error(void);

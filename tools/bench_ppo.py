@@ -24,8 +24,12 @@ def main():
                     help="torch: plain-PyTorch restatement of ppo_v2.update (tools/torch_ppo_baseline.py) on the same env")
     ap.add_argument("--blas", default=None, help="torch.backends.cuda.preferred_blas_library (cublas / cublaslt)")
     args = ap.parse_args()
+    import faulthandler
+
     import torch
 
+    if os.environ.get("PPO_BENCH_DUMP_AFTER"):  # where is it stuck: Python stacks of every thread after N seconds
+        faulthandler.dump_traceback_later(int(os.environ["PPO_BENCH_DUMP_AFTER"]), exit=True)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -95,7 +99,14 @@ def main():
                        "envs_per_gpu": n, "batch_size": args.batch_size, "ppo_epochs": args.epochs,
                        "obs_dim": env.obs_dim, "parallelism": f"env-sharded x{world}, gradient all-reduce per minibatch"}}))
     if pg is not None:
-        torch.distributed.destroy_process_group()
+        # destroy_process_group() blocks when CUDA graphs that captured NCCL kernels were replayed on its
+        # communicators (seen on 2 x B200): release the graphs, meet at a barrier and leave without it
+        if hasattr(agent, "close"):
+            agent.close()
+        torch.distributed.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
