@@ -127,7 +127,7 @@ class PPOAgent:
     def __init__(self, state_dim, action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, entropy_coef=0.01, value_coef=1.0,
                  max_grad_norm=0.5, ppo_epochs=10, batch_size=64, device="cuda", checkpoint_dir="checkpoints",
                  use_wandb=False, seed: Optional[int] = 0, process_group=None, dropout_p: float = DROPOUT_P,
-                 use_graphs: bool = True):
+                 use_graphs: bool = True, graph_scope: str = "update"):
         if use_wandb:
             raise NotImplementedError("wandb logging is not part of the device path; read agent.stats() instead")
         if not torch.cuda.is_available():
@@ -139,6 +139,9 @@ class PPOAgent:
         self.gamma, self.epsilon, self.entropy_coef, self.value_coef = gamma, epsilon, entropy_coef, value_coef
         self.max_grad_norm, self.ppo_epochs, self.batch_size = max_grad_norm, ppo_epochs, batch_size
         self.lam, self.dropout_p, self.use_graphs = 0.95, float(dropout_p), use_graphs
+        if graph_scope not in ("update", "minibatch"):
+            raise ValueError("graph_scope must be 'update' or 'minibatch'")
+        self.graph_scope = graph_scope
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
@@ -277,30 +280,32 @@ class PPOAgent:
         self._optim_step(net, 0)
         main.wait_stream(side)
 
-    def _replay_minibatch(self, bb, n, B, adv, returns):
-        key = (n, B, adv.data_ptr(), returns.data_ptr())
+    def _replay(self, key, sizes, bb, n, adv, returns):
+        """Replays the CUDA graph of the minibatches `sizes` (one minibatch, or all of an update), capturing it on
+        first use."""
         if key not in self._graphs:
             # warm up once eagerly on a side stream (cuBLAS workspaces, lazy module loads), with the control
             # block and the parameters restored afterwards so the warm-up is not a training step
-            saved = [t.clone() for t in (self.ctrl, self.actor.theta, self.actor.m, self.actor.v, self.critic.theta,
-                                         self.critic.m, self.critic.v)]
+            state = (self.ctrl, self.actor.theta, self.actor.m, self.actor.v, self.critic.theta, self.critic.m,
+                     self.critic.v)
+            saved = [t.clone() for t in state]
             s = torch.cuda.Stream(device=self.device)
             s.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(s):
-                self._minibatch(bb, n, B, adv, returns)
+                for B in sorted(set(sizes)):
+                    self._minibatch(bb, n, B, adv, returns)
             torch.cuda.current_stream(self.device).wait_stream(s)
-            for t, v in zip((self.ctrl, self.actor.theta, self.actor.m, self.actor.v, self.critic.theta, self.critic.m,
-                             self.critic.v), saved):
+            for t, v in zip(state, saved):
                 t.copy_(v)
             before = self.kernel_launches
             g = torch.cuda.CUDAGraph()
             # thread_local: the NCCL watchdog thread may query events while this thread captures
             with torch.cuda.graph(g, capture_error_mode="thread_local" if self.world > 1 else "global"):
-                self._minibatch(bb, n, B, adv, returns)
+                for B in sizes:
+                    self._minibatch(bb, n, B, adv, returns)
             self._launches_per_graph[key] = self.kernel_launches - before
             self.kernel_launches = before
-            # capture does not execute: nothing to restore
-            self._graphs[key] = g
+            self._graphs[key] = g  # capture does not execute: nothing to restore
         self._graphs[key].replay()
         self.kernel_launches += self._launches_per_graph[key]
 
@@ -358,16 +363,17 @@ class PPOAgent:
         returns = bb["returns"][self.rank * n:(self.rank + 1) * n]
         self._k(self.lib.ppo_begin_update, self.ctrl)
         perm_t = None if perms is None else torch.as_tensor(np.asarray(perms), device=dev).to(torch.int32).contiguous()
-        mb_index = 0
-        for _ in range(self.ppo_epochs):
-            for start in range(0, n, self.batch_size):
-                B = min(self.batch_size, n - start)
-                if explicit or not self.use_graphs:
-                    masks = None if minibatch_masks is None else minibatch_masks[mb_index]
-                    self._minibatch(bb, n, B, adv, returns, perm_t, 0 if perm_t is None else perm_t.shape[0], masks)
-                else:
-                    self._replay_minibatch(bb, n, B, adv, returns)
-                mb_index += 1
+        sizes = [min(self.batch_size, n - start) for _ in range(self.ppo_epochs)
+                 for start in range(0, n, self.batch_size)]
+        if explicit or not self.use_graphs:
+            for mb_index, B in enumerate(sizes):
+                masks = None if minibatch_masks is None else minibatch_masks[mb_index]
+                self._minibatch(bb, n, B, adv, returns, perm_t, 0 if perm_t is None else perm_t.shape[0], masks)
+        elif self.graph_scope == "update":  # every minibatch of the update in one graph launch
+            self._replay((n, "update", adv.data_ptr(), returns.data_ptr()), sizes, bb, n, adv, returns)
+        else:
+            for B in sizes:
+                self._replay((n, B, adv.data_ptr(), returns.data_ptr()), [B], bb, n, adv, returns)
         self._k(self.lib.ppo_plateau_step, self.ctrl, 0.5, 100)
         return bb
 

@@ -291,7 +291,7 @@ def test_graph_update_matches_oracle(torch_cuda):
             perms.append(out.cpu().numpy())
         launches0 = ag.kernel_launches
         ag.update(b["states"], b["actions"], rewards, lp, b["next_states"], b["dones"])
-        assert ag.kernel_launches - launches0 > epochs * 5 * 20  # the graph replays are counted
+        assert ag.kernel_launches - launches0 > epochs * 5 * 20  # the kernels inside the replayed graph are counted
         ora.update(b["states"], b["actions"], rewards, lp, b["next_states"], b["dones"], perms=perms)
         torch.cuda.synchronize()
         assert ag.read_ctrl().epoch == (it + 1) * epochs
