@@ -1956,10 +1956,13 @@ static int launch_wpb(const HandsArgs& A, cudaStream_t stream, int env_begin, in
 //   different actions per env (config 3, B = 16384, ms per step):  2 -> 45.8, 5 -> 33.4, 10 -> 31.8
 // so both shapes are built and pp_set_schedule (or its auto-tuner) picks one per handle.
 constexpr int WARPS_PER_BLOCK = PP_WPB;
-constexpr int WARPS_PER_BLOCK_DIVERGENT = 10;
+#ifndef PP_WPB_DIVERGENT
+#define PP_WPB_DIVERGENT 10
+#endif
+constexpr int WARPS_PER_BLOCK_DIVERGENT = PP_WPB_DIVERGENT;
 int pp_launch_hands(const HandsArgs& A, cudaStream_t stream, int env_begin, int env_count, int block_envs) {
   if (env_count < 0) env_count = A.num_envs - env_begin;
-  if (block_envs >= WARPS_PER_BLOCK_DIVERGENT)
+  if (block_envs > WARPS_PER_BLOCK)
     return launch_wpb<WARPS_PER_BLOCK_DIVERGENT>(A, stream, env_begin, env_count);
   return launch_wpb<WARPS_PER_BLOCK>(A, stream, env_begin, env_count);
 }
