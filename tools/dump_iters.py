@@ -1,0 +1,26 @@
+"""Per-env solver counters over consecutive control steps of config 3 (analysis of the load imbalance inside a block).
+usage: python tools/dump_iters.py <envs> <steps> <out.npy>   -> int32 [steps, envs, 8]"""
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+import torch  # noqa: E402
+
+from diffusion_piano_b200 import music, suite  # noqa: E402
+
+B, steps, out = int(sys.argv[1]), int(sys.argv[2]), sys.argv[3]
+task = suite.PianoWithShadowHands(music.load("GurenNoYumiyaCut14s"), n_steps_lookahead=1, trim_silence=True)
+env = suite.BatchedEnvironment(task, B, canonical_actions=True, auto_reset=True, schedule="lockstep")
+g = torch.Generator(device="cuda")
+g.manual_seed(0)
+env.reset_device()
+cnt = torch.zeros((B, 8), dtype=torch.int32, device="cuda")
+rows = []
+for t in range(steps):
+    env.step_device(torch.rand((B, 45), device="cuda", generator=g) * 2 - 1)
+    env.engine.get_diag(counters=cnt)
+    rows.append(cnt.cpu().numpy().copy())
+np.save(out, np.asarray(rows))
