@@ -109,19 +109,20 @@ __global__ void __launch_bounds__(256) relu_ln_fwd_kernel(
     }
 }
 
-// Backward of the block: 32 rows per CTA (one per warp), column sums staged through shared memory, per-CTA
-// partials to scratch, the last CTA (ticket) adds the partials in CTA order.
-__global__ void __launch_bounds__(1024) relu_ln_bwd_kernel(
+// Backward of the block: 8 rows per CTA (one per warp), the three column sums of the CTA's rows staged through
+// shared memory in one pass, per-CTA partials to scratch, the last CTA (ticket) adds the partials in CTA order.
+constexpr int kBwdRows = 8;
+__global__ void __launch_bounds__(256) relu_ln_bwd_kernel(
     const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
     const float* __restrict__ gamma, const uint8_t* __restrict__ mask, float p, float* __restrict__ dy,
     float* __restrict__ dbias, float* __restrict__ dgamma, float* __restrict__ dbeta, float* scratch,
     uint32_t* ticket, int rows, int H) {
-  __shared__ float col[32][257];
+  __shared__ float col[3][kBwdRows][256];
   __shared__ bool is_last;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, row = blockIdx.x * 32 + warp;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, row = blockIdx.x * kBwdRows + warp;
   const int vpt = H >> 5;
   const bool live = row < rows;
-  float d_o[8], xh[8], dyv[8];
+  float d_o[8], xh[8], hv[8];
   float s1 = 0.f, s2 = 0.f, mu = 0.f, rstd = 0.f;
   const float keep_scale = 1.f / (1.f - p);
   if (live) {
@@ -130,14 +131,15 @@ __global__ void __launch_bounds__(1024) relu_ln_bwd_kernel(
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    d_o[j] = xh[j] = dyv[j] = 0.f;
+    d_o[j] = xh[j] = hv[j] = 0.f;
     if (j < vpt && live) {
       const int c = lane + 32 * j;
       const size_t i = (size_t)row * H + c;
       float g = dout[i];
       if (p > 0.f) g = mask[i] ? g * keep_scale : 0.f;
       d_o[j] = g;
-      xh[j] = (hbuf[i] - mu) * rstd;
+      hv[j] = hbuf[i];
+      xh[j] = (hv[j] - mu) * rstd;
       const float dx = g * gamma[c];
       s1 += dx;
       s2 += dx * xh[j];
@@ -147,25 +149,26 @@ __global__ void __launch_bounds__(1024) relu_ln_bwd_kernel(
   s2 = warp_sum(s2) / H;
 #pragma unroll
   for (int j = 0; j < 8; ++j)
-    if (j < vpt && live) {
+    if (j < vpt) {
       const int c = lane + 32 * j;
-      const size_t i = (size_t)row * H + c;
-      const float dh = rstd * (d_o[j] * gamma[c] - s1 - xh[j] * s2);
-      dyv[j] = hbuf[i] > 0.f ? dh : 0.f;
-      dy[i] = dyv[j];
+      float dyv = 0.f;
+      if (live) {
+        const float dh = rstd * (d_o[j] * gamma[c] - s1 - xh[j] * s2);
+        dyv = hv[j] > 0.f ? dh : 0.f;
+        dy[(size_t)row * H + c] = dyv;
+      }
+      col[0][warp][c] = dyv;             // -> dbias
+      col[1][warp][c] = d_o[j] * xh[j];  // -> dgamma
+      col[2][warp][c] = d_o[j];          // -> dbeta
     }
-  // three column sums over this CTA's 32 rows: dbias (dy), dgamma (dout * xhat), dbeta (dout)
+  __syncthreads();
   float* part = scratch + (size_t)blockIdx.x * 3 * H;
-  for (int which = 0; which < 3; ++which) {
-    __syncthreads();
+  if (threadIdx.x < H) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (j < vpt) col[warp][lane + 32 * j] = which == 0 ? dyv[j] : which == 1 ? d_o[j] * xh[j] : d_o[j];
-    __syncthreads();
-    if (threadIdx.x < H) {
+    for (int which = 0; which < 3; ++which) {
       float a = 0.f;
-#pragma unroll 8
-      for (int w = 0; w < 32; ++w) a += col[w][threadIdx.x];
+#pragma unroll
+      for (int w = 0; w < kBwdRows; ++w) a += col[which][w][threadIdx.x];
       part[which * H + threadIdx.x] = a;
     }
   }
@@ -177,7 +180,7 @@ __global__ void __launch_bounds__(1024) relu_ln_bwd_kernel(
   __threadfence();
   for (int i = threadIdx.x; i < 3 * H; i += blockDim.x) {
     float a = 0.f;
-    for (int b = 0; b < (int)gridDim.x; ++b) a += scratch[(size_t)b * 3 * H + i];
+    for (int b = 0; b < (int)gridDim.x; ++b) a += __ldcg(scratch + (size_t)b * 3 * H + i);
     float* dst = i < H ? dbias : i < 2 * H ? dgamma : dbeta;
     dst[i % H] = a;
   }
@@ -185,14 +188,18 @@ __global__ void __launch_bounds__(1024) relu_ln_bwd_kernel(
 }
 
 // ---------------------------------------------------------------- heads
-// Policy head, one CTA of 32 warps, warp per row (rows w, w+32, ...), lane owns action dims lane and lane+32.
-__global__ void __launch_bounds__(1024) policy_head_kernel(
+// Policy head: warp per row, 8 rows per CTA, lane owns action dims lane and lane+32. Column sums (d bias,
+// d log_std) and the loss scalars go through per-CTA partials and the last CTA (ticket), in CTA order.
+constexpr int kHeadRows = 8, kHeadPart = 130;  // partial record: 64 d-bias, 64 d-log_std, surrogate sum, ratio sum
+__global__ void __launch_bounds__(256) policy_head_kernel(
     const float* __restrict__ y4, const float* __restrict__ b4, const float* __restrict__ log_std,
     const float* __restrict__ actions, const float* __restrict__ old_logp, const float* __restrict__ adv,
     float clip_eps, float entropy_coef, float* __restrict__ dz, float* __restrict__ db4,
-    float* __restrict__ dlog_std, float* __restrict__ logp_out, ppo_ctrl* ctrl, int B, int A) {
-  __shared__ float col_b[32][65], col_s[32][65], red[32][2];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float* __restrict__ dlog_std, float* __restrict__ logp_out, ppo_ctrl* ctrl, float* scratch, uint32_t* ticket,
+    int B, int A) {
+  __shared__ float col_b[kHeadRows][64], col_s[kHeadRows][64], red[kHeadRows][2];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, row = blockIdx.x * kHeadRows + warp;
   float ls[2], inv_var[2], bb[2];
   bool has[2];
   float ent_row = 0.f;
@@ -207,7 +214,7 @@ __global__ void __launch_bounds__(1024) policy_head_kernel(
   }
   const float entropy = warp_sum(ent_row) / A;  // mean over [B, A] of a row-constant
   float acc_b[2] = {0.f, 0.f}, acc_s[2] = {0.f, 0.f}, acc_surr = 0.f, acc_ratio = 0.f;
-  for (int row = warp; row < B; row += 32) {
+  if (row < B) {
     float mu[2], diff[2], lp = 0.f;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -227,19 +234,17 @@ __global__ void __launch_bounds__(1024) policy_head_kernel(
     const float w1 = surr1 < surr2 ? 1.f : surr1 == surr2 ? 0.5f : 0.f;
     const float w2 = surr2 < surr1 ? 1.f : surr1 == surr2 ? 0.5f : 0.f;
     const float dlogp = -(w1 + (inside ? w2 : 0.f)) * a * ratio / B;
-    if (lane == 0) {
-      acc_surr += fminf(surr1, surr2);
-      acc_ratio += ratio;
-      if (logp_out != nullptr) logp_out[row] = lp;
-    }
+    acc_surr = fminf(surr1, surr2);
+    acc_ratio = ratio;
+    if (lane == 0 && logp_out != nullptr) logp_out[row] = lp;
 #pragma unroll
     for (int j = 0; j < 2; ++j)
       if (has[j]) {
         const float dmu = dlogp * diff[j] * inv_var[j];
         const float g = dmu * (1.f - mu[j] * mu[j]);
         dz[(size_t)row * A + lane + 32 * j] = g;
-        acc_b[j] += g;
-        acc_s[j] += dlogp * (diff[j] * diff[j] * inv_var[j] - 1.f);
+        acc_b[j] = g;
+        acc_s[j] = dlogp * (diff[j] * diff[j] * inv_var[j] - 1.f);
       }
   }
 #pragma unroll
@@ -252,26 +257,47 @@ __global__ void __launch_bounds__(1024) policy_head_kernel(
     red[warp][1] = acc_ratio;
   }
   __syncthreads();
-  if (threadIdx.x < A) {
+  float* part = scratch + (size_t)blockIdx.x * kHeadPart;
+  if (threadIdx.x < 64) {
     float sb = 0.f, ss = 0.f;
-    for (int w = 0; w < 32; ++w) {
+#pragma unroll
+    for (int w = 0; w < kHeadRows; ++w) {
       sb += col_b[w][threadIdx.x];
       ss += col_s[w][threadIdx.x];
     }
-    db4[threadIdx.x] = sb;
-    const float raw = log_std[threadIdx.x];
-    dlog_std[threadIdx.x] = (raw >= -20.f && raw <= 2.f) ? ss - entropy_coef / A : 0.f;
+    part[threadIdx.x] = sb;
+    part[64 + threadIdx.x] = ss;
+  } else if (threadIdx.x < 66) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kHeadRows; ++w) t += red[w][threadIdx.x - 64];
+    part[64 + threadIdx.x] = t;  // 128: surrogate sum, 129: ratio sum
   }
-  if (threadIdx.x == 0) {
-    float s = 0.f, r = 0.f;
-    for (int w = 0; w < 32; ++w) {
-      s += red[w][0];
-      r += red[w][1];
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  if (threadIdx.x < kHeadPart) {
+    float t = 0.f;
+    for (int b = 0; b < (int)gridDim.x; ++b) t += __ldcg(scratch + (size_t)b * kHeadPart + threadIdx.x);
+    const int c = threadIdx.x;
+    if (c < 64) {
+      if (c < A) db4[c] = t;
+    } else if (c < 128) {
+      if (c - 64 < A) {
+        const float raw = log_std[c - 64];
+        dlog_std[c - 64] = (raw >= -20.f && raw <= 2.f) ? t - entropy_coef / A : 0.f;
+      }
+    } else if (c == 128) {
+      ctrl->actor_loss = -t / B - entropy_coef * entropy;
+      ctrl->entropy = entropy;
+    } else {
+      ctrl->mean_ratio = t / B;
     }
-    ctrl->actor_loss = -s / B - entropy_coef * entropy;
-    ctrl->entropy = entropy;
-    ctrl->mean_ratio = r / B;
   }
+  if (threadIdx.x == 0) *ticket = 0;
 }
 
 __global__ void __launch_bounds__(1024) value_head_kernel(const float* __restrict__ y4, const float* __restrict__ b4,
@@ -493,48 +519,69 @@ __global__ void permutation_kernel(const ppo_ctrl* ctrl, uint32_t salt, int N, i
 }
 
 // ---------------------------------------------------------------- clip_grad_norm_ + Adam
-__global__ void __launch_bounds__(1024) grad_sumsq_kernel(const float* __restrict__ grad, int n, float* scratch,
-                                                          uint32_t* ticket, ppo_ctrl* ctrl, int which) {
-  __shared__ float red[32];
+__global__ void __launch_bounds__(256) grad_sumsq_kernel(const float* __restrict__ grad, int n, float* scratch,
+                                                         uint32_t* ticket, ppo_ctrl* ctrl, int which) {
+  __shared__ float red[8];
   __shared__ bool is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float s = 0.f;
-  for (int i = blockIdx.x * 1024 + threadIdx.x; i < n; i += gridDim.x * 1024) s += grad[i] * grad[i];
+  const int n4 = n >> 2;  // tensors are 16-byte aligned and padded with zeros to multiples of 4
+  const float4* g4 = reinterpret_cast<const float4*>(grad);
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < n4; i += gridDim.x * 256) {
+    const float4 g = g4[i];
+    s += g.x * g.x + g.y * g.y + g.z * g.z + g.w * g.w;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) { const float g = grad[(n4 << 2) + threadIdx.x]; s += g * g; }
   s = warp_sum(s);
   if (lane == 0) red[warp] = s;
   __syncthreads();
   if (threadIdx.x == 0) {
     float t = 0.f;
-    for (int w = 0; w < 32; ++w) t += red[w];
+    for (int w = 0; w < 8; ++w) t += red[w];
     scratch[blockIdx.x] = t;
     __threadfence();
     is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
   }
   __syncthreads();
-  if (!is_last || threadIdx.x != 0) return;
+  if (!is_last || warp != 0) return;
   __threadfence();
+  // fixed order: lane l adds partials l, l+32, ...; then a fixed butterfly
   float t = 0.f;
-  for (int b = 0; b < (int)gridDim.x; ++b) t += ((volatile float*)scratch)[b];
-  ctrl->norm2[which] = t;
-  ctrl->adam_t[which] += 1;
-  *ticket = 0;
+  for (int b = lane; b < (int)gridDim.x; b += 32) t += __ldcg(scratch + b);
+  t = warp_sum(t);
+  if (lane == 0) {
+    ctrl->norm2[which] = t;
+    ctrl->adam_t[which] += 1;
+    *ticket = 0;
+  }
 }
 
-__global__ void __launch_bounds__(256) clip_adam_kernel(float* __restrict__ theta, const float* __restrict__ grad,
-                                                        float* __restrict__ m, float* __restrict__ v, int n,
+__global__ void __launch_bounds__(256) clip_adam_kernel(float4* __restrict__ theta, const float4* __restrict__ grad,
+                                                        float4* __restrict__ m, float4* __restrict__ v, int n4,
                                                         const ppo_ctrl* ctrl, int which, float max_norm,
                                                         float grad_scale, float b1, float b2, float eps) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+  if (i >= n4) return;
   const float total = sqrtf(ctrl->norm2[which]) * grad_scale;
   const float coef = fminf(max_norm / (total + 1e-6f), 1.f) * grad_scale;
   const float t = (float)ctrl->adam_t[which];
-  const float bc1 = 1.f - powf(b1, t), bc2 = 1.f - powf(b2, t);
-  const float g = grad[i] * coef;
-  const float mi = b1 * m[i] + (1.f - b1) * g, vi = b2 * v[i] + (1.f - b2) * g * g;
-  m[i] = mi;
-  v[i] = vi;
-  theta[i] -= (ctrl->lr[which] / bc1) * mi / (sqrtf(vi) / sqrtf(bc2) + eps);
+  const float bc1 = 1.f - powf(b1, t), inv_sqrt_bc2 = 1.f / sqrtf(1.f - powf(b2, t));
+  const float step = ctrl->lr[which] / bc1;
+  const float4 g4 = grad[i];
+  float4 m4 = m[i], v4 = v[i], p4 = theta[i];
+  const float g[4] = {g4.x * coef, g4.y * coef, g4.z * coef, g4.w * coef};
+  float* mm = &m4.x;
+  float* vv = &v4.x;
+  float* pp = &p4.x;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    mm[k] = b1 * mm[k] + (1.f - b1) * g[k];
+    vv[k] = b2 * vv[k] + (1.f - b2) * g[k] * g[k];
+    pp[k] -= step * mm[k] / (sqrtf(vv[k]) * inv_sqrt_bc2 + eps);
+  }
+  m[i] = m4;
+  v[i] = v4;
+  theta[i] = p4;
 }
 
 // ---------------------------------------------------------------- control block
@@ -612,9 +659,9 @@ int ppo_relu_ln_bwd(const float* dout, const float* h, const float* stats, const
                     float dropout_p, float* dy, float* dbias, float* dgamma, float* dbeta, float* scratch,
                     uint32_t* ticket, int rows, int H, void* stream) {
   if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
-  if (rows <= 0 || rows > 2048) return invalid("rows must be in 1..2048 (scratch holds 64 CTA partials)");
+  if (rows <= 0 || rows > 2048) return invalid("rows must be in 1..2048 (scratch holds 256 CTA partials)");
   if (dropout_p > 0.f && mask == nullptr) return invalid("dropout backward needs the mask");
-  relu_ln_bwd_kernel<<<(rows + 31) / 32, 1024, 0, (cudaStream_t)stream>>>(dout, h, stats, gamma, mask, dropout_p, dy,
+  relu_ln_bwd_kernel<<<(rows + kBwdRows - 1) / kBwdRows, 256, 0, (cudaStream_t)stream>>>(dout, h, stats, gamma, mask, dropout_p, dy,
                                                                          dbias, dgamma, dbeta, scratch, ticket, rows,
                                                                          H);
   PPO_LAUNCH_CHECK("ppo_relu_ln_bwd");
@@ -622,11 +669,14 @@ int ppo_relu_ln_bwd(const float* dout, const float* h, const float* stats, const
 
 int ppo_policy_head(const float* y4, const float* b4, const float* log_std, const float* actions,
                     const float* old_logp, const float* adv, float clip_eps, float entropy_coef, float* dz,
-                    float* db4, float* dlog_std, float* logp_out, ppo_ctrl* ctrl, int B, int A, void* stream) {
+                    float* db4, float* dlog_std, float* logp_out, ppo_ctrl* ctrl, float* scratch, uint32_t* ticket,
+                    int B, int A, void* stream) {
   if (A <= 0 || A > 64) return invalid("action dim must be in 1..64");
   if (B <= 0) return invalid("B");
-  policy_head_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(y4, b4, log_std, actions, old_logp, adv, clip_eps,
-                                                          entropy_coef, dz, db4, dlog_std, logp_out, ctrl, B, A);
+  if (scratch == nullptr || ticket == nullptr) return invalid("scratch / ticket");
+  policy_head_kernel<<<(B + kHeadRows - 1) / kHeadRows, 256, 0, (cudaStream_t)stream>>>(
+      y4, b4, log_std, actions, old_logp, adv, clip_eps, entropy_coef, dz, db4, dlog_std, logp_out, ctrl, scratch,
+      ticket, B, A);
   PPO_LAUNCH_CHECK("ppo_policy_head");
 }
 
@@ -682,17 +732,23 @@ int ppo_permutation(const ppo_ctrl* ctrl, uint32_t perm_salt, int N, int32_t* ou
 int ppo_grad_sumsq(const float* grad, int n, float* scratch, uint32_t* ticket, ppo_ctrl* ctrl, int which,
                    void* stream) {
   if (n <= 0 || (which != 0 && which != 1)) return invalid("n / which");
-  int blocks = (n + 4095) / 4096;
-  if (blocks > 1024) blocks = 1024;
-  grad_sumsq_kernel<<<blocks, 1024, 0, (cudaStream_t)stream>>>(grad, n, scratch, ticket, ctrl, which);
+  if ((reinterpret_cast<uintptr_t>(grad) & 15) != 0) return invalid("grad must be 16-byte aligned");
+  int blocks = (n / 4 + 2 * 256 - 1) / (2 * 256);  // two float4 per thread
+  if (blocks > 592) blocks = 592;                  // 4 CTAs per SM
+  if (blocks < 1) blocks = 1;
+  grad_sumsq_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(grad, n, scratch, ticket, ctrl, which);
   PPO_LAUNCH_CHECK("ppo_grad_sumsq");
 }
 
 int ppo_clip_adam(float* theta, const float* grad, float* m, float* v, int n, const ppo_ctrl* ctrl, int which,
                   float max_norm, float grad_scale, float beta1, float beta2, float eps, void* stream) {
-  if (n <= 0 || (which != 0 && which != 1)) return invalid("n / which");
-  clip_adam_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(theta, grad, m, v, n, ctrl, which, max_norm,
-                                                                     grad_scale, beta1, beta2, eps);
+  if (n <= 0 || (n & 3) != 0 || (which != 0 && which != 1)) return invalid("n (a multiple of 4) / which");
+  if (((reinterpret_cast<uintptr_t>(theta) | reinterpret_cast<uintptr_t>(grad) | reinterpret_cast<uintptr_t>(m) |
+        reinterpret_cast<uintptr_t>(v)) & 15) != 0)
+    return invalid("theta / grad / m / v must be 16-byte aligned");
+  clip_adam_kernel<<<(n / 4 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<float4*>(theta), reinterpret_cast<const float4*>(grad), reinterpret_cast<float4*>(m),
+      reinterpret_cast<float4*>(v), n / 4, ctrl, which, max_norm, grad_scale, beta1, beta2, eps);
   PPO_LAUNCH_CHECK("ppo_clip_adam");
 }
 

@@ -27,7 +27,7 @@ _SIGNATURES = {
     "ppo_ctrl_init": (I, [P, U64, F, F, P]),
     "ppo_relu_ln_fwd": (I, [P, P, P, P, P, P, P, I, I, F, P, P, P, U32, P]),
     "ppo_relu_ln_bwd": (I, [P, P, P, P, P, F, P, P, P, P, P, P, I, I, P]),
-    "ppo_policy_head": (I, [P, P, P, P, P, P, F, F, P, P, P, P, P, I, I, P]),
+    "ppo_policy_head": (I, [P, P, P, P, P, P, F, F, P, P, P, P, P, P, P, I, I, P]),
     "ppo_value_head": (I, [P, P, P, P, P, P, I, P]),
     "ppo_add_bias": (I, [P, P, P, I, P]),
     "ppo_sample_actions": (I, [P, P, P, P, P, P, P, I, I, P]),

@@ -91,7 +91,7 @@ class _Net:
         self.p = {k: self._view(self.theta, k) for k in self.shapes}
         self.g = {k: self._view(self.grad, k) for k in self.shapes}
         self.device = device
-        self.scratch = torch.zeros(3 * HIDDEN * 64 + 1024, dtype=torch.float32, device=device)
+        self.scratch = torch.zeros(3 * HIDDEN * 256 + 1024, dtype=torch.float32, device=device)
         self.ticket = torch.zeros(4, dtype=torch.int32, device=device)
         self.wstream = torch.cuda.Stream(device=device)
         self.train: Dict[int, dict] = {}
@@ -275,7 +275,7 @@ class PPOAgent:
         y4, buf = self._forward(net, mb["states"], True)
         self._k(self.lib.ppo_policy_head, y4, net.p["network.9.bias"], net.p["log_std"], mb["actions"], mb["logp"],
                 mb["adv"], self.epsilon, self.entropy_coef, mb["dz"], net.g["network.9.bias"], net.g["log_std"],
-                mb["new_logp"], self.ctrl, B, self.action_dim)
+                mb["new_logp"], self.ctrl, net.scratch, net.ticket[2:], B, self.action_dim)
         self._backward(net, mb["states"], buf, mb["dz"], 0.0)
         self._optim_step(net, 0)
         main.wait_stream(side)

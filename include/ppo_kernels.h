@@ -70,16 +70,18 @@ int ppo_relu_ln_fwd(const float* y, const float* bias, const float* gamma, const
                     uint8_t* mask_out, const ppo_ctrl* ctrl_dev, uint32_t rng_stream, void* stream);
 
 /* dy = d/dy of the block above given dout; dbias/dgamma/dbeta [H] are OVERWRITTEN with the column sums.
- * rows <= 2048; scratch: >= 3 * H * ceil(rows/32) floats; ticket: one zero-initialised uint32 (left at zero). */
+ * rows <= 2048; scratch: >= 3 * H * ceil(rows/8) floats; ticket: one zero-initialised uint32 (left at zero). */
 int ppo_relu_ln_bwd(const float* dout, const float* h, const float* stats, const float* gamma,
                     const uint8_t* mask, float dropout_p, float* dy, float* dbias, float* dgamma, float* dbeta,
                     float* scratch, uint32_t* ticket, int rows, int H, void* stream);
 
 /* y4 [B,A] is the last Linear's output WITHOUT bias. Writes dz [B,A] (gradient of the actor loss with respect
- * to y4), db4 [A], dlog_std [A], optionally logp_out [B]; ctrl->actor_loss / entropy / mean_ratio. */
+ * to y4), db4 [A], dlog_std [A], optionally logp_out [B]; ctrl->actor_loss / entropy / mean_ratio.
+ * scratch: >= 130 * ceil(B/8) floats; ticket: one zero-initialised uint32 (left at zero). */
 int ppo_policy_head(const float* y4, const float* b4, const float* log_std, const float* actions,
                     const float* old_logp, const float* adv, float clip_eps, float entropy_coef, float* dz,
-                    float* db4, float* dlog_std, float* logp_out, ppo_ctrl* ctrl_dev, int B, int A, void* stream);
+                    float* db4, float* dlog_std, float* logp_out, ppo_ctrl* ctrl_dev, float* scratch,
+                    uint32_t* ticket, int B, int A, void* stream);
 
 /* y4 [B] without bias. dv [B] = 2 (v - ret) / B, db4 [1]; ctrl->critic_loss / mean_value. */
 int ppo_value_head(const float* y4, const float* b4, const float* returns, float* dv, float* db4,
@@ -111,10 +113,11 @@ int ppo_gather_minibatch(const float* states, const float* actions, const float*
 int ppo_permutation(const ppo_ctrl* ctrl_dev, uint32_t perm_salt, int N, int32_t* out, void* stream);
 
 /* ctrl->norm2[which] = sum(grad^2) (fixed-order two-level reduction); bumps ctrl->adam_t[which].
- * scratch >= 1024 floats, ticket as above. */
+ * grad 16-byte aligned; scratch >= 592 floats, ticket as above. */
 int ppo_grad_sumsq(const float* grad, int n, float* scratch, uint32_t* ticket, ppo_ctrl* ctrl_dev, int which,
                    void* stream);
-/* g = grad * grad_scale * min(1, max_norm / (sqrt(norm2) * grad_scale + 1e-6)); Adam(b1, b2, eps) with
+/* n a multiple of 4, buffers 16-byte aligned.
+ * g = grad * grad_scale * min(1, max_norm / (sqrt(norm2) * grad_scale + 1e-6)); Adam(b1, b2, eps) with
  * lr = ctrl->lr[which], t = ctrl->adam_t[which]. grad_scale = 1/world_size after a summing all-reduce. */
 int ppo_clip_adam(float* theta, const float* grad, float* m, float* v, int n, const ppo_ctrl* ctrl_dev, int which,
                   float max_norm, float grad_scale, float beta1, float beta2, float eps, void* stream);

@@ -67,7 +67,7 @@ def test_block_forward_backward_matches_oracle(torch_cuda):
         np.testing.assert_allclose(out.cpu().numpy(), o_ref, atol=2e-5)
         dy, db, dg, dbe = torch.empty_like(ty), torch.empty(H, device="cuda"), torch.empty(H, device="cuda"), \
             torch.empty(H, device="cuda")
-        scratch = torch.zeros(3 * H * ((rows + 31) // 32), device="cuda")
+        scratch = torch.zeros(3 * H * ((rows + 7) // 8), device="cuda")
         ticket = torch.zeros(1, dtype=torch.int32, device="cuda")
         for _ in range(2):  # twice: the ticket must be left at zero
             _kernels.check(lib.ppo_relu_ln_bwd(tdo.data_ptr(), h.data_ptr(), stats.data_ptr(), tg.data_ptr(),
@@ -108,9 +108,14 @@ def test_policy_head_matches_oracle(torch_cuda):
     dz, db4, dls, lp = torch.empty(B, A, device="cuda"), torch.empty(A, device="cuda"), torch.empty(A, device="cuda"), \
         torch.empty(B, device="cuda")
     tz, tb, tl, ta, to, tadv = d(z), d(b4), d(log_std), d(actions), d(old), d(adv)
-    _kernels.check(lib.ppo_policy_head(tz.data_ptr(), tb.data_ptr(), tl.data_ptr(), ta.data_ptr(), to.data_ptr(),
-                                       tadv.data_ptr(), 0.2, 0.01, dz.data_ptr(), db4.data_ptr(), dls.data_ptr(),
-                                       lp.data_ptr(), ctrl.data_ptr(), B, A, _stream(torch)))
+    scratch = torch.zeros(130 * ((B + 7) // 8), device="cuda")
+    ticket = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for _ in range(2):  # twice: the ticket must be left at zero
+        _kernels.check(lib.ppo_policy_head(tz.data_ptr(), tb.data_ptr(), tl.data_ptr(), ta.data_ptr(), to.data_ptr(),
+                                           tadv.data_ptr(), 0.2, 0.01, dz.data_ptr(), db4.data_ptr(), dls.data_ptr(),
+                                           lp.data_ptr(), ctrl.data_ptr(), scratch.data_ptr(), ticket.data_ptr(), B, A,
+                                           _stream(torch)))
+    assert int(ticket.item()) == 0
     c = _kernels.PPOCtrl.from_buffer_copy(ctrl.cpu().numpy().tobytes())
     np.testing.assert_allclose(lp.cpu().numpy(), logp, rtol=2e-5, atol=2e-4)
     # a ratio within float32 rounding of the clip edge may fall on the other side: compare all but those rows
@@ -303,7 +308,8 @@ def test_graph_update_matches_oracle(torch_cuda):
             # gradient into a fraction of a full step, so a few elements drift by multiples of the learning rate
             # while the bulk agrees to a few 1e-6
             err = np.abs(v.numpy().astype(np.float64) - theirs[k]).ravel()
-            assert np.quantile(err, 0.98) < 1.5e-5 and err.max() < 2e-3, (name, k, np.quantile(err, 0.98), err.max())
+            assert np.median(err) < 3e-6 and np.quantile(err, 0.98) < 5e-5 and err.max() < 2e-3, \
+                (name, k, np.median(err), np.quantile(err, 0.98), err.max())
 
 
 def test_dropout_statistics_and_determinism(torch_cuda):
