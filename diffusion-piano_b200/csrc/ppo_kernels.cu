@@ -109,82 +109,226 @@ __global__ void __launch_bounds__(256) relu_ln_fwd_kernel(
     }
 }
 
-// Backward of the block: 8 rows per CTA (one per warp), the three column sums of the CTA's rows staged through
-// shared memory in one pass, per-CTA partials to scratch, the last CTA (ticket) adds the partials in CTA order.
-constexpr int kBwdRows = 8;
-__global__ void __launch_bounds__(256) relu_ln_bwd_kernel(
+// Backward of the block, row part: dy (what the next dA GEMM waits for). Warp per row, 8 rows per CTA.
+__global__ void __launch_bounds__(256) relu_ln_bwd_dy_kernel(
     const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
-    const float* __restrict__ gamma, const uint8_t* __restrict__ mask, float p, float* __restrict__ dy,
-    float* __restrict__ dbias, float* __restrict__ dgamma, float* __restrict__ dbeta, float* scratch,
-    uint32_t* ticket, int rows, int H) {
-  __shared__ float col[3][kBwdRows][256];
-  __shared__ bool is_last;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, row = blockIdx.x * kBwdRows + warp;
+    const float* __restrict__ gamma, const uint8_t* __restrict__ mask, float p, float* __restrict__ dy, int rows,
+    int H) {
+  const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
   const int vpt = H >> 5;
-  const bool live = row < rows;
-  float d_o[8], xh[8], hv[8];
-  float s1 = 0.f, s2 = 0.f, mu = 0.f, rstd = 0.f;
-  const float keep_scale = 1.f / (1.f - p);
-  if (live) {
-    mu = stats[2 * row];
-    rstd = stats[2 * row + 1];
-  }
+  float dx[8], xh[8], hv[8];
+  float s1 = 0.f, s2 = 0.f;
+  const float keep_scale = 1.f / (1.f - p), mu = stats[2 * row], rstd = stats[2 * row + 1];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    d_o[j] = xh[j] = hv[j] = 0.f;
-    if (j < vpt && live) {
+  for (int j = 0; j < 8; ++j)
+    if (j < vpt) {
       const int c = lane + 32 * j;
       const size_t i = (size_t)row * H + c;
       float g = dout[i];
       if (p > 0.f) g = mask[i] ? g * keep_scale : 0.f;
-      d_o[j] = g;
       hv[j] = hbuf[i];
       xh[j] = (hv[j] - mu) * rstd;
-      const float dx = g * gamma[c];
-      s1 += dx;
-      s2 += dx * xh[j];
+      dx[j] = g * gamma[c];
+      s1 += dx[j];
+      s2 += dx[j] * xh[j];
     }
-  }
   s1 = warp_sum(s1) / H;
   s2 = warp_sum(s2) / H;
 #pragma unroll
   for (int j = 0; j < 8; ++j)
     if (j < vpt) {
-      const int c = lane + 32 * j;
-      float dyv = 0.f;
-      if (live) {
-        const float dh = rstd * (d_o[j] * gamma[c] - s1 - xh[j] * s2);
-        dyv = hv[j] > 0.f ? dh : 0.f;
-        dy[(size_t)row * H + c] = dyv;
+      const float dh = rstd * (dx[j] - s1 - xh[j] * s2);
+      dy[(size_t)row * H + lane + 32 * j] = hv[j] > 0.f ? dh : 0.f;
+    }
+}
+
+// Backward of the block, column part (off the dependent chain): d bias = sum dy, d gamma = sum dout * xhat,
+// d beta = sum dout. One CTA per 32 columns, 8 warps striding the rows, summed through shared memory in warp order.
+__global__ void __launch_bounds__(256) relu_ln_colsums_kernel(
+    const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
+    const uint8_t* __restrict__ mask, float p, const float* __restrict__ dy, float* __restrict__ dbias,
+    float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int H) {
+  __shared__ float red[3][8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, c = blockIdx.x * 32 + lane;
+  const float keep_scale = 1.f / (1.f - p);
+  float sb = 0.f, sg = 0.f, se = 0.f;
+  for (int r = warp; r < rows; r += 8) {
+    const size_t i = (size_t)r * H + c;
+    float g = dout[i];
+    if (p > 0.f) g = mask[i] ? g * keep_scale : 0.f;
+    sb += dy[i];
+    sg += g * ((hbuf[i] - stats[2 * r]) * stats[2 * r + 1]);
+    se += g;
+  }
+  red[0][warp][lane] = sb;
+  red[1][warp][lane] = sg;
+  red[2][warp][lane] = se;
+  __syncthreads();
+  if (warp < 3) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[warp][w][lane];
+    (warp == 0 ? dbias : warp == 1 ? dgamma : dbeta)[c] = t;
+  }
+}
+
+// ---------------------------------------------------------------- small-M fp32 GEMMs
+// The minibatch GEMMs are 128 x 256 x 256..329: cuBLAS answers them with a 32x32x16 SIMT kernel on 32 CTAs of two
+// warps, 4.7 - 8 us per call inside the graph (tools/microbench_chain.py) - most of a minibatch's 110 us. These
+// three kernels spread the same FFMA work over 100 - 250 CTAs with every global load coalesced and no shared-memory
+// staging of the big operand; fixed summation order (bit-reproducible).
+
+// C[M,N] = A[M,K] . B[N,K]^T (forward: activations x weight rows). One warp per 4 x 8 output tile, lanes along k:
+// both operands are read along their contiguous dimension; the 32 partial sums per lane are reduced by a
+// transposing butterfly (31 shuffles) that leaves output element l of the tile on lane l.
+__global__ void __launch_bounds__(128) gemm_nt_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
+                                                      float* __restrict__ C, int M, int N, int K) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int m0 = blockIdx.y * 4, n0 = blockIdx.x * 32 + warp * 8;
+  if (n0 >= N) return;
+  const float* ap[4];
+  const float* bp[8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) ap[i] = A + (size_t)min(m0 + i, M - 1) * K;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) bp[j] = Bm + (size_t)min(n0 + j, N - 1) * K;
+  float acc[32];
+#pragma unroll
+  for (int t = 0; t < 32; ++t) acc[t] = 0.f;
+#pragma unroll 2
+  for (int k0 = 0; k0 < K; k0 += 32) {
+    const int k = k0 + lane;
+    const bool ok = k < K;
+    float xv[4], wv[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) xv[i] = ok ? ap[i][k] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) wv[j] = ok ? bp[j][k] : 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i * 8 + j] = fmaf(xv[i], wv[j], acc[i * 8 + j]);
+  }
+#pragma unroll
+  for (int off = 16, n = 16; off >= 1; off >>= 1, n >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      if (t < n) {
+        const float send = up ? acc[t] : acc[t + n], keep = up ? acc[t + n] : acc[t];
+        acc[t] = keep + __shfl_xor_sync(0xffffffffu, send, off);
       }
-      col[0][warp][c] = dyv;             // -> dbias
-      col[1][warp][c] = d_o[j] * xh[j];  // -> dgamma
-      col[2][warp][c] = d_o[j];          // -> dbeta
+  }
+  const int mi = m0 + (lane >> 3), nj = n0 + (lane & 7);
+  if (mi < M && nj < N) C[(size_t)mi * N + nj] = acc[0];
+}
+
+// C[M,K] = A[M,N] . B[N,K] (dA = dY x W). CTA = 8 output rows x 32 output columns; lane = column k (B rows are read
+// coalesced), the 8 warps split the contraction index n, so that every warp has all its B loads in flight at once;
+// the 8 partial tiles are added through shared memory in warp order.
+__global__ void __launch_bounds__(256) gemm_nn_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
+                                                      float* __restrict__ C, int M, int N, int K) {
+  __shared__ __align__(16) float As[8][256];  // reused for the partial tiles [8 warps][8 rows][32 k]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int k = blockIdx.x * 32 + lane, m0 = blockIdx.y * 8;
+  const bool kok = k < K;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  for (int nb = 0; nb < N; nb += 256) {
+    const int nc = min(256, N - nb);
+    const int npw = (((nc + 7) >> 3) + 3) & ~3;  // n per warp, a multiple of 4
+    __syncthreads();
+    for (int t = threadIdx.x; t < 8 * 256; t += 256) {
+      const int i = t >> 8, n = t & 255;
+      As[i][n] = (n < nc && m0 + i < M) ? A[(size_t)(m0 + i) * N + nb + n] : 0.f;
     }
-  __syncthreads();
-  float* part = scratch + (size_t)blockIdx.x * 3 * H;
-  if (threadIdx.x < H) {
+    __syncthreads();
+    const int nlo = warp * npw;
+    if (kok && nlo < nc) {
+      const float* bcol = Bm + (size_t)(nb + nlo) * K + k;
+#pragma unroll 8
+      for (int nn = 0; nn < npw; nn += 4) {
+        float bv[4];
 #pragma unroll
-    for (int which = 0; which < 3; ++which) {
-      float a = 0.f;
+        for (int u = 0; u < 4; ++u) bv[u] = nlo + nn + u < nc ? bcol[(size_t)(nn + u) * K] : 0.f;
 #pragma unroll
-      for (int w = 0; w < kBwdRows; ++w) a += col[which][w][threadIdx.x];
-      part[which * H + threadIdx.x] = a;
+        for (int i = 0; i < 8; ++i) {
+          const float4 av = *reinterpret_cast<const float4*>(&As[i][nlo + nn]);
+          acc[i] = fmaf(av.x, bv[0], acc[i]);
+          acc[i] = fmaf(av.y, bv[1], acc[i]);
+          acc[i] = fmaf(av.z, bv[2], acc[i]);
+          acc[i] = fmaf(av.w, bv[3], acc[i]);
+        }
+      }
     }
   }
-  __threadfence();
   __syncthreads();
-  if (threadIdx.x == 0) is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  float* part = &As[0][0];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) part[(warp * 8 + i) * 32 + lane] = acc[i];
   __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  for (int i = threadIdx.x; i < 3 * H; i += blockDim.x) {
-    float a = 0.f;
-    for (int b = 0; b < (int)gridDim.x; ++b) a += __ldcg(scratch + (size_t)b * 3 * H + i);
-    float* dst = i < H ? dbias : i < 2 * H ? dgamma : dbeta;
-    dst[i % H] = a;
+  {
+    const int i = warp;  // 256 threads = 8 rows x 32 columns
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += part[(w * 8 + i) * 32 + lane];
+    if (kok && m0 + i < M) C[(size_t)(m0 + i) * K + k] = t;
   }
-  if (threadIdx.x == 0) *ticket = 0;
+}
+
+// C[N,K] = A[M,N]^T . B[M,K] (dW = dY^T x activations). CTA = 8 output rows n x 32 output columns k; lane = k (B rows
+// read coalesced), the 8 warps split the contraction index m; partial tiles added through shared memory.
+__global__ void __launch_bounds__(256) gemm_tn_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
+                                                      float* __restrict__ C, int M, int N, int K) {
+  __shared__ __align__(16) float As[256][8];  // reused for the partial tiles [8 warps][8 n][32 k]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int k = blockIdx.x * 32 + lane, n0 = blockIdx.y * 8;
+  const bool kok = k < K;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (int mb = 0; mb < M; mb += 256) {
+    const int mc = min(256, M - mb);
+    const int mpw = (mc + 7) >> 3;  // m per warp
+    __syncthreads();
+    for (int t = threadIdx.x; t < 256 * 8; t += 256) {
+      const int m = t >> 3, j = t & 7;
+      As[m][j] = (m < mc && n0 + j < N) ? A[(size_t)(mb + m) * N + n0 + j] : 0.f;
+    }
+    __syncthreads();
+    const int mlo = warp * mpw, mhi = min(mc, mlo + mpw);
+    if (kok) {
+      const float* bcol = Bm + (size_t)mb * K + k;
+#pragma unroll 8
+      for (int m = mlo; m < mhi; ++m) {
+        const float bv = bcol[(size_t)m * K];
+        const float4 a0 = *reinterpret_cast<const float4*>(&As[m][0]);
+        const float4 a1 = *reinterpret_cast<const float4*>(&As[m][4]);
+        acc[0] = fmaf(a0.x, bv, acc[0]);
+        acc[1] = fmaf(a0.y, bv, acc[1]);
+        acc[2] = fmaf(a0.z, bv, acc[2]);
+        acc[3] = fmaf(a0.w, bv, acc[3]);
+        acc[4] = fmaf(a1.x, bv, acc[4]);
+        acc[5] = fmaf(a1.y, bv, acc[5]);
+        acc[6] = fmaf(a1.z, bv, acc[6]);
+        acc[7] = fmaf(a1.w, bv, acc[7]);
+      }
+    }
+  }
+  __syncthreads();
+  float* part = &As[0][0];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[(warp * 8 + j) * 32 + lane] = acc[j];
+  __syncthreads();
+  {
+    const int j = warp;
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += part[(w * 8 + j) * 32 + lane];
+    if (kok && n0 + j < N) C[(size_t)(n0 + j) * K + k] = t;
+  }
 }
 
 // ---------------------------------------------------------------- heads
@@ -643,6 +787,22 @@ int ppo_ctrl_init(ppo_ctrl* c, uint64_t seed, float lr_actor, float lr_critic, v
   PPO_LAUNCH_CHECK("ppo_ctrl_init");
 }
 
+int ppo_gemm_nt(const float* A, const float* B, float* C, int M, int N, int K, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return invalid("gemm sizes");
+  gemm_nt_kernel<<<dim3((N + 31) / 32, (M + 3) / 4), 128, 0, (cudaStream_t)stream>>>(A, B, C, M, N, K);
+  PPO_LAUNCH_CHECK("ppo_gemm_nt");
+}
+int ppo_gemm_nn(const float* A, const float* B, float* C, int M, int N, int K, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return invalid("gemm sizes");
+  gemm_nn_kernel<<<dim3((K + 31) / 32, (M + 7) / 8), 256, 0, (cudaStream_t)stream>>>(A, B, C, M, N, K);
+  PPO_LAUNCH_CHECK("ppo_gemm_nn");
+}
+int ppo_gemm_tn(const float* A, const float* B, float* C, int M, int N, int K, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return invalid("gemm sizes");
+  gemm_tn_kernel<<<dim3((K + 31) / 32, (N + 7) / 8), 256, 0, (cudaStream_t)stream>>>(A, B, C, M, N, K);
+  PPO_LAUNCH_CHECK("ppo_gemm_tn");
+}
+
 int ppo_relu_ln_fwd(const float* y, const float* bias, const float* gamma, const float* beta, float* out,
                     float* h_save, float* stats, int rows, int H, float dropout_p, const uint8_t* mask_in,
                     uint8_t* mask_out, const ppo_ctrl* ctrl, uint32_t rng_stream, void* stream) {
@@ -655,16 +815,32 @@ int ppo_relu_ln_fwd(const float* y, const float* bias, const float* gamma, const
   PPO_LAUNCH_CHECK("ppo_relu_ln_fwd");
 }
 
-int ppo_relu_ln_bwd(const float* dout, const float* h, const float* stats, const float* gamma, const uint8_t* mask,
-                    float dropout_p, float* dy, float* dbias, float* dgamma, float* dbeta, float* scratch,
-                    uint32_t* ticket, int rows, int H, void* stream) {
+int ppo_relu_ln_bwd_dy(const float* dout, const float* h, const float* stats, const float* gamma, const uint8_t* mask,
+                       float dropout_p, float* dy, int rows, int H, void* stream) {
   if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
-  if (rows <= 0 || rows > 2048) return invalid("rows must be in 1..2048 (scratch holds 256 CTA partials)");
+  if (rows <= 0) return invalid("rows");
   if (dropout_p > 0.f && mask == nullptr) return invalid("dropout backward needs the mask");
-  relu_ln_bwd_kernel<<<(rows + kBwdRows - 1) / kBwdRows, 256, 0, (cudaStream_t)stream>>>(dout, h, stats, gamma, mask, dropout_p, dy,
-                                                                         dbias, dgamma, dbeta, scratch, ticket, rows,
-                                                                         H);
-  PPO_LAUNCH_CHECK("ppo_relu_ln_bwd");
+  relu_ln_bwd_dy_kernel<<<(rows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(dout, h, stats, gamma, mask, dropout_p, dy,
+                                                                         rows, H);
+  PPO_LAUNCH_CHECK("ppo_relu_ln_bwd_dy");
+}
+
+int ppo_relu_ln_colsums(const float* dout, const float* h, const float* stats, const uint8_t* mask, float dropout_p,
+                        const float* dy, float* dbias, float* dgamma, float* dbeta, int rows, int H, void* stream) {
+  if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
+  if (rows <= 0) return invalid("rows");
+  if (dropout_p > 0.f && mask == nullptr) return invalid("dropout backward needs the mask");
+  relu_ln_colsums_kernel<<<H / 32, 256, 0, (cudaStream_t)stream>>>(dout, h, stats, mask, dropout_p, dy, dbias, dgamma,
+                                                                  dbeta, rows, H);
+  PPO_LAUNCH_CHECK("ppo_relu_ln_colsums");
+}
+
+int ppo_relu_ln_bwd(const float* dout, const float* h, const float* stats, const float* gamma, const uint8_t* mask,
+                    float dropout_p, float* dy, float* dbias, float* dgamma, float* dbeta, int rows, int H,
+                    void* stream) {
+  int rc = ppo_relu_ln_bwd_dy(dout, h, stats, gamma, mask, dropout_p, dy, rows, H, stream);
+  if (rc != 0) return rc;
+  return ppo_relu_ln_colsums(dout, h, stats, mask, dropout_p, dy, dbias, dgamma, dbeta, rows, H, stream);
 }
 
 int ppo_policy_head(const float* y4, const float* b4, const float* log_std, const float* actions,

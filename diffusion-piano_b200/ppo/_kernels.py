@@ -25,8 +25,13 @@ _SIGNATURES = {
     "ppo_version": (ctypes.c_char_p, []),
     "ppo_ctrl_size": (I, []),
     "ppo_ctrl_init": (I, [P, U64, F, F, P]),
+    "ppo_gemm_nt": (I, [P, P, P, I, I, I, P]),
+    "ppo_gemm_nn": (I, [P, P, P, I, I, I, P]),
+    "ppo_gemm_tn": (I, [P, P, P, I, I, I, P]),
     "ppo_relu_ln_fwd": (I, [P, P, P, P, P, P, P, I, I, F, P, P, P, U32, P]),
-    "ppo_relu_ln_bwd": (I, [P, P, P, P, P, F, P, P, P, P, P, P, I, I, P]),
+    "ppo_relu_ln_bwd_dy": (I, [P, P, P, P, P, F, P, I, I, P]),
+    "ppo_relu_ln_colsums": (I, [P, P, P, P, F, P, P, P, P, I, I, P]),
+    "ppo_relu_ln_bwd": (I, [P, P, P, P, P, F, P, P, P, P, I, I, P]),
     "ppo_policy_head": (I, [P, P, P, P, P, P, F, F, P, P, P, P, P, P, P, I, I, P]),
     "ppo_value_head": (I, [P, P, P, P, P, P, I, P]),
     "ppo_add_bias": (I, [P, P, P, I, P]),

@@ -9,8 +9,9 @@ What differs from the reference, by design:
   two streams) is ONE CUDA graph, replayed `ppo_epochs * ceil(N / batch_size)` times; cursor, epoch, RNG
   counter, Adam step counts, learning rates, the plateau schedulers and the RunningMeanStd live in a device
   control block (`ppo_ctrl`, include/ppo_kernels.h).
-* GEMMs are cuBLAS SGEMM (fp32, as the reference's default `torch.backends.cuda.matmul.allow_tf32=False`);
-  every other operation is a hand-written kernel of libppo_kernels.so. No autograd is involved.
+* fp32 arithmetic as the reference's default (`torch.backends.cuda.matmul.allow_tf32=False`): the minibatch GEMMs
+  are this library's small-M FFMA kernels (cuBLAS needs 4.7 - 8 us for a 128-row SGEMM inside the graph), whole-batch
+  inference uses cuBLAS SGEMM, every other operation is a hand-written kernel of libppo_kernels.so. No autograd.
 * Shuffling is a keyed Feistel permutation computed in the gather kernel, dropout masks are Philox draws: the
   same distributions as the reference's, not the same streams (tests inject explicit permutations / masks).
 * Several GPUs (`process_group`): every rank steps its own env shard; the reward / value vectors are
@@ -93,7 +94,8 @@ class _Net:
         self.device = device
         self.scratch = torch.zeros(3 * HIDDEN * 256 + 1024, dtype=torch.float32, device=device)
         self.ticket = torch.zeros(4, dtype=torch.int32, device=device)
-        self.wstream = torch.cuda.Stream(device=device)
+        self.wstream = torch.cuda.Stream(device=device)  # weight-gradient GEMMs
+        self.cstream = torch.cuda.Stream(device=device)  # bias / LayerNorm parameter gradients (column sums)
         self.train: Dict[int, dict] = {}
 
     def _view(self, flat, k):
@@ -127,7 +129,7 @@ class PPOAgent:
     def __init__(self, state_dim, action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, entropy_coef=0.01, value_coef=1.0,
                  max_grad_norm=0.5, ppo_epochs=10, batch_size=64, device="cuda", checkpoint_dir="checkpoints",
                  use_wandb=False, seed: Optional[int] = 0, process_group=None, dropout_p: float = DROPOUT_P,
-                 use_graphs: bool = True, graph_scope: str = "update"):
+                 use_graphs: bool = True, graph_scope: str = "update", gemm: str = "custom"):
         if use_wandb:
             raise NotImplementedError("wandb logging is not part of the device path; read agent.stats() instead")
         if not torch.cuda.is_available():
@@ -142,6 +144,9 @@ class PPOAgent:
         if graph_scope not in ("update", "minibatch"):
             raise ValueError("graph_scope must be 'update' or 'minibatch'")
         self.graph_scope = graph_scope
+        if gemm not in ("custom", "cublas"):
+            raise ValueError("gemm must be 'custom' or 'cublas'")
+        self.gemm, self.small_m = gemm, 512
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
@@ -178,9 +183,28 @@ class PPOAgent:
         _kernels.check(fn(*conv, torch.cuda.current_stream(self.device).cuda_stream))
         self.kernel_launches += 1
 
+    # GEMMs: this library's small-M kernels for minibatches, cuBLAS (torch.mm) for whole-batch inference
+    def _mm_nt(self, a, b, out):  # out[M,N] = a[M,K] . b[N,K]^T
+        if self.gemm == "custom" and a.shape[0] <= self.small_m:
+            self._k(self.lib.ppo_gemm_nt, a, b, out, a.shape[0], b.shape[0], a.shape[1])
+        else:
+            torch.mm(a, b.t(), out=out)
+
+    def _mm_nn(self, a, b, out):  # out[M,K] = a[M,N] . b[N,K]
+        if self.gemm == "custom" and a.shape[0] <= self.small_m:
+            self._k(self.lib.ppo_gemm_nn, a, b, out, a.shape[0], a.shape[1], b.shape[1])
+        else:
+            torch.mm(a, b, out=out)
+
+    def _mm_tn(self, a, b, out):  # out[N,K] = a[M,N]^T . b[M,K]
+        if self.gemm == "custom" and a.shape[0] <= self.small_m:
+            self._k(self.lib.ppo_gemm_tn, a, b, out, a.shape[0], a.shape[1], b.shape[1])
+        else:
+            torch.mm(a.t(), b, out=out)
+
     def _block_fwd(self, net: _Net, blk: int, x, buf, training: bool, p: float, mask_in, rng_stream: int):
         li, ni = net.linears[blk], net.norms[blk]
-        torch.mm(x, net.p[f"network.{li}.weight"].t(), out=buf["y"][blk])
+        self._mm_nt(x, net.p[f"network.{li}.weight"], buf["y"][blk])
         use_p = p if net.dropout_after[blk] else 0.0
         self._k(self.lib.ppo_relu_ln_fwd, buf["y"][blk], net.p[f"network.{li}.bias"], net.p[f"network.{ni}.weight"],
                 net.p[f"network.{ni}.bias"], buf["a"][blk], buf["y"][blk] if training else None,
@@ -198,7 +222,7 @@ class PPOAgent:
             if masks is not None and net.dropout_after[blk]:
                 m, mi = masks[mi], mi + 1
             a = self._block_fwd(net, blk, a, buf, training, p, m, rng_stream)
-        torch.mm(a, net.p[f"network.{net.linears[3]}.weight"].t(), out=buf["y"][3])
+        self._mm_nt(a, net.p[f"network.{net.linears[3]}.weight"], buf["y"][3])
         return buf["y"][3], buf
 
     def _backward(self, net: _Net, x, buf, dz, p: float):
@@ -208,23 +232,28 @@ class PPOAgent:
         li = net.linears[3]
         wstream.wait_stream(chain)
         with torch.cuda.stream(wstream):
-            torch.mm(dz.t(), buf["a"][2], out=net.g[f"network.{li}.weight"])
-        torch.mm(dz, net.p[f"network.{li}.weight"], out=buf["da"][2])
+            self._mm_tn(dz, buf["a"][2], net.g[f"network.{li}.weight"])
+        self._mm_nn(dz, net.p[f"network.{li}.weight"], buf["da"][2])
         for blk in (2, 1, 0):
             li, ni = net.linears[blk], net.norms[blk]
             use_p = p if net.dropout_after[blk] else 0.0
-            self._k(self.lib.ppo_relu_ln_bwd, buf["da"][blk], buf["y"][blk], buf["stats"][blk],
-                    net.p[f"network.{ni}.weight"], buf["mask"][blk] if use_p > 0 else None, use_p, buf["dy"][blk],
-                    net.g[f"network.{li}.bias"], net.g[f"network.{ni}.weight"], net.g[f"network.{ni}.bias"],
-                    net.scratch, net.ticket, x.shape[0], net.dims[blk + 1])
+            mask = buf["mask"][blk] if use_p > 0 else None
+            self._k(self.lib.ppo_relu_ln_bwd_dy, buf["da"][blk], buf["y"][blk], buf["stats"][blk],
+                    net.p[f"network.{ni}.weight"], mask, use_p, buf["dy"][blk], x.shape[0], net.dims[blk + 1])
+            a_prev = x if blk == 0 else buf["a"][blk - 1]
+            # parameter gradients of the block leave the chain: column sums and the weight-gradient GEMM
+            wstream.wait_stream(chain)
+            net.cstream.wait_stream(chain)
+            with torch.cuda.stream(net.cstream):
+                self._k(self.lib.ppo_relu_ln_colsums, buf["da"][blk], buf["y"][blk], buf["stats"][blk], mask, use_p,
+                        buf["dy"][blk], net.g[f"network.{li}.bias"], net.g[f"network.{ni}.weight"],
+                        net.g[f"network.{ni}.bias"], x.shape[0], net.dims[blk + 1])
+            with torch.cuda.stream(wstream):
+                self._mm_tn(buf["dy"][blk], a_prev, net.g[f"network.{li}.weight"])
             if blk > 0:
-                wstream.wait_stream(chain)
-                with torch.cuda.stream(wstream):
-                    torch.mm(buf["dy"][blk].t(), buf["a"][blk - 1], out=net.g[f"network.{li}.weight"])
-                torch.mm(buf["dy"][blk], net.p[f"network.{li}.weight"], out=buf["da"][blk - 1])
-            else:
-                torch.mm(buf["dy"][blk].t(), x, out=net.g[f"network.{li}.weight"])
+                self._mm_nn(buf["dy"][blk], net.p[f"network.{li}.weight"], buf["da"][blk - 1])
         chain.wait_stream(wstream)
+        chain.wait_stream(net.cstream)
 
     def _optim_step(self, net: _Net, which: int):
         if self.world > 1:

@@ -61,6 +61,16 @@ int ppo_ctrl_size(void); /* sizeof(ppo_ctrl), for the binding's self-check */
  * RunningMeanStd (0, 1, 1e-4). */
 int ppo_ctrl_init(ppo_ctrl* ctrl_dev, uint64_t seed, float lr_actor, float lr_critic, void* stream);
 
+/* fp32 GEMMs for small M (a minibatch: 128 rows), row-major contiguous operands, fixed summation order. They
+ * replace the cuBLAS calls behind `nn.Linear` forward / backward (ppo_v2.py:54-63,79-92 through autograd) where
+ * cuBLAS picks a 32-CTA SIMT kernel; large M (whole-batch inference) stays on cuBLAS.
+ *   ppo_gemm_nt: C[M,N] = A[M,K] . B[N,K]^T    (forward:  activations x weight^T)
+ *   ppo_gemm_nn: C[M,K] = A[M,N] . B[N,K]      (backward: dA = dY x weight)
+ *   ppo_gemm_tn: C[N,K] = A[M,N]^T . B[M,K]    (backward: dW = dY^T x activations) */
+int ppo_gemm_nt(const float* A, const float* B, float* C, int M, int N, int K, void* stream);
+int ppo_gemm_nn(const float* A, const float* B, float* C, int M, int N, int K, void* stream);
+int ppo_gemm_tn(const float* A, const float* B, float* C, int M, int N, int K, void* stream);
+
 /* out = dropout(LayerNorm(relu(y + bias))); rows x H, H a multiple of 32 and <= 256. h_save (post-ReLU) and
  * stats [rows,2] = (mean, rstd) are what the backward needs (NULL at inference; h_save may alias y).
  * dropout_p > 0: keep-mask from mask_in [rows,H] bytes if given, else Philox(seed, rng_counter, rng_stream, i);
@@ -69,11 +79,18 @@ int ppo_relu_ln_fwd(const float* y, const float* bias, const float* gamma, const
                     float* h_save, float* stats, int rows, int H, float dropout_p, const uint8_t* mask_in,
                     uint8_t* mask_out, const ppo_ctrl* ctrl_dev, uint32_t rng_stream, void* stream);
 
-/* dy = d/dy of the block above given dout; dbias/dgamma/dbeta [H] are OVERWRITTEN with the column sums.
- * rows <= 2048; scratch: >= 3 * H * ceil(rows/8) floats; ticket: one zero-initialised uint32 (left at zero). */
+/* Backward of the block above given dout. ppo_relu_ln_bwd_dy writes dy [rows,H] (what the next dA GEMM waits
+ * for); ppo_relu_ln_colsums OVERWRITES dbias / dgamma / dbeta [H] with the column sums (it reads dy, so it runs
+ * after _dy - on another stream if the caller wants it off its dependent chain); ppo_relu_ln_bwd does both in
+ * order on one stream. Deterministic (fixed summation order). */
+int ppo_relu_ln_bwd_dy(const float* dout, const float* h, const float* stats, const float* gamma,
+                       const uint8_t* mask, float dropout_p, float* dy, int rows, int H, void* stream);
+int ppo_relu_ln_colsums(const float* dout, const float* h, const float* stats, const uint8_t* mask,
+                        float dropout_p, const float* dy, float* dbias, float* dgamma, float* dbeta, int rows,
+                        int H, void* stream);
 int ppo_relu_ln_bwd(const float* dout, const float* h, const float* stats, const float* gamma,
                     const uint8_t* mask, float dropout_p, float* dy, float* dbias, float* dgamma, float* dbeta,
-                    float* scratch, uint32_t* ticket, int rows, int H, void* stream);
+                    int rows, int H, void* stream);
 
 /* y4 [B,A] is the last Linear's output WITHOUT bias. Writes dz [B,A] (gradient of the actor loss with respect
  * to y4), db4 [A], dlog_std [A], optionally logp_out [B]; ctrl->actor_loss / entropy / mean_ratio.

@@ -67,20 +67,37 @@ def test_block_forward_backward_matches_oracle(torch_cuda):
         np.testing.assert_allclose(out.cpu().numpy(), o_ref, atol=2e-5)
         dy, db, dg, dbe = torch.empty_like(ty), torch.empty(H, device="cuda"), torch.empty(H, device="cuda"), \
             torch.empty(H, device="cuda")
-        scratch = torch.zeros(3 * H * ((rows + 7) // 8), device="cuda")
-        ticket = torch.zeros(1, dtype=torch.int32, device="cuda")
-        for _ in range(2):  # twice: the ticket must be left at zero
-            _kernels.check(lib.ppo_relu_ln_bwd(tdo.data_ptr(), h.data_ptr(), stats.data_ptr(), tg.data_ptr(),
-                                               tm.data_ptr() if p > 0 else None, p, dy.data_ptr(), db.data_ptr(),
-                                               dg.data_ptr(), dbe.data_ptr(), scratch.data_ptr(), ticket.data_ptr(),
-                                               rows, H, _stream(torch)))
+        _kernels.check(lib.ppo_relu_ln_bwd(tdo.data_ptr(), h.data_ptr(), stats.data_ptr(), tg.data_ptr(),
+                                           tm.data_ptr() if p > 0 else None, p, dy.data_ptr(), db.data_ptr(),
+                                           dg.data_ptr(), dbe.data_ptr(), rows, H, _stream(torch)))
         d_in = dout.astype(np.float64) * (mask / (1 - p) if p > 0 else 1.0)
         dx_ref, _, db_ref, dg_ref, dbe_ref = po._block_backward(d_in, cache, np.eye(H), gamma.astype(np.float64))
         np.testing.assert_allclose(dy.cpu().numpy(), dx_ref, atol=3e-5)
         np.testing.assert_allclose(db.cpu().numpy(), db_ref, atol=2e-4)
         np.testing.assert_allclose(dg.cpu().numpy(), dg_ref, atol=2e-4)
         np.testing.assert_allclose(dbe.cpu().numpy(), dbe_ref, atol=2e-4)
-        assert int(ticket.item()) == 0
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 329), (128, 45, 256), (44, 1, 128), (300, 128, 256), (7, 256, 57)])
+def test_small_m_gemms(torch_cuda, M, N, K):
+    """The three GEMM kernels against float64 matmul on ragged shapes (nt: forward, nn: dA, tn: dW)."""
+    torch = torch_cuda
+    from diffusion_piano_b200.ppo import _kernels
+
+    lib = _kernels.load()
+    gcpu = torch.Generator().manual_seed(M * 1000 + N)
+    a = torch.randn(M, K, generator=gcpu).cuda()
+    w = torch.randn(N, K, generator=gcpu).cuda()
+    dy = torch.randn(M, N, generator=gcpu).cuda()
+    y, da, dw = torch.full((M, N), 7.0, device="cuda"), torch.full((M, K), 7.0, device="cuda"), \
+        torch.full((N, K), 7.0, device="cuda")
+    _kernels.check(lib.ppo_gemm_nt(a.data_ptr(), w.data_ptr(), y.data_ptr(), M, N, K, _stream(torch)))
+    _kernels.check(lib.ppo_gemm_nn(dy.data_ptr(), w.data_ptr(), da.data_ptr(), M, N, K, _stream(torch)))
+    _kernels.check(lib.ppo_gemm_tn(dy.data_ptr(), a.data_ptr(), dw.data_ptr(), M, N, K, _stream(torch)))
+    a64, w64, dy64 = a.double(), w.double(), dy.double()
+    for got, ref in ((y, a64 @ w64.t()), (da, dy64 @ w64), (dw, dy64.t() @ a64)):
+        scale = ref.abs().max().item()
+        assert (got.double() - ref).abs().max().item() < 2e-6 * scale * max(1.0, (max(M, N, K) / 64) ** 0.5)
 
 
 def test_policy_head_matches_oracle(torch_cuda):

@@ -23,6 +23,8 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "torch", "torch-hostgae"],
                     help="torch: plain-PyTorch restatement of ppo_v2.update (tools/torch_ppo_baseline.py) on the same env")
     ap.add_argument("--graph-scope", default="update", choices=["update", "minibatch"])
+    ap.add_argument("--schedule", default="auto", choices=["auto", "lockstep", "divergent"])
+    ap.add_argument("--gemm", default="custom", choices=["custom", "cublas"])
     ap.add_argument("--blas", default=None, help="torch.backends.cuda.preferred_blas_library (cublas / cublaslt)")
     args = ap.parse_args()
     import faulthandler
@@ -45,11 +47,12 @@ def main():
     from diffusion_piano_b200.ppo import PPOAgent
 
     task = suite.PianoWithShadowHands(music.load("CrossingFieldCut10s"), n_steps_lookahead=1, trim_silence=True)
-    env = suite.BatchedEnvironment(task, args.envs, device=local, canonical_actions=True, auto_reset=True)
+    env = suite.BatchedEnvironment(task, args.envs, device=local, canonical_actions=True, auto_reset=True,
+                                   schedule=args.schedule)
     if args.impl == "product":
         agent = PPOAgent(env.obs_dim, env.action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=args.batch_size,
                          ppo_epochs=args.epochs, device=f"cuda:{local}", seed=0, process_group=pg,
-                         use_graphs=not args.eager, graph_scope=args.graph_scope)
+                         use_graphs=not args.eager, graph_scope=args.graph_scope, gemm=args.gemm)
     else:
         sys.path.insert(0, str(ROOT / "tools"))
         from torch_ppo_baseline import TorchPPO
@@ -95,7 +98,7 @@ def main():
             "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "phases_ms": {"select_actions": act, "env_step": step, "update": upd},
             "minibatches_per_update": mbs, "us_per_minibatch": 1e3 * upd / mbs, "gpu_launches": launches,
-            "impl": args.impl, "graphs": not args.eager, "stats": agent.stats(),
+            "impl": args.impl, "graphs": not args.eager, "schedule": env.engine.get_schedule(), "stats": agent.stats(),
             "config": {"workload": "PianoWithShadowHands 'Crossing Field Cut 10s', ppo_v2 update every control step",
                        "envs_per_gpu": n, "batch_size": args.batch_size, "ppo_epochs": args.epochs,
                        "obs_dim": env.obs_dim, "parallelism": f"env-sharded x{world}, gradient all-reduce per minibatch"}}))
