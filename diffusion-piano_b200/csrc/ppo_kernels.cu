@@ -278,6 +278,92 @@ __global__ void __launch_bounds__(256) gemm_nn_kernel(const float* __restrict__ 
   }
 }
 
+// LayerNorm / ReLU / dropout backward of a block fused with the dA GEMM that consumes it:
+// dy[M,H] = block_backward(dout, h, stats, gamma, mask) (as relu_ln_bwd_dy_kernel), C[M,K] = dy . B[H,K].
+// Same tiling as gemm_nn_kernel (8 rows x 32 columns per CTA); every CTA of a row block recomputes its 8 dy rows
+// straight into shared memory (warp per row), the CTA with blockIdx.x == 0 also stores them for the dW GEMM and
+// the column sums. Saves one dependent launch per block on the backward chain.
+__global__ void __launch_bounds__(256) ln_bwd_gemm_nn_kernel(
+    const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
+    const float* __restrict__ gamma, const uint8_t* __restrict__ mask, float p, float* __restrict__ dy,
+    const float* __restrict__ Bm, float* __restrict__ C, int M, int H, int K) {
+  __shared__ __align__(16) float As[8][256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int k = blockIdx.x * 32 + lane, m0 = blockIdx.y * 8;
+  const bool kok = k < K;
+  {
+    const int row = m0 + warp, vpt = H >> 5;
+    const bool live = row < M;
+    float dx[8], xh[8], hv[8];
+    float s1 = 0.f, s2 = 0.f;
+    const float keep_scale = 1.f / (1.f - p);
+    const float mu = live ? stats[2 * row] : 0.f, rstd = live ? stats[2 * row + 1] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      dx[j] = xh[j] = hv[j] = 0.f;
+      if (j < vpt && live) {
+        const int c = lane + 32 * j;
+        const size_t i = (size_t)row * H + c;
+        float g = dout[i];
+        if (p > 0.f) g = mask[i] ? g * keep_scale : 0.f;
+        hv[j] = hbuf[i];
+        xh[j] = (hv[j] - mu) * rstd;
+        dx[j] = g * gamma[c];
+        s1 += dx[j];
+        s2 += dx[j] * xh[j];
+      }
+    }
+    s1 = warp_sum(s1) / H;
+    s2 = warp_sum(s2) / H;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = lane + 32 * j;
+      float v = 0.f;
+      if (j < vpt && live) {
+        const float dh = rstd * (dx[j] - s1 - xh[j] * s2);
+        v = hv[j] > 0.f ? dh : 0.f;
+        if (blockIdx.x == 0) dy[(size_t)row * H + c] = v;
+      }
+      As[warp][c] = v;  // columns >= H are zero
+    }
+  }
+  __syncthreads();
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  const int npw = (((H + 7) >> 3) + 3) & ~3;
+  const int nlo = warp * npw;
+  if (kok && nlo < H) {
+    const float* bcol = Bm + (size_t)nlo * K + k;
+#pragma unroll 8
+    for (int nn = 0; nn < npw; nn += 4) {
+      float bv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) bv[u] = nlo + nn + u < H ? bcol[(size_t)(nn + u) * K] : 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float4 av = *reinterpret_cast<const float4*>(&As[i][nlo + nn]);
+        acc[i] = fmaf(av.x, bv[0], acc[i]);
+        acc[i] = fmaf(av.y, bv[1], acc[i]);
+        acc[i] = fmaf(av.z, bv[2], acc[i]);
+        acc[i] = fmaf(av.w, bv[3], acc[i]);
+      }
+    }
+  }
+  __syncthreads();
+  float* part = &As[0][0];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) part[(warp * 8 + i) * 32 + lane] = acc[i];
+  __syncthreads();
+  {
+    const int i = warp;
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += part[(w * 8 + i) * 32 + lane];
+    if (kok && m0 + i < M) C[(size_t)(m0 + i) * K + k] = t;
+  }
+}
+
 // C[N,K] = A[M,N]^T . B[M,K] (dW = dY^T x activations). CTA = 8 output rows n x 32 output columns k; lane = k (B rows
 // read coalesced), the 8 warps split the contraction index m; partial tiles added through shared memory.
 __global__ void __launch_bounds__(256) gemm_tn_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
@@ -823,6 +909,16 @@ int ppo_relu_ln_bwd_dy(const float* dout, const float* h, const float* stats, co
   relu_ln_bwd_dy_kernel<<<(rows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(dout, h, stats, gamma, mask, dropout_p, dy,
                                                                          rows, H);
   PPO_LAUNCH_CHECK("ppo_relu_ln_bwd_dy");
+}
+
+int ppo_ln_bwd_gemm_nn(const float* dout, const float* h, const float* stats, const float* gamma, const uint8_t* mask,
+                       float dropout_p, float* dy, const float* W, float* dA, int rows, int H, int K, void* stream) {
+  if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
+  if (rows <= 0 || K <= 0) return invalid("rows / K");
+  if (dropout_p > 0.f && mask == nullptr) return invalid("dropout backward needs the mask");
+  ln_bwd_gemm_nn_kernel<<<dim3((K + 31) / 32, (rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
+      dout, h, stats, gamma, mask, dropout_p, dy, W, dA, rows, H, K);
+  PPO_LAUNCH_CHECK("ppo_ln_bwd_gemm_nn");
 }
 
 int ppo_relu_ln_colsums(const float* dout, const float* h, const float* stats, const uint8_t* mask, float dropout_p,

@@ -30,6 +30,7 @@ _SIGNATURES = {
     "ppo_gemm_tn": (I, [P, P, P, I, I, I, P]),
     "ppo_relu_ln_fwd": (I, [P, P, P, P, P, P, P, I, I, F, P, P, P, U32, P]),
     "ppo_relu_ln_bwd_dy": (I, [P, P, P, P, P, F, P, I, I, P]),
+    "ppo_ln_bwd_gemm_nn": (I, [P, P, P, P, P, F, P, P, P, I, I, I, P]),
     "ppo_relu_ln_colsums": (I, [P, P, P, P, F, P, P, P, P, I, I, P]),
     "ppo_relu_ln_bwd": (I, [P, P, P, P, P, F, P, P, P, P, I, I, P]),
     "ppo_policy_head": (I, [P, P, P, P, P, P, F, F, P, P, P, P, P, P, P, I, I, P]),

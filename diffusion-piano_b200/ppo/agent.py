@@ -238,8 +238,14 @@ class PPOAgent:
             li, ni = net.linears[blk], net.norms[blk]
             use_p = p if net.dropout_after[blk] else 0.0
             mask = buf["mask"][blk] if use_p > 0 else None
-            self._k(self.lib.ppo_relu_ln_bwd_dy, buf["da"][blk], buf["y"][blk], buf["stats"][blk],
-                    net.p[f"network.{ni}.weight"], mask, use_p, buf["dy"][blk], x.shape[0], net.dims[blk + 1])
+            fused = blk > 0 and self.gemm == "custom" and x.shape[0] <= self.small_m
+            if fused:  # dy of this block and dA for the block below in one launch
+                self._k(self.lib.ppo_ln_bwd_gemm_nn, buf["da"][blk], buf["y"][blk], buf["stats"][blk],
+                        net.p[f"network.{ni}.weight"], mask, use_p, buf["dy"][blk], net.p[f"network.{li}.weight"],
+                        buf["da"][blk - 1], x.shape[0], net.dims[blk + 1], net.dims[blk])
+            else:
+                self._k(self.lib.ppo_relu_ln_bwd_dy, buf["da"][blk], buf["y"][blk], buf["stats"][blk],
+                        net.p[f"network.{ni}.weight"], mask, use_p, buf["dy"][blk], x.shape[0], net.dims[blk + 1])
             a_prev = x if blk == 0 else buf["a"][blk - 1]
             # parameter gradients of the block leave the chain: column sums and the weight-gradient GEMM
             wstream.wait_stream(chain)
@@ -250,7 +256,7 @@ class PPOAgent:
                         net.g[f"network.{ni}.bias"], x.shape[0], net.dims[blk + 1])
             with torch.cuda.stream(wstream):
                 self._mm_tn(buf["dy"][blk], a_prev, net.g[f"network.{li}.weight"])
-            if blk > 0:
+            if blk > 0 and not fused:
                 self._mm_nn(buf["dy"][blk], net.p[f"network.{li}.weight"], buf["da"][blk - 1])
         chain.wait_stream(wstream)
         chain.wait_stream(net.cstream)

@@ -85,6 +85,12 @@ int ppo_relu_ln_fwd(const float* y, const float* bias, const float* gamma, const
  * order on one stream. Deterministic (fixed summation order). */
 int ppo_relu_ln_bwd_dy(const float* dout, const float* h, const float* stats, const float* gamma,
                        const uint8_t* mask, float dropout_p, float* dy, int rows, int H, void* stream);
+/* ppo_relu_ln_bwd_dy fused with the dA GEMM of the Linear below the block: dy [rows,H] as above, and
+ * dA [rows,K] = dy . W with W [H,K] the weight of this block's own Linear (the gradient flowing to the block
+ * below). One dependent launch instead of two. */
+int ppo_ln_bwd_gemm_nn(const float* dout, const float* h, const float* stats, const float* gamma,
+                       const uint8_t* mask, float dropout_p, float* dy, const float* W, float* dA, int rows, int H,
+                       int K, void* stream);
 int ppo_relu_ln_colsums(const float* dout, const float* h, const float* stats, const uint8_t* mask,
                         float dropout_p, const float* dy, float* dbias, float* dgamma, float* dbeta, int rows,
                         int H, void* stream);
