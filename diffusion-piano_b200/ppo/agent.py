@@ -29,7 +29,7 @@ from typing import Dict, List, Optional, Sequence
 import numpy as np
 import torch
 
-from . import _kernels
+from . import _kernels, dist
 
 HIDDEN = 256
 ACTOR_LINEARS, ACTOR_NORMS = (0, 3, 6, 9), (2, 5, 8)
@@ -385,17 +385,14 @@ class PPOAgent:
             y4, _ = self._forward(self.critic, x, False, p, masks, rng_stream=rs)
             self._k(self.lib.ppo_add_bias, y4, self.critic.p["network.11.bias"], packed[row], n)
         if self.world > 1:
-            torch.distributed.all_gather_into_tensor(bb["gathered"].view(-1), packed.view(-1), group=self.pg)
-            glob = bb["glob"].view(4, self.world, n)
-            glob.copy_(bb["gathered"].permute(1, 0, 2))
-            glob = bb["glob"]
+            glob = dist.gather_global_batch(packed, bb["gathered"], bb["glob"], self.pg)
         else:
             glob = packed
         ng = n * self.world
         self._k(self.lib.ppo_prepare_batch, glob[0], glob[1], glob[2], glob[3], self.gamma, self.lam, bb["rewards_n"],
                 bb["returns"], bb["adv_raw"], bb["adv"], self.ctrl, ng)
-        adv = bb["adv"][self.rank * n:(self.rank + 1) * n]
-        returns = bb["returns"][self.rank * n:(self.rank + 1) * n]
+        mine = dist.shard_slice(self.rank, n)
+        adv, returns = bb["adv"][mine], bb["returns"][mine]
         self._k(self.lib.ppo_begin_update, self.ctrl)
         perm_t = None if perms is None else torch.as_tensor(np.asarray(perms), device=dev).to(torch.int32).contiguous()
         sizes = [min(self.batch_size, n - start) for _ in range(self.ppo_epochs)
