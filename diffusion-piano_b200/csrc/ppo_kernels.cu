@@ -421,12 +421,16 @@ __global__ void __launch_bounds__(256) gemm_tn_kernel(const float* __restrict__ 
 // Policy head: warp per row, 8 rows per CTA, lane owns action dims lane and lane+32. Column sums (d bias,
 // d log_std) and the loss scalars go through per-CTA partials and the last CTA (ticket), in CTA order.
 constexpr int kHeadRows = 8, kHeadPart = 130;  // partial record: 64 d-bias, 64 d-log_std, surrogate sum, ratio sum
+// FUSED: the last Linear and its dA are computed here as well - z = a3 . W4^T with lanes along the H3 inputs and
+// a transposing butterfly that leaves z[lane] and z[lane+32] on the lane, dA3 = dz . W4 with dz broadcast by
+// shuffles - so that the chain Linear -> head -> dA GEMM is one launch.
+template <bool FUSED>
 __global__ void __launch_bounds__(256) policy_head_kernel(
     const float* __restrict__ y4, const float* __restrict__ b4, const float* __restrict__ log_std,
     const float* __restrict__ actions, const float* __restrict__ old_logp, const float* __restrict__ adv,
     float clip_eps, float entropy_coef, float* __restrict__ dz, float* __restrict__ db4,
     float* __restrict__ dlog_std, float* __restrict__ logp_out, ppo_ctrl* ctrl, float* scratch, uint32_t* ticket,
-    int B, int A) {
+    int B, int A, const float* __restrict__ a3, const float* __restrict__ W4, float* __restrict__ dA3, int H3) {
   __shared__ float col_b[kHeadRows][64], col_s[kHeadRows][64], red[kHeadRows][2];
   __shared__ bool is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, row = blockIdx.x * kHeadRows + warp;
@@ -445,13 +449,43 @@ __global__ void __launch_bounds__(256) policy_head_kernel(
   const float entropy = warp_sum(ent_row) / A;  // mean over [B, A] of a row-constant
   float acc_b[2] = {0.f, 0.f}, acc_s[2] = {0.f, 0.f}, acc_surr = 0.f, acc_ratio = 0.f;
   if (row < B) {
-    float mu[2], diff[2], lp = 0.f;
+    float zf[2] = {0.f, 0.f};
+    if (FUSED) {
+      float av[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) av[i] = lane + 32 * i < H3 ? a3[(size_t)row * H3 + lane + 32 * i] : 0.f;
+      float acc[64];  // slot s holds action dim (s >> 1) + 32 * (s & 1): the butterfly ends with slots 2l, 2l+1 on lane l
+#pragma unroll
+      for (int sl = 0; sl < 64; ++sl) {
+        const int d = (sl >> 1) + 32 * (sl & 1);
+        float t = 0.f;
+        if (d < A) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (lane + 32 * i < H3) t = fmaf(av[i], W4[(size_t)d * H3 + lane + 32 * i], t);
+        }
+        acc[sl] = t;
+      }
+#pragma unroll
+      for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int t = 0; t < 32; ++t)
+          if (t < n) {
+            const float send = up ? acc[t] : acc[t + n], keep = up ? acc[t + n] : acc[t];
+            acc[t] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+          }
+      }
+      zf[0] = acc[0];
+      zf[1] = acc[1];
+    }
+    float mu[2], diff[2], gz[2] = {0.f, 0.f}, lp = 0.f;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       mu[j] = diff[j] = 0.f;
       if (has[j]) {
         const size_t i = (size_t)row * A + lane + 32 * j;
-        mu[j] = tanhf(y4[i] + bb[j]);
+        mu[j] = tanhf((FUSED ? zf[j] : y4[i]) + bb[j]);
         diff[j] = actions[i] - mu[j];
         lp += -0.5f * diff[j] * diff[j] * inv_var[j] - ls[j] - kHalfLog2Pi;
       }
@@ -473,9 +507,25 @@ __global__ void __launch_bounds__(256) policy_head_kernel(
         const float dmu = dlogp * diff[j] * inv_var[j];
         const float g = dmu * (1.f - mu[j] * mu[j]);
         dz[(size_t)row * A + lane + 32 * j] = g;
+        gz[j] = g;
         acc_b[j] = g;
         acc_s[j] = dlogp * (diff[j] * diff[j] * inv_var[j] - 1.f);
       }
+    if (FUSED) {
+      float o[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = 0.f;
+#pragma unroll 5
+      for (int d = 0; d < A; ++d) {
+        const float g = __shfl_sync(0xffffffffu, d < 32 ? gz[0] : gz[1], d & 31);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (lane + 32 * i < H3) o[i] = fmaf(g, W4[(size_t)d * H3 + lane + 32 * i], o[i]);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (lane + 32 * i < H3) dA3[(size_t)row * H3 + lane + 32 * i] = o[i];
+    }
   }
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
@@ -547,6 +597,45 @@ __global__ void __launch_bounds__(1024) value_head_kernel(const float* __restric
   sq = warp_sum(sq);
   sv = warp_sum(sv);
   sd = warp_sum(sd);
+  if (lane == 0) red[warp][0] = sq, red[warp][1] = sv, red[warp][2] = sd;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, c = 0.f, d = 0.f;
+    for (int w = 0; w < 32; ++w) a += red[w][0], c += red[w][1], d += red[w][2];
+    ctrl->critic_loss = a / B;
+    ctrl->mean_value = c / B;
+    db4[0] = d;
+  }
+}
+
+// Value head with the critic's last Linear (H3 -> 1) and its dA folded in: warp per row.
+__global__ void __launch_bounds__(1024) value_head_fused_kernel(
+    const float* __restrict__ a3, const float* __restrict__ w4, const float* __restrict__ b4,
+    const float* __restrict__ returns, float* __restrict__ dv, float* __restrict__ dA3, float* __restrict__ db4,
+    ppo_ctrl* ctrl, int B, int H3) {
+  __shared__ float red[32][3];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float wv[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) wv[i] = lane + 32 * i < H3 ? w4[lane + 32 * i] : 0.f;
+  const float b = b4[0];
+  float sq = 0.f, sv = 0.f, sd = 0.f;
+  for (int row = warp; row < B; row += 32) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (lane + 32 * i < H3) t = fmaf(a3[(size_t)row * H3 + lane + 32 * i], wv[i], t);
+    const float v = warp_sum(t) + b, e = v - returns[row], g = 2.f * e / B;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (lane + 32 * i < H3) dA3[(size_t)row * H3 + lane + 32 * i] = g * wv[i];
+    if (lane == 0) {
+      dv[row] = g;
+      sq += e * e;
+      sv += v;
+      sd += g;
+    }
+  }
   if (lane == 0) red[warp][0] = sq, red[warp][1] = sv, red[warp][2] = sd;
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -946,10 +1035,24 @@ int ppo_policy_head(const float* y4, const float* b4, const float* log_std, cons
   if (A <= 0 || A > 64) return invalid("action dim must be in 1..64");
   if (B <= 0) return invalid("B");
   if (scratch == nullptr || ticket == nullptr) return invalid("scratch / ticket");
-  policy_head_kernel<<<(B + kHeadRows - 1) / kHeadRows, 256, 0, (cudaStream_t)stream>>>(
+  policy_head_kernel<false><<<(B + kHeadRows - 1) / kHeadRows, 256, 0, (cudaStream_t)stream>>>(
       y4, b4, log_std, actions, old_logp, adv, clip_eps, entropy_coef, dz, db4, dlog_std, logp_out, ctrl, scratch,
-      ticket, B, A);
+      ticket, B, A, nullptr, nullptr, nullptr, 0);
   PPO_LAUNCH_CHECK("ppo_policy_head");
+}
+
+int ppo_policy_head_fused(const float* a3, const float* W4, const float* b4, const float* log_std,
+                          const float* actions, const float* old_logp, const float* adv, float clip_eps,
+                          float entropy_coef, float* dz, float* dA3, float* db4, float* dlog_std, float* logp_out,
+                          ppo_ctrl* ctrl, float* scratch, uint32_t* ticket, int B, int A, int H3, void* stream) {
+  if (A <= 0 || A > 64) return invalid("action dim must be in 1..64");
+  if (B <= 0 || H3 <= 0 || H3 > 256) return invalid("B / H3 (<= 256)");
+  if (scratch == nullptr || ticket == nullptr || a3 == nullptr || W4 == nullptr || dA3 == nullptr)
+    return invalid("null operand");
+  policy_head_kernel<true><<<(B + kHeadRows - 1) / kHeadRows, 256, 0, (cudaStream_t)stream>>>(
+      nullptr, b4, log_std, actions, old_logp, adv, clip_eps, entropy_coef, dz, db4, dlog_std, logp_out, ctrl, scratch,
+      ticket, B, A, a3, W4, dA3, H3);
+  PPO_LAUNCH_CHECK("ppo_policy_head_fused");
 }
 
 int ppo_value_head(const float* y4, const float* b4, const float* returns, float* dv, float* db4, ppo_ctrl* ctrl,
@@ -957,6 +1060,13 @@ int ppo_value_head(const float* y4, const float* b4, const float* returns, float
   if (B <= 0) return invalid("B");
   value_head_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(y4, b4, returns, dv, db4, ctrl, B);
   PPO_LAUNCH_CHECK("ppo_value_head");
+}
+
+int ppo_value_head_fused(const float* a3, const float* w4, const float* b4, const float* returns, float* dv,
+                         float* dA3, float* db4, ppo_ctrl* ctrl, int B, int H3, void* stream) {
+  if (B <= 0 || H3 <= 0 || H3 > 256) return invalid("B / H3 (<= 256)");
+  value_head_fused_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(a3, w4, b4, returns, dv, dA3, db4, ctrl, B, H3);
+  PPO_LAUNCH_CHECK("ppo_value_head_fused");
 }
 
 int ppo_add_bias(const float* y4, const float* b4, float* out, int n, void* stream) {

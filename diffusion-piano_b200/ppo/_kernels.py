@@ -34,6 +34,8 @@ _SIGNATURES = {
     "ppo_relu_ln_colsums": (I, [P, P, P, P, F, P, P, P, P, I, I, P]),
     "ppo_relu_ln_bwd": (I, [P, P, P, P, P, F, P, P, P, P, I, I, P]),
     "ppo_policy_head": (I, [P, P, P, P, P, P, F, F, P, P, P, P, P, P, P, I, I, P]),
+    "ppo_policy_head_fused": (I, [P, P, P, P, P, P, P, F, F, P, P, P, P, P, P, P, P, I, I, I, P]),
+    "ppo_value_head_fused": (I, [P, P, P, P, P, P, P, P, I, I, P]),
     "ppo_value_head": (I, [P, P, P, P, P, P, I, P]),
     "ppo_add_bias": (I, [P, P, P, I, P]),
     "ppo_sample_actions": (I, [P, P, P, P, P, P, P, I, I, P]),

@@ -147,6 +147,12 @@ class PPOAgent:
         if gemm not in ("custom", "cublas"):
             raise ValueError("gemm must be 'custom' or 'cublas'")
         self.gemm, self.small_m = gemm, 512
+        # heads with the last Linear and its dA inside (ppo_*_head_fused). Measured on B200 (update, B = 4096):
+        # neither 25.3 ms, value head only 25.0 ms, policy head only 29.9 ms (the 45-wide head does 2 x 360 loads
+        # per warp on 16 CTAs: slower than the two GEMM launches it saves) - so only the value head by default
+        import os
+        self.fuse_policy_head = os.environ.get("PPO_FUSE_POLICY_HEAD", "0") == "1"
+        self.fuse_value_head = os.environ.get("PPO_FUSE_VALUE_HEAD", "1") == "1"
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
@@ -213,8 +219,10 @@ class PPOAgent:
                 buf["mask"][blk] if (training and use_p > 0) else None, self.ctrl, rng_stream + blk)
         return buf["a"][blk]
 
-    def _forward(self, net: _Net, x, training: bool, p: float = 0.0, masks=None, rng_stream: int = 0):
-        """Three blocks + the last Linear (without its bias: the head kernels add it). Returns y4."""
+    def _forward(self, net: _Net, x, training: bool, p: float = 0.0, masks=None, rng_stream: int = 0,
+                 last: bool = True):
+        """Three blocks + the last Linear (without its bias: the head kernels add it). Returns y4 (last=False: the
+        fused head kernels compute the last Linear themselves)."""
         buf = net.buffers(x.shape[0], training)
         a, mi = x, 0
         for blk in range(3):
@@ -222,18 +230,21 @@ class PPOAgent:
             if masks is not None and net.dropout_after[blk]:
                 m, mi = masks[mi], mi + 1
             a = self._block_fwd(net, blk, a, buf, training, p, m, rng_stream)
-        self._mm_nt(a, net.p[f"network.{net.linears[3]}.weight"], buf["y"][3])
+        if last:
+            self._mm_nt(a, net.p[f"network.{net.linears[3]}.weight"], buf["y"][3])
         return buf["y"][3], buf
 
-    def _backward(self, net: _Net, x, buf, dz, p: float):
-        """dz = gradient with respect to the last Linear's output; fills net.grad (except the head's bias)."""
+    def _backward(self, net: _Net, x, buf, dz, p: float, da_ready: bool = False):
+        """dz = gradient with respect to the last Linear's output; fills net.grad (except the head's bias).
+        da_ready: the fused head already wrote dA of the third block into buf["da"][2]."""
         chain = torch.cuda.current_stream(self.device)
         wstream = net.wstream  # weight-gradient GEMMs leave the dependent chain dA -> LN backward -> dA ...
         li = net.linears[3]
         wstream.wait_stream(chain)
         with torch.cuda.stream(wstream):
             self._mm_tn(dz, buf["a"][2], net.g[f"network.{li}.weight"])
-        self._mm_nn(dz, net.p[f"network.{li}.weight"], buf["da"][2])
+        if not da_ready:
+            self._mm_nn(dz, net.p[f"network.{li}.weight"], buf["da"][2])
         for blk in (2, 1, 0):
             li, ni = net.linears[blk], net.norms[blk]
             use_p = p if net.dropout_after[blk] else 0.0
@@ -298,20 +309,34 @@ class PPOAgent:
         # critic on the side stream (ppo_v2.py:274-282: critic first - the two steps are independent)
         with torch.cuda.stream(side):
             net = self.critic
-            y4, buf = self._forward(net, mb["states"], True, self.dropout_p, masks, rng_stream=1)
+            small = self.gemm == "custom" and B <= self.small_m
+            fused = small and self.fuse_value_head
+            y4, buf = self._forward(net, mb["states"], True, self.dropout_p, masks, rng_stream=1, last=not fused)
             # cursor / epoch / RNG counter were last read by the gather and the dropout above: bump them here,
             # off the actor's (longer) chain
             self._k(self.lib.ppo_advance, self.ctrl, n, B)
-            self._k(self.lib.ppo_value_head, y4, net.p["network.11.bias"], mb["ret"], mb["dv"],
-                    net.g["network.11.bias"], self.ctrl, B)
-            self._backward(net, mb["states"], buf, mb["dv"], self.dropout_p)
+            if fused:
+                self._k(self.lib.ppo_value_head_fused, buf["a"][2], net.p["network.11.weight"],
+                        net.p["network.11.bias"], mb["ret"], mb["dv"], buf["da"][2], net.g["network.11.bias"],
+                        self.ctrl, B, net.dims[3])
+            else:
+                self._k(self.lib.ppo_value_head, y4, net.p["network.11.bias"], mb["ret"], mb["dv"],
+                        net.g["network.11.bias"], self.ctrl, B)
+            self._backward(net, mb["states"], buf, mb["dv"], self.dropout_p, da_ready=fused)
             self._optim_step(net, 1)
         net = self.actor
-        y4, buf = self._forward(net, mb["states"], True)
-        self._k(self.lib.ppo_policy_head, y4, net.p["network.9.bias"], net.p["log_std"], mb["actions"], mb["logp"],
-                mb["adv"], self.epsilon, self.entropy_coef, mb["dz"], net.g["network.9.bias"], net.g["log_std"],
-                mb["new_logp"], self.ctrl, net.scratch, net.ticket[2:], B, self.action_dim)
-        self._backward(net, mb["states"], buf, mb["dz"], 0.0)
+        fused = small and self.fuse_policy_head
+        y4, buf = self._forward(net, mb["states"], True, last=not fused)
+        if fused:
+            self._k(self.lib.ppo_policy_head_fused, buf["a"][2], net.p["network.9.weight"], net.p["network.9.bias"],
+                    net.p["log_std"], mb["actions"], mb["logp"], mb["adv"], self.epsilon, self.entropy_coef, mb["dz"],
+                    buf["da"][2], net.g["network.9.bias"], net.g["log_std"], mb["new_logp"], self.ctrl, net.scratch,
+                    net.ticket[2:], B, self.action_dim, net.dims[3])
+        else:
+            self._k(self.lib.ppo_policy_head, y4, net.p["network.9.bias"], net.p["log_std"], mb["actions"], mb["logp"],
+                    mb["adv"], self.epsilon, self.entropy_coef, mb["dz"], net.g["network.9.bias"], net.g["log_std"],
+                    mb["new_logp"], self.ctrl, net.scratch, net.ticket[2:], B, self.action_dim)
+        self._backward(net, mb["states"], buf, mb["dz"], 0.0, da_ready=fused)
         self._optim_step(net, 0)
         main.wait_stream(side)
 

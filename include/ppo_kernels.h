@@ -106,9 +106,20 @@ int ppo_policy_head(const float* y4, const float* b4, const float* log_std, cons
                     float* db4, float* dlog_std, float* logp_out, ppo_ctrl* ctrl_dev, float* scratch,
                     uint32_t* ticket, int B, int A, void* stream);
 
+/* The same with the last Linear and its dA inside (one dependent launch instead of three): a3 [B,H3] is the third
+ * block's output, W4 [A,H3] the last Linear's weight; also writes dA3 [B,H3] = dz . W4. H3 <= 256. */
+int ppo_policy_head_fused(const float* a3, const float* W4, const float* b4, const float* log_std,
+                          const float* actions, const float* old_logp, const float* adv, float clip_eps,
+                          float entropy_coef, float* dz, float* dA3, float* db4, float* dlog_std, float* logp_out,
+                          ppo_ctrl* ctrl_dev, float* scratch, uint32_t* ticket, int B, int A, int H3, void* stream);
+
 /* y4 [B] without bias. dv [B] = 2 (v - ret) / B, db4 [1]; ctrl->critic_loss / mean_value. */
 int ppo_value_head(const float* y4, const float* b4, const float* returns, float* dv, float* db4,
                    ppo_ctrl* ctrl_dev, int B, void* stream);
+
+/* The same with the critic's last Linear (w4 [H3]) and its dA inside: v = a3 . w4 + b4, dA3 [B,H3] = dv w4. */
+int ppo_value_head_fused(const float* a3, const float* w4, const float* b4, const float* returns, float* dv,
+                         float* dA3, float* db4, ppo_ctrl* ctrl_dev, int B, int H3, void* stream);
 
 /* values[i] = y4[i] + b4 (critic inference on the whole batch). */
 int ppo_add_bias(const float* y4, const float* b4, float* out, int n, void* stream);

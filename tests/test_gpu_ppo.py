@@ -285,6 +285,30 @@ def test_update_matches_reference_and_oracle(torch_cuda):
     assert abs(c.actor_loss - al) < 2e-4 * max(1.0, abs(al))
 
 
+def test_fused_heads_match_unfused(torch_cuda, monkeypatch):
+    """ppo_policy_head_fused / ppo_value_head_fused (last Linear and its dA inside the head kernel) against the
+    three-launch path: same update on the reference's recorded permutations and masks."""
+    torch = torch_cuda
+    z, (sd, ad, n, batch, epochs, stride), masks, actor, critic, b = _golden()
+    n_mb = epochs * ((n + batch - 1) // batch)
+    dm = lambda m: torch.as_tensor(m.astype(np.uint8), device="cuda")  # noqa: E731
+    results = []
+    for pol, val in (("0", "0"), ("1", "1")):
+        monkeypatch.setenv("PPO_FUSE_POLICY_HEAD", pol)
+        monkeypatch.setenv("PPO_FUSE_VALUE_HEAD", val)
+        ag = _agent(torch, sd, ad, actor, critic, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch, ppo_epochs=epochs)
+        assert ag.fuse_policy_head == (pol == "1") and ag.fuse_value_head == (val == "1")
+        ag.update(b["states"], b["actions"], b["rewards"].astype(np.float32), z["log_probs"], b["next_states"],
+                  b["dones"], perms=z["perms"], value_masks=[dm(m) for m in masks[0:2]],
+                  next_value_masks=[dm(m) for m in masks[2:4]],
+                  minibatch_masks=[[dm(m) for m in masks[4 + 2 * i: 6 + 2 * i]] for i in range(n_mb)])
+        results.append((ag.actor.theta.clone(), ag.critic.theta.clone(), ag.read_ctrl()))
+    for i in (0, 1):
+        assert (results[0][i] - results[1][i]).abs().max().item() < 4e-6
+    assert abs(results[0][2].actor_loss - results[1][2].actor_loss) < 1e-5
+    assert abs(results[0][2].critic_loss - results[1][2].critic_loss) < 1e-5
+
+
 def test_graph_update_matches_oracle(torch_cuda):
     """The CUDA-graph path (device-side permutation, no dropout so that the oracle can follow): parameters after
     two updates against the oracle fed the materialised permutations."""
