@@ -69,10 +69,12 @@ def train(env, cfg: TrainConfig, process_group=None, agent: Optional[PPOAgent] =
                 on_step(episode, step)
             if cfg.max_steps_per_episode is not None and step >= cfg.max_steps_per_episode:
                 break
-            # every env terminates at frame count `frames` unless wrong-press termination ends it early
-            if step >= frames or (getattr(env.task, "_wrong_press_termination", False) and bool(dones.all())):
-                if bool(dones.all()):
-                    break
+            # all envs play the same song in lockstep: they are done together after `frames` steps, so the
+            # reference's `if all(dones): break` needs a device read only then (or every step when a wrong press
+            # may end an env early)
+            may_be_done = step >= frames or bool(getattr(env.task, "_wrong_press_termination", False))
+            if may_be_done and bool(dones.all()):
+                break
             obs = next_obs
         # statistics of the episode: one small all-reduce outside the step
         total = torch.stack([episode_rewards.sum(), torch.tensor(float(n), device=env.device)])
