@@ -1,5 +1,6 @@
 // pp_api.cu - the C-ABI of include/piano_step.h: handle lifetime, model upload, launches.
 #include <cstdarg>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -26,6 +27,7 @@ static int fail(int code, const char* fmt, ...) {
 
 // auto-tuning of the launch shape: full-batch steps SKIP .. SKIP+STEPS-1 alternate the two shapes under CUDA events
 constexpr int PP_TUNE_SKIP = 4, PP_TUNE_STEPS = 12;
+constexpr int PP_MAX_HOST_CHUNKS = 8;
 
 struct pp_env {
   pp_config cfg;
@@ -54,8 +56,11 @@ struct pp_env {
   int* order = nullptr;  // [N]
   cudaEvent_t tune_ev[2 * PP_TUNE_STEPS] = {};
   // host-buffer path
-  cudaStream_t hstream = nullptr, hstream2 = nullptr;  // host-buffer calls: the batch is stepped in two halves
-  cudaEvent_t h_ready = nullptr;                       // so that the first half's D2H overlaps the second half's step
+  // host-buffer calls: the batch is stepped in host_chunks pieces on their own streams, so that a piece's D2H
+  // overlaps the later pieces' steps (hstream is piece 0 and carries the H2D of the actions)
+  cudaStream_t hstream = nullptr, hstream_more[PP_MAX_HOST_CHUNKS - 1] = {};
+  int host_chunks = 6;  // e2e of config 2 (B = 4096, 40 steps): 2 pieces 1.224 M, 3: 1.243 M, 4: 1.244 M, 6: 1.256 M, 8: 1.254 M env-steps/s
+  cudaEvent_t h_ready = nullptr;
   float *h_actions = nullptr, *h_obs = nullptr, *h_reward = nullptr, *h_terms = nullptr, *h_discount = nullptr;
   uint8_t* h_done = nullptr;
   float *d_actions = nullptr, *d_obs = nullptr, *d_reward = nullptr, *d_terms = nullptr, *d_discount = nullptr;
@@ -323,7 +328,11 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(cudaMemcpy(e->act_max_d, e->act_max.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
   // host-buffer path: pinned staging + device mirrors
   CUDA_OK(cudaStreamCreateWithFlags(&e->hstream, cudaStreamNonBlocking));
-  CUDA_OK(cudaStreamCreateWithFlags(&e->hstream2, cudaStreamNonBlocking));
+  for (auto& hs : e->hstream_more) CUDA_OK(cudaStreamCreateWithFlags(&hs, cudaStreamNonBlocking));
+  if (const char* hc = getenv("PP_HOST_CHUNKS")) {  // measured on B200, config 2 (B = 4096): see pp_step_host
+    const int k = atoi(hc);
+    if (k >= 1 && k <= PP_MAX_HOST_CHUNKS) e->host_chunks = k;
+  }
   CUDA_OK(cudaEventCreateWithFlags(&e->h_ready, cudaEventDisableTiming));
   CUDA_OK(cudaMallocHost((void**)&e->h_actions, (size_t)N * e->action_dim * 4));
   CUDA_OK(cudaMallocHost((void**)&e->h_obs, (size_t)N * e->obs_dim * 4));
@@ -354,7 +363,7 @@ extern "C" int pp_destroy(pp_env* e) {
   void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
   for (void* p : host) if (p) cudaFreeHost(p);
   if (e->hstream) cudaStreamDestroy(e->hstream);
-  if (e->hstream2) cudaStreamDestroy(e->hstream2);
+  for (auto hs : e->hstream_more) if (hs) cudaStreamDestroy(hs);
   if (e->h_ready) cudaEventDestroy(e->h_ready);
   for (auto ev : e->tune_ev) if (ev) cudaEventDestroy(ev);
   delete e;
@@ -508,14 +517,20 @@ extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* 
              pd = is_pinned(done), pc = is_pinned(discount);
   if (!pa) memcpy(e->h_actions, actions, N * e->action_dim * 4);
   CUDA_OK(cudaMemcpyAsync(e->d_actions, pa ? actions : e->h_actions, N * e->action_dim * 4, cudaMemcpyHostToDevice, s));
-  // two halves on two streams (hands task, large batches): the first half's results travel to the host while
-  // the second half is still stepping. Both grids are resident together, so the device does the same work.
-  const bool split = e->cfg.task == PP_TASK_PIANO_WITH_SHADOW_HANDS && N >= 1024;
-  const size_t n0 = split ? ((N / 2) & ~(size_t)1) : N;
-  if (split) { CUDA_OK(cudaEventRecord(e->h_ready, s)); CUDA_OK(cudaStreamWaitEvent(e->hstream2, e->h_ready, 0)); }
-  for (int half = 0; half < (split ? 2 : 1); half++) {
-    cudaStream_t hs = half ? e->hstream2 : s;
-    const size_t b = half ? n0 : 0, n = half ? N - n0 : n0;
+  // pieces on their own streams (hands task, large batches): a piece's results travel to the host while the later
+  // pieces are still stepping. All grids are resident together, so the device does the same work.
+  const bool split = e->cfg.task == PP_TASK_PIANO_WITH_SHADOW_HANDS && N >= 1024 && e->host_chunks > 1;
+  const int pieces = split ? e->host_chunks : 1;
+  const size_t per = split ? ((N / pieces + 9) / 10) * 10 : N;  // a multiple of both block shapes (2 and 10 envs)
+  if (split) {
+    CUDA_OK(cudaEventRecord(e->h_ready, s));
+    for (int k = 1; k < pieces; k++) CUDA_OK(cudaStreamWaitEvent(e->hstream_more[k - 1], e->h_ready, 0));
+  }
+  for (int k = 0; k < pieces; k++) {
+    cudaStream_t hs = k ? e->hstream_more[k - 1] : s;
+    const size_t b = (size_t)k * per;
+    if (b >= N) break;
+    const size_t n = k == pieces - 1 ? N - b : (b + per <= N ? per : N - b);
     int rc = launch(e, PP_MODE_STEP, nullptr, e->d_actions, obs ? e->d_obs : nullptr, e->d_reward,
                     terms ? e->d_terms : nullptr, e->d_done, discount ? e->d_discount : nullptr, hs, (int)b, (int)n);
     if (rc != PP_OK) return rc;
@@ -525,7 +540,7 @@ extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* 
     if (discount) CUDA_OK(d2h(discount + b, e->h_discount + b, e->d_discount + b, n * 4, pc, hs));
     CUDA_OK(d2h(done + b, e->h_done + b, e->d_done + b, n, pd, hs));
   }
-  if (split) CUDA_OK(cudaStreamSynchronize(e->hstream2));
+  for (int k = 1; k < pieces; k++) CUDA_OK(cudaStreamSynchronize(e->hstream_more[k - 1]));
   CUDA_OK(cudaStreamSynchronize(s));
   if (obs && !po) memcpy(obs, e->h_obs, N * e->obs_dim * 4);
   if (!pr) memcpy(reward, e->h_reward, N * 4);
