@@ -433,3 +433,44 @@ def test_train_loop_config4_smoke(torch_cuda):
         assert torch.equal(other.actor.theta, agent.actor.theta) and torch.equal(other.critic.m, agent.critic.m)
         assert bytes(other.read_ctrl()) == bytes(agent.read_ctrl())
     env.close()
+
+
+def test_reference_loop_with_numpy_api(torch_cuda):
+    """The reference's loop body as written (parallelized_base_v2.py:116-166): numpy observation dicts from
+    VectorizedPianoEnv, hand-concatenated states, numpy in / numpy out agent calls."""
+    from diffusion_piano_b200 import music, suite
+    from diffusion_piano_b200.ppo import PPOAgent
+
+    num_envs = 8
+    vec_env = suite.VectorizedPianoEnv(num_envs, music.load("GurenNoYumiyaCut14s"))
+    observation_spec = vec_env.envs[0].observation_spec()
+    action_spec = vec_env.envs[0].action_spec()
+    state_dim = sum(int(np.prod(spec.shape)) for spec in observation_spec.values())
+    action_dim = action_spec.shape[0]
+    assert (state_dim, action_dim) == (329, 45)
+    agent = PPOAgent(state_dim=state_dim, action_dim=action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=4,
+                     device="cuda", checkpoint_dir="/tmp/ppo_numpy_api", ppo_epochs=2)
+    keys = ("goal", "fingering", "piano/state", "piano/sustain_state", "rh_shadow_hand/joints_pos",
+            "lh_shadow_hand/joints_pos")
+
+    def flat(o):
+        return np.stack([np.concatenate([o[k][i].flatten() for k in keys]) for i in range(num_envs)])
+
+    obs = vec_env.reset()
+    episode_rewards = np.zeros(num_envs)
+    before = agent.actor.theta.clone()
+    for _ in range(3):
+        states = flat(obs)
+        actions, log_probs = agent.select_actions(states)
+        assert isinstance(actions, np.ndarray) and actions.shape == (num_envs, 45) and log_probs.shape == (num_envs,)
+        next_obs, rewards, dones = vec_env.step(actions)
+        next_states = flat(next_obs)
+        episode_rewards += rewards
+        agent.update(states=states, actions=actions, rewards=rewards, log_probs=log_probs, next_states=next_states,
+                     dones=dones)
+        assert not all(dones)
+        obs = next_obs
+    st = agent.stats()
+    assert st["adam_steps"] == 3 * 2 * 2 and np.isfinite(st["actor_loss"]) and np.isfinite(episode_rewards).all()
+    assert (agent.actor.theta - before).abs().max().item() > 0
+    vec_env.batched.close()
