@@ -178,6 +178,7 @@ class PPOAgent:
         self._k(self.lib.ppo_ctrl_init, self.ctrl, (seed or 0) * 1000003 + self.rank, lr, lr * 2)
         self.checkpoint_dir = Path(checkpoint_dir)
         self._side = torch.cuda.Stream(device=self.device)
+        self._pref = torch.cuda.Stream(device=self.device)  # gather of the next minibatch
         self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
         self._batch: Dict[int, dict] = {}
         self._launches_per_graph: Dict[tuple, int] = {}
@@ -289,8 +290,8 @@ class PPOAgent:
                 returns=f(ng), adv_raw=f(ng), adv=f(ng), values=f(n), next_values=f(n))
         return self._batch[n]
 
-    def _minibatch_buffers(self, B: int) -> dict:
-        key = ("mb", B)
+    def _minibatch_buffers(self, B: int, parity: int = 0) -> dict:
+        key = ("mb", B, parity)
         if key not in self._batch:
             f = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.device)  # noqa: E731
             self._batch[key] = dict(states=f(B, self.state_dim), actions=f(B, self.action_dim), logp=f(B), adv=f(B),
@@ -298,14 +299,26 @@ class PPOAgent:
         return self._batch[key]
 
     # ------------------------------------------------------------------ one minibatch (graph body)
-    def _minibatch(self, bb: dict, n: int, B: int, adv, returns, perm=None, perm_epochs: int = 0, masks=None):
-        mb = self._minibatch_buffers(B)
+    def _gather(self, bb: dict, n: int, B: int, adv, returns, perm, perm_epochs: int, parity: int) -> dict:
+        mb = self._minibatch_buffers(B, parity)
         self._k(self.lib.ppo_gather_minibatch, bb["states"], bb["actions"], bb["logp"], adv, returns, perm,
                 perm_epochs, self.ctrl, 0, n, self.state_dim, self.action_dim, B, mb["states"], mb["actions"],
                 mb["logp"], mb["adv"], mb["ret"])
+        return mb
+
+    def _minibatch(self, bb: dict, n: int, B: int, adv, returns, perm=None, perm_epochs: int = 0, masks=None,
+                   mb: Optional[dict] = None, next_B: Optional[int] = None, parity: int = 0):
+        """One minibatch update. `mb`: rows already gathered by the previous call's prefetch; `next_B`: gather the
+        next minibatch (into the other buffer set) as soon as the cursor has moved, off both networks' chains.
+        Returns the prefetched buffers (or None)."""
         main = torch.cuda.current_stream(self.device)
+        if mb is None:
+            mb = self._gather(bb, n, B, adv, returns, perm, perm_epochs, parity)
+        else:
+            main.wait_stream(self._pref)
         side = self._side
         side.wait_stream(main)
+        next_mb = None
         # critic on the side stream (ppo_v2.py:274-282: critic first - the two steps are independent)
         with torch.cuda.stream(side):
             net = self.critic
@@ -315,6 +328,10 @@ class PPOAgent:
             # cursor / epoch / RNG counter were last read by the gather and the dropout above: bump them here,
             # off the actor's (longer) chain
             self._k(self.lib.ppo_advance, self.ctrl, n, B)
+            if next_B is not None:
+                self._pref.wait_stream(side)
+                with torch.cuda.stream(self._pref):
+                    next_mb = self._gather(bb, n, next_B, adv, returns, perm, perm_epochs, parity ^ 1)
             if fused:
                 self._k(self.lib.ppo_value_head_fused, buf["a"][2], net.p["network.11.weight"],
                         net.p["network.11.bias"], mb["ret"], mb["dv"], buf["da"][2], net.g["network.11.bias"],
@@ -339,6 +356,7 @@ class PPOAgent:
         self._backward(net, mb["states"], buf, mb["dz"], 0.0, da_ready=fused)
         self._optim_step(net, 0)
         main.wait_stream(side)
+        return next_mb
 
     def _replay(self, key, sizes, bb, n, adv, returns):
         """Replays the CUDA graph of the minibatches `sizes` (one minibatch, or all of an update), capturing it on
@@ -353,6 +371,7 @@ class PPOAgent:
             s.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(s):
                 for B in sorted(set(sizes)):
+                    self._minibatch_buffers(B, 1)  # both buffer sets exist before the capture
                     self._minibatch(bb, n, B, adv, returns)
             torch.cuda.current_stream(self.device).wait_stream(s)
             for t, v in zip(state, saved):
@@ -361,8 +380,10 @@ class PPOAgent:
             g = torch.cuda.CUDAGraph()
             # thread_local: the NCCL watchdog thread may query events while this thread captures
             with torch.cuda.graph(g, capture_error_mode="thread_local" if self.world > 1 else "global"):
-                for B in sizes:
-                    self._minibatch(bb, n, B, adv, returns)
+                mb = None
+                for i, B in enumerate(sizes):
+                    mb = self._minibatch(bb, n, B, adv, returns, mb=mb,
+                                         next_B=sizes[i + 1] if i + 1 < len(sizes) else None, parity=i & 1)
             self._launches_per_graph[key] = self.kernel_launches - before
             self.kernel_launches = before
             self._graphs[key] = g  # capture does not execute: nothing to restore
@@ -423,9 +444,12 @@ class PPOAgent:
         sizes = [min(self.batch_size, n - start) for _ in range(self.ppo_epochs)
                  for start in range(0, n, self.batch_size)]
         if explicit or not self.use_graphs:
+            mb = None
             for mb_index, B in enumerate(sizes):
                 masks = None if minibatch_masks is None else minibatch_masks[mb_index]
-                self._minibatch(bb, n, B, adv, returns, perm_t, 0 if perm_t is None else perm_t.shape[0], masks)
+                mb = self._minibatch(bb, n, B, adv, returns, perm_t, 0 if perm_t is None else perm_t.shape[0], masks,
+                                     mb=mb, next_B=sizes[mb_index + 1] if mb_index + 1 < len(sizes) else None,
+                                     parity=mb_index & 1)
         elif self.graph_scope == "update":  # every minibatch of the update in one graph launch
             self._replay((n, "update", adv.data_ptr(), returns.data_ptr()), sizes, bb, n, adv, returns)
         else:
