@@ -54,6 +54,7 @@ struct pp_env {
   int sched_mode = PP_SCHED_AUTO, block_envs = 2, tune_calls = 0;
   bool sort_work = false, tuned = false;
   int* order = nullptr;  // [N]
+  uint4* substep_act = nullptr;  // caller-owned [N, n_substeps] (pp_set_substep_activations) or null
   cudaEvent_t tune_ev[2 * PP_TUNE_STEPS] = {};
   // host-buffer path
   // host-buffer calls: the batch is stepped in host_chunks pieces on their own streams, so that a piece's D2H
@@ -439,6 +440,7 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     A.discount = discount; A.done = done; A.qacc = e->qacc; A.act_force = e->act_force;
     A.act_vel = e->act_vel; A.site_xpos = e->site_xpos; A.activation = e->activation;
     A.counters = e->counters;
+    A.substep_act = mode == PP_MODE_STEP ? e->substep_act : nullptr;
     A.eval = EvalAccum{e->eval_sum, e->eval_steps, e->eval_episode, e->eval_count};
     const bool full = env_begin == 0 && (env_count < 0 || env_count == c.num_envs);
     int block_envs = e->block_envs;
@@ -607,6 +609,15 @@ extern "C" int pp_get_metrics(pp_env* e, float* episode_metrics, int32_t* episod
   const size_t N = e->cfg.num_envs;
   COPY_IF(episode_metrics, e->eval_episode, N * 6 * 4);
   COPY_IF(episode_count, e->eval_count, N * 4);
+  return PP_OK;
+}
+
+extern "C" int pp_set_substep_activations(pp_env* e, uint32_t* buf_dev) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  if (e->cfg.task != PP_TASK_PIANO_WITH_SHADOW_HANDS)
+    return fail(PP_ERR_UNSUPPORTED, "per-substep activations are recorded by the two-hands step only");
+  if (buf_dev && (reinterpret_cast<uintptr_t>(buf_dev) & 15) != 0) return fail(PP_ERR_INVALID, "buffer must be 16-byte aligned");
+  e->substep_act = reinterpret_cast<uint4*>(buf_dev);
   return PP_OK;
 }
 

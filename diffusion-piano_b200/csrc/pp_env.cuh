@@ -52,6 +52,7 @@ struct HandsArgs {
   uint8_t* activation;
   int* counters;  // [N,8]
   const int* order;  // [N] launch slot -> env (null: identity); envs of similar expected work share a block
+  uint4* substep_act;  // [N, n_substeps] or null: key activation bits 0-31 / 32-63 / 64-87 and the pedal after every substep
   EvalAccum eval;  // musical metrics accumulators
 };
 

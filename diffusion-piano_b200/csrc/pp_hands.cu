@@ -1722,6 +1722,19 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         pp_scalar_euler(Mk, kt.damping, o.h, ftot, qk[i], vk[i]);
       }
       __syncwarp();
+      if (A.substep_act) {
+        // Piano.after_substep -> MidiModule.after_substep (piano.py:154-162, midi_module.py:47-98): the key and
+        // pedal activations after EVERY substep, as bit masks; the host turns their changes into note events
+        unsigned bits[3];
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+          const int k = lane + 32 * i;
+          float nrm = 0.f; bool on = false;
+          if (k < PP_NKEY) pp_key_state(qk[i], kt.hi[k], nrm, on);
+          bits[i] = __ballot_sync(FULL, on);
+        }
+        if (lane == 0) A.substep_act[(size_t)env * nsub + sub] = make_uint4(bits[0], bits[1], bits[2], sustain >= 0.5f ? 1u : 0u);
+      }
       cnt_ncon = ncon; cnt_iter = iter; cnt_drop = ndrop;
       sum_iter += iter; sum_ls += ls_total; sum_dense += dense_mode ? 1 : 0; sum_coupled += nlr;
       {  // key limit rows count towards nefc (diagnostic)

@@ -118,6 +118,11 @@ class BatchedPianoEngine:
         """y shift [N] of both hands that each env takes at its next reset (None: zero again)."""
         _lib.check(self.lib.pp_set_hand_offsets(self._h, _ptr(y_off), stream))
 
+    def set_substep_activations(self, buf):
+        """uint32 CUDA tensor [N, n_substeps, 4] that every later step fills with the key / pedal activation bits
+        after each substep (None: stop). The caller keeps the tensor alive."""
+        _lib.check(self.lib.pp_set_substep_activations(self._h, _ptr(buf)))
+
     def get_metrics(self, episode_metrics=None, episode_count=None, stream: int = 0):
         """Musical metrics of every env's last finished episode: [N,6] f32, and [N] i32 episode counts."""
         _lib.check(self.lib.pp_get_metrics(self._h, _ptr(episode_metrics), _ptr(episode_count), stream))

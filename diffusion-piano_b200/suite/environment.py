@@ -112,7 +112,42 @@ class BatchedEnvironment:
     def reset(self) -> Dict[str, np.ndarray]:
         self._draw_hand_offsets()
         self.engine.reset_host(obs=self._h_obs)
+        for i, m in getattr(self, "_midi_modules", {}).items():
+            m.initialize_episode()
+            self._midi_substeps[i] = 0
+        self._h_done[...] = 0
         return self._split(self._h_obs)
+
+    # ---- MIDI events (reference Piano.midi_module, models/piano/midi_module.py): recorded per substep on the device
+    def enable_midi_events(self, envs=(0,)):
+        """Starts recording the key / pedal activations after every physics substep (pp_set_substep_activations)
+        and returns {env index: MidiModule}; the modules are fed by the numpy `step()` of this class."""
+        from ..music.midi_module import MidiModule
+
+        torch = self._torch
+        nsub = self.task.physics_steps_per_control_step
+        if not hasattr(self, "_midi_words"):
+            self._midi_words = torch.zeros((self.num_envs, nsub, 4), dtype=torch.int32, device=self.device)
+            self.engine.set_substep_activations(self._midi_words)
+            self._midi_modules, self._midi_substeps = {}, {}
+        for i in envs:
+            if i not in self._midi_modules:
+                self._midi_modules[int(i)] = MidiModule()
+                self._midi_substeps[int(i)] = 0
+        return self._midi_modules
+
+    def _feed_midi(self, was_done: np.ndarray) -> None:
+        idx = sorted(self._midi_modules)
+        words = self._midi_words[idx].cpu().numpy().view(np.uint32)
+        nsub = words.shape[1]
+        for row, i in enumerate(idx):
+            m = self._midi_modules[i]
+            if self._auto_reset and was_done[i]:  # this call reset the env: no substep ran (initialize_episode)
+                m.initialize_episode()
+                self._midi_substeps[i] = 0
+                continue
+            m.after_step_words(words[row], self._midi_substeps[i], self.task.physics_timestep)
+            self._midi_substeps[i] += nsub
 
     def step(self, actions):
         a = np.asarray(actions)
@@ -121,8 +156,11 @@ class BatchedEnvironment:
         self._h_actions[...] = a  # float64 -> float32 into the page-locked buffer
         if self._auto_reset:
             self._draw_hand_offsets()
+        was_done = self._h_done.astype(bool) if getattr(self, "_midi_modules", None) else None
         self.engine.step_host(self._h_actions, self._h_obs, self._h_reward, self._h_done, self._h_terms,
                               self._h_discount)
+        if was_done is not None:
+            self._feed_midi(was_done)
         return self._split(self._h_obs), self._h_reward.astype(np.float64), self._h_done.astype(bool)
 
     @property
@@ -239,6 +277,12 @@ class Environment:
     @property
     def batched(self) -> BatchedEnvironment:
         return self._b
+
+    @property
+    def midi_module(self):
+        """`environment.task.piano.midi_module` of the reference (viewer/runtime.py:135): note / pedal events of
+        this env, recorded from the first access on."""
+        return self._b.enable_midi_events((0,))[0]
 
     def close(self):
         self._b.close()

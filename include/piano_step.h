@@ -113,6 +113,13 @@ int pp_get_metrics(pp_env *env, float *episode_metrics_dev, int32_t *episode_cou
  * uniform(-0.05, 0.05)); it stays in force until the reset after. NULL: zero shift from the next reset on. */
 int pp_set_hand_offsets(pp_env *env, const float *y_off_dev, void *stream);
 
+/* Piano.after_substep -> MidiModule.after_substep (robopianist/models/piano/piano.py:154-162,
+ * midi_module.py:47-98): the reference turns the key / pedal activations after EVERY physics substep into MIDI
+ * note-on / note-off / sustain events. buf_dev: caller-owned uint32 [N, n_substeps, 4], 16-byte aligned, written
+ * by every later pp_step / pp_step_host: words 0-2 = activation bits of keys 0-31, 32-63, 64-87, word 3 = pedal.
+ * NULL stops the recording. Two-hands task only. */
+int pp_set_substep_activations(pp_env *env, uint32_t *buf_dev);
+
 /* diagnostics of the LAST substep of the last pp_step (device pointers, any may be NULL):
  * qacc [N,nv]; actuator_force [N,nu]; actuator_velocity [N,nu]; site_xpos [N,nsite,3];
  * activation [N,88] u8; counters [N,8] i32 = {ncon, nefc, newton iterations, dropped contacts} of the last substep, then
