@@ -7,6 +7,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/ppo_kernels.h"
 
@@ -28,6 +29,37 @@ int invalid(const char* what) {
     if (e_ != cudaSuccess) return fail(name, e_); \
     return 0;                                  \
   } while (0)
+
+// Programmatic dependent launch (sm_90+): a kernel launched with this attribute may start while its predecessor in
+// the stream is still running; it must call cudaGridDependencySynchronize() before touching anything the
+// predecessor reads or writes. Every kernel launched through launch_k does so as its first statement, so memory
+// semantics stay those of a plain stream and only the launch latency of a dependent chain is overlapped.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t s, bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+bool use_pdl() {  // PPO_PDL=0 turns programmatic dependent launch off (A/B measurements)
+  static const bool on = [] { const char* e = getenv("PPO_PDL"); return e == nullptr || e[0] != '0'; }();
+  return on;
+}
+
+__global__ void pdl_probe_kernel(float* v, int n, int early) {
+  if (early) cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) v[i] += 1.f;
+}
 
 constexpr float kLnEps = 1e-5f;
 constexpr float kHalfLog2Pi = 0.91893853320467274178f;
@@ -64,6 +96,7 @@ __global__ void __launch_bounds__(256) relu_ln_fwd_kernel(
     const float* __restrict__ beta, float* __restrict__ out, float* h_save, float* __restrict__ stats, int rows,
     int H, float p, const uint8_t* __restrict__ mask_in, uint8_t* __restrict__ mask_out, const ppo_ctrl* ctrl,
     uint32_t rng_stream) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int vpt = H >> 5;
@@ -114,6 +147,7 @@ __global__ void __launch_bounds__(256) relu_ln_bwd_dy_kernel(
     const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
     const float* __restrict__ gamma, const uint8_t* __restrict__ mask, float p, float* __restrict__ dy, int rows,
     int H) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int vpt = H >> 5;
@@ -149,6 +183,7 @@ __global__ void __launch_bounds__(256) relu_ln_colsums_kernel(
     const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
     const uint8_t* __restrict__ mask, float p, const float* __restrict__ dy, float* __restrict__ dbias,
     float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int H) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   __shared__ float red[3][8][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, c = blockIdx.x * 32 + lane;
   const float keep_scale = 1.f / (1.f - p);
@@ -184,6 +219,7 @@ __global__ void __launch_bounds__(256) relu_ln_colsums_kernel(
 // transposing butterfly (31 shuffles) that leaves output element l of the tile on lane l.
 __global__ void __launch_bounds__(128) gemm_nt_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
                                                       float* __restrict__ C, int M, int N, int K) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int m0 = blockIdx.y * 4, n0 = blockIdx.x * 32 + warp * 8;
   if (n0 >= N) return;
@@ -229,6 +265,7 @@ __global__ void __launch_bounds__(128) gemm_nt_kernel(const float* __restrict__ 
 // the 8 partial tiles are added through shared memory in warp order.
 __global__ void __launch_bounds__(256) gemm_nn_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
                                                       float* __restrict__ C, int M, int N, int K) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   __shared__ __align__(16) float As[8][256];  // reused for the partial tiles [8 warps][8 rows][32 k]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int k = blockIdx.x * 32 + lane, m0 = blockIdx.y * 8;
@@ -287,6 +324,7 @@ __global__ void __launch_bounds__(256) ln_bwd_gemm_nn_kernel(
     const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
     const float* __restrict__ gamma, const uint8_t* __restrict__ mask, float p, float* __restrict__ dy,
     const float* __restrict__ Bm, float* __restrict__ C, int M, int H, int K) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   __shared__ __align__(16) float As[8][256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int k = blockIdx.x * 32 + lane, m0 = blockIdx.y * 8;
@@ -368,6 +406,7 @@ __global__ void __launch_bounds__(256) ln_bwd_gemm_nn_kernel(
 // read coalesced), the 8 warps split the contraction index m; partial tiles added through shared memory.
 __global__ void __launch_bounds__(256) gemm_tn_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
                                                       float* __restrict__ C, int M, int N, int K) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   __shared__ __align__(16) float As[256][8];  // reused for the partial tiles [8 warps][8 n][32 k]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int k = blockIdx.x * 32 + lane, n0 = blockIdx.y * 8;
@@ -431,6 +470,7 @@ __global__ void __launch_bounds__(256) policy_head_kernel(
     float clip_eps, float entropy_coef, float* __restrict__ dz, float* __restrict__ db4,
     float* __restrict__ dlog_std, float* __restrict__ logp_out, ppo_ctrl* ctrl, float* scratch, uint32_t* ticket,
     int B, int A, const float* __restrict__ a3, const float* __restrict__ W4, float* __restrict__ dA3, int H3) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   __shared__ float col_b[kHeadRows][64], col_s[kHeadRows][64], red[kHeadRows][2];
   __shared__ bool is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, row = blockIdx.x * kHeadRows + warp;
@@ -583,6 +623,7 @@ __global__ void __launch_bounds__(256) policy_head_kernel(
 __global__ void __launch_bounds__(1024) value_head_kernel(const float* __restrict__ y4, const float* __restrict__ b4,
                                                           const float* __restrict__ returns, float* __restrict__ dv,
                                                           float* __restrict__ db4, ppo_ctrl* ctrl, int B) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   __shared__ float red[32][3];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float sq = 0.f, sv = 0.f, sd = 0.f;
@@ -613,6 +654,7 @@ __global__ void __launch_bounds__(1024) value_head_fused_kernel(
     const float* __restrict__ a3, const float* __restrict__ w4, const float* __restrict__ b4,
     const float* __restrict__ returns, float* __restrict__ dv, float* __restrict__ dA3, float* __restrict__ db4,
     ppo_ctrl* ctrl, int B, int H3) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   __shared__ float red[32][3];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float wv[8];
@@ -649,6 +691,7 @@ __global__ void __launch_bounds__(1024) value_head_fused_kernel(
 
 __global__ void add_bias_kernel(const float* __restrict__ y, const float* __restrict__ b, float* __restrict__ out,
                                 int n) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = y[i] + b[0];
 }
@@ -658,6 +701,7 @@ __global__ void __launch_bounds__(256) sample_actions_kernel(
     const float* __restrict__ y4, const float* __restrict__ b4, const float* __restrict__ log_std,
     const float* __restrict__ noise_in, float* __restrict__ actions, float* __restrict__ logp,
     const ppo_ctrl* ctrl, int N, int A) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= N) return;
   float lp = 0.f;
@@ -701,6 +745,7 @@ __global__ void __launch_bounds__(1024) prepare_batch_kernel(
     const float* __restrict__ rewards, const float* __restrict__ dones, const float* __restrict__ values,
     const float* __restrict__ next_values, float gamma, float lam, float* __restrict__ rewards_n,
     float* __restrict__ returns, float* __restrict__ adv_raw, float* __restrict__ adv, ppo_ctrl* ctrl, int N) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   __shared__ double shd[32];
   __shared__ float sA[1024], sB[1024];
   const int tid = threadIdx.x;
@@ -818,6 +863,7 @@ __global__ void __launch_bounds__(128) gather_minibatch_kernel(
     int perm_epochs, const ppo_ctrl* ctrl, uint32_t salt, int N, int S, int A, float* __restrict__ b_states,
     float* __restrict__ b_actions, float* __restrict__ b_logp, float* __restrict__ b_adv,
     float* __restrict__ b_returns) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   const int r = blockIdx.x, pos = ctrl->cursor + r;
   int src;
   if (perm != nullptr)
@@ -833,6 +879,7 @@ __global__ void __launch_bounds__(128) gather_minibatch_kernel(
   }
 }
 __global__ void permutation_kernel(const ppo_ctrl* ctrl, uint32_t salt, int N, int32_t* out) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < N) out[i] = (int32_t)feistel_perm((uint32_t)i, (uint32_t)N, perm_key(ctrl, salt));
 }
@@ -840,6 +887,7 @@ __global__ void permutation_kernel(const ppo_ctrl* ctrl, uint32_t salt, int N, i
 // ---------------------------------------------------------------- clip_grad_norm_ + Adam
 __global__ void __launch_bounds__(256) grad_sumsq_kernel(const float* __restrict__ grad, int n, float* scratch,
                                                          uint32_t* ticket, ppo_ctrl* ctrl, int which) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   __shared__ float red[8];
   __shared__ bool is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -879,6 +927,7 @@ __global__ void __launch_bounds__(256) clip_adam_kernel(float4* __restrict__ the
                                                         float4* __restrict__ m, float4* __restrict__ v, int n4,
                                                         const ppo_ctrl* ctrl, int which, float max_norm,
                                                         float grad_scale, float b1, float b2, float eps) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n4) return;
   const float total = sqrtf(ctrl->norm2[which]) * grad_scale;
@@ -917,6 +966,7 @@ __global__ void ctrl_init_kernel(ppo_ctrl* c, uint64_t seed, float lr_a, float l
   *c = z;
 }
 __global__ void advance_kernel(ppo_ctrl* c, int N, int B) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   c->rng_counter += 1;
   if (B > 0) {
     c->cursor += B;
@@ -926,9 +976,13 @@ __global__ void advance_kernel(ppo_ctrl* c, int N, int B) {
     }
   }
 }
-__global__ void begin_update_kernel(ppo_ctrl* c) { c->cursor = 0; }
+__global__ void begin_update_kernel(ppo_ctrl* c) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  c->cursor = 0;
+}
 
 __global__ void plateau_kernel(ppo_ctrl* c, float factor, int patience) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
   for (int which = 0; which < 2; ++which) {
     const float metric = which == 0 ? c->mean_reward_n : c->critic_loss;
     const float best = c->best[which];
@@ -964,17 +1018,17 @@ int ppo_ctrl_init(ppo_ctrl* c, uint64_t seed, float lr_actor, float lr_critic, v
 
 int ppo_gemm_nt(const float* A, const float* B, float* C, int M, int N, int K, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0) return invalid("gemm sizes");
-  gemm_nt_kernel<<<dim3((N + 31) / 32, (M + 3) / 4), 128, 0, (cudaStream_t)stream>>>(A, B, C, M, N, K);
+  launch_k(gemm_nt_kernel, dim3(dim3((N + 31) / 32, (M + 3) / 4)), dim3(128), (cudaStream_t)stream, use_pdl(), A, B, C, M, N, K);
   PPO_LAUNCH_CHECK("ppo_gemm_nt");
 }
 int ppo_gemm_nn(const float* A, const float* B, float* C, int M, int N, int K, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0) return invalid("gemm sizes");
-  gemm_nn_kernel<<<dim3((K + 31) / 32, (M + 7) / 8), 256, 0, (cudaStream_t)stream>>>(A, B, C, M, N, K);
+  launch_k(gemm_nn_kernel, dim3(dim3((K + 31) / 32, (M + 7) / 8)), dim3(256), (cudaStream_t)stream, use_pdl(), A, B, C, M, N, K);
   PPO_LAUNCH_CHECK("ppo_gemm_nn");
 }
 int ppo_gemm_tn(const float* A, const float* B, float* C, int M, int N, int K, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0) return invalid("gemm sizes");
-  gemm_tn_kernel<<<dim3((K + 31) / 32, (N + 7) / 8), 256, 0, (cudaStream_t)stream>>>(A, B, C, M, N, K);
+  launch_k(gemm_tn_kernel, dim3(dim3((K + 31) / 32, (N + 7) / 8)), dim3(256), (cudaStream_t)stream, use_pdl(), A, B, C, M, N, K);
   PPO_LAUNCH_CHECK("ppo_gemm_tn");
 }
 
@@ -984,7 +1038,7 @@ int ppo_relu_ln_fwd(const float* y, const float* bias, const float* gamma, const
   if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
   if (rows <= 0) return invalid("rows");
   if (dropout_p > 0.f && mask_in == nullptr && ctrl == nullptr) return invalid("dropout needs ctrl or mask_in");
-  relu_ln_fwd_kernel<<<(rows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(y, bias, gamma, beta, out, h_save, stats, rows,
+  launch_k(relu_ln_fwd_kernel, dim3((rows + 7) / 8), dim3(256), (cudaStream_t)stream, use_pdl(), y, bias, gamma, beta, out, h_save, stats, rows,
                                                                       H, dropout_p, mask_in, mask_out, ctrl,
                                                                       rng_stream);
   PPO_LAUNCH_CHECK("ppo_relu_ln_fwd");
@@ -995,7 +1049,7 @@ int ppo_relu_ln_bwd_dy(const float* dout, const float* h, const float* stats, co
   if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
   if (rows <= 0) return invalid("rows");
   if (dropout_p > 0.f && mask == nullptr) return invalid("dropout backward needs the mask");
-  relu_ln_bwd_dy_kernel<<<(rows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(dout, h, stats, gamma, mask, dropout_p, dy,
+  launch_k(relu_ln_bwd_dy_kernel, dim3((rows + 7) / 8), dim3(256), (cudaStream_t)stream, use_pdl(), dout, h, stats, gamma, mask, dropout_p, dy,
                                                                          rows, H);
   PPO_LAUNCH_CHECK("ppo_relu_ln_bwd_dy");
 }
@@ -1005,7 +1059,7 @@ int ppo_ln_bwd_gemm_nn(const float* dout, const float* h, const float* stats, co
   if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
   if (rows <= 0 || K <= 0) return invalid("rows / K");
   if (dropout_p > 0.f && mask == nullptr) return invalid("dropout backward needs the mask");
-  ln_bwd_gemm_nn_kernel<<<dim3((K + 31) / 32, (rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
+  launch_k(ln_bwd_gemm_nn_kernel, dim3(dim3((K + 31) / 32, (rows + 7) / 8)), dim3(256), (cudaStream_t)stream, use_pdl(), 
       dout, h, stats, gamma, mask, dropout_p, dy, W, dA, rows, H, K);
   PPO_LAUNCH_CHECK("ppo_ln_bwd_gemm_nn");
 }
@@ -1015,7 +1069,7 @@ int ppo_relu_ln_colsums(const float* dout, const float* h, const float* stats, c
   if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
   if (rows <= 0) return invalid("rows");
   if (dropout_p > 0.f && mask == nullptr) return invalid("dropout backward needs the mask");
-  relu_ln_colsums_kernel<<<H / 32, 256, 0, (cudaStream_t)stream>>>(dout, h, stats, mask, dropout_p, dy, dbias, dgamma,
+  launch_k(relu_ln_colsums_kernel, dim3(H / 32), dim3(256), (cudaStream_t)stream, use_pdl(), dout, h, stats, mask, dropout_p, dy, dbias, dgamma,
                                                                   dbeta, rows, H);
   PPO_LAUNCH_CHECK("ppo_relu_ln_colsums");
 }
@@ -1035,7 +1089,7 @@ int ppo_policy_head(const float* y4, const float* b4, const float* log_std, cons
   if (A <= 0 || A > 64) return invalid("action dim must be in 1..64");
   if (B <= 0) return invalid("B");
   if (scratch == nullptr || ticket == nullptr) return invalid("scratch / ticket");
-  policy_head_kernel<false><<<(B + kHeadRows - 1) / kHeadRows, 256, 0, (cudaStream_t)stream>>>(
+  launch_k(policy_head_kernel<false>, dim3((B + kHeadRows - 1) / kHeadRows), dim3(256), (cudaStream_t)stream, use_pdl(), 
       y4, b4, log_std, actions, old_logp, adv, clip_eps, entropy_coef, dz, db4, dlog_std, logp_out, ctrl, scratch,
       ticket, B, A, nullptr, nullptr, nullptr, 0);
   PPO_LAUNCH_CHECK("ppo_policy_head");
@@ -1049,7 +1103,7 @@ int ppo_policy_head_fused(const float* a3, const float* W4, const float* b4, con
   if (B <= 0 || H3 <= 0 || H3 > 256) return invalid("B / H3 (<= 256)");
   if (scratch == nullptr || ticket == nullptr || a3 == nullptr || W4 == nullptr || dA3 == nullptr)
     return invalid("null operand");
-  policy_head_kernel<true><<<(B + kHeadRows - 1) / kHeadRows, 256, 0, (cudaStream_t)stream>>>(
+  launch_k(policy_head_kernel<true>, dim3((B + kHeadRows - 1) / kHeadRows), dim3(256), (cudaStream_t)stream, use_pdl(), 
       nullptr, b4, log_std, actions, old_logp, adv, clip_eps, entropy_coef, dz, db4, dlog_std, logp_out, ctrl, scratch,
       ticket, B, A, a3, W4, dA3, H3);
   PPO_LAUNCH_CHECK("ppo_policy_head_fused");
@@ -1058,20 +1112,30 @@ int ppo_policy_head_fused(const float* a3, const float* W4, const float* b4, con
 int ppo_value_head(const float* y4, const float* b4, const float* returns, float* dv, float* db4, ppo_ctrl* ctrl,
                    int B, void* stream) {
   if (B <= 0) return invalid("B");
-  value_head_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(y4, b4, returns, dv, db4, ctrl, B);
+  launch_k(value_head_kernel, dim3(1), dim3(1024), (cudaStream_t)stream, use_pdl(), y4, b4, returns, dv, db4, ctrl, B);
   PPO_LAUNCH_CHECK("ppo_value_head");
 }
 
 int ppo_value_head_fused(const float* a3, const float* w4, const float* b4, const float* returns, float* dv,
                          float* dA3, float* db4, ppo_ctrl* ctrl, int B, int H3, void* stream) {
   if (B <= 0 || H3 <= 0 || H3 > 256) return invalid("B / H3 (<= 256)");
-  value_head_fused_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(a3, w4, b4, returns, dv, dA3, db4, ctrl, B, H3);
+  launch_k(value_head_fused_kernel, dim3(1), dim3(1024), (cudaStream_t)stream, use_pdl(), a3, w4, b4, returns, dv, dA3, db4, ctrl, B, H3);
   PPO_LAUNCH_CHECK("ppo_value_head_fused");
+}
+
+/* measurement probe (tools/microbench_chain.py): v[i] += 1 launched plainly (mode 0), with programmatic dependent
+ * launch (1), or with it and an early trigger (2) */
+int ppo_pdl_probe(float* v, int n, int mode, void* stream) {
+  if (n <= 0) return invalid("n");
+  cudaError_t e = launch_k(pdl_probe_kernel, dim3((n + 255) / 256), dim3(256), (cudaStream_t)stream, mode > 0, v, n,
+                           mode > 1 ? 1 : 0);
+  if (e != cudaSuccess) return fail("ppo_pdl_probe", e);
+  return 0;
 }
 
 int ppo_add_bias(const float* y4, const float* b4, float* out, int n, void* stream) {
   if (n <= 0) return invalid("n");
-  add_bias_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(y4, b4, out, n);
+  launch_k(add_bias_kernel, dim3((n + 255) / 256), dim3(256), (cudaStream_t)stream, use_pdl(), y4, b4, out, n);
   PPO_LAUNCH_CHECK("ppo_add_bias");
 }
 
@@ -1079,7 +1143,7 @@ int ppo_sample_actions(const float* y4, const float* b4, const float* log_std, c
                        float* logp, const ppo_ctrl* ctrl, int N, int A, void* stream) {
   if (A <= 0 || A > 64) return invalid("action dim must be in 1..64");
   if (N <= 0) return invalid("N");
-  sample_actions_kernel<<<(N + 7) / 8, 256, 0, (cudaStream_t)stream>>>(y4, b4, log_std, noise_in, actions, logp, ctrl,
+  launch_k(sample_actions_kernel, dim3((N + 7) / 8), dim3(256), (cudaStream_t)stream, use_pdl(), y4, b4, log_std, noise_in, actions, logp, ctrl,
                                                                       N, A);
   PPO_LAUNCH_CHECK("ppo_sample_actions");
 }
@@ -1088,7 +1152,7 @@ int ppo_prepare_batch(const float* rewards, const float* dones, const float* val
                       float gamma, float lam, float* rewards_n, float* returns, float* adv_raw, float* adv,
                       ppo_ctrl* ctrl, int N, void* stream) {
   if (N < 2) return invalid("N must be >= 2 (unbiased std)");
-  prepare_batch_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(rewards, dones, values, next_values, gamma, lam,
+  launch_k(prepare_batch_kernel, dim3(1), dim3(1024), (cudaStream_t)stream, use_pdl(), rewards, dones, values, next_values, gamma, lam,
                                                             rewards_n, returns, adv_raw, adv, ctrl, N);
   PPO_LAUNCH_CHECK("ppo_prepare_batch");
 }
@@ -1099,7 +1163,7 @@ int ppo_gather_minibatch(const float* states, const float* actions, const float*
                          float* b_logp, float* b_adv, float* b_returns, void* stream) {
   if (B <= 0 || N <= 0) return invalid("sizes");
   if (perm != nullptr && perm_epochs <= 0) return invalid("perm_epochs");
-  gather_minibatch_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(states, actions, old_logp, adv, returns, perm,
+  launch_k(gather_minibatch_kernel, dim3(B), dim3(128), (cudaStream_t)stream, use_pdl(), states, actions, old_logp, adv, returns, perm,
                                                               perm_epochs, ctrl, perm_salt, N, S, A, b_states,
                                                               b_actions, b_logp, b_adv, b_returns);
   PPO_LAUNCH_CHECK("ppo_gather_minibatch");
@@ -1107,7 +1171,7 @@ int ppo_gather_minibatch(const float* states, const float* actions, const float*
 
 int ppo_permutation(const ppo_ctrl* ctrl, uint32_t perm_salt, int N, int32_t* out, void* stream) {
   if (N <= 0) return invalid("N");
-  permutation_kernel<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(ctrl, perm_salt, N, out);
+  launch_k(permutation_kernel, dim3((N + 255) / 256), dim3(256), (cudaStream_t)stream, use_pdl(), ctrl, perm_salt, N, out);
   PPO_LAUNCH_CHECK("ppo_permutation");
 }
 
@@ -1118,7 +1182,7 @@ int ppo_grad_sumsq(const float* grad, int n, float* scratch, uint32_t* ticket, p
   int blocks = (n / 4 + 2 * 256 - 1) / (2 * 256);  // two float4 per thread
   if (blocks > 592) blocks = 592;                  // 4 CTAs per SM
   if (blocks < 1) blocks = 1;
-  grad_sumsq_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(grad, n, scratch, ticket, ctrl, which);
+  launch_k(grad_sumsq_kernel, dim3(blocks), dim3(256), (cudaStream_t)stream, use_pdl(), grad, n, scratch, ticket, ctrl, which);
   PPO_LAUNCH_CHECK("ppo_grad_sumsq");
 }
 
@@ -1128,24 +1192,24 @@ int ppo_clip_adam(float* theta, const float* grad, float* m, float* v, int n, co
   if (((reinterpret_cast<uintptr_t>(theta) | reinterpret_cast<uintptr_t>(grad) | reinterpret_cast<uintptr_t>(m) |
         reinterpret_cast<uintptr_t>(v)) & 15) != 0)
     return invalid("theta / grad / m / v must be 16-byte aligned");
-  clip_adam_kernel<<<(n / 4 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+  launch_k(clip_adam_kernel, dim3((n / 4 + 255) / 256), dim3(256), (cudaStream_t)stream, use_pdl(), 
       reinterpret_cast<float4*>(theta), reinterpret_cast<const float4*>(grad), reinterpret_cast<float4*>(m),
       reinterpret_cast<float4*>(v), n / 4, ctrl, which, max_norm, grad_scale, beta1, beta2, eps);
   PPO_LAUNCH_CHECK("ppo_clip_adam");
 }
 
 int ppo_advance(ppo_ctrl* ctrl, int N, int B, void* stream) {
-  advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, N, B);
+  launch_k(advance_kernel, dim3(1), dim3(1), (cudaStream_t)stream, use_pdl(), ctrl, N, B);
   PPO_LAUNCH_CHECK("ppo_advance");
 }
 
 int ppo_begin_update(ppo_ctrl* ctrl, void* stream) {
-  begin_update_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl);
+  launch_k(begin_update_kernel, dim3(1), dim3(1), (cudaStream_t)stream, use_pdl(), ctrl);
   PPO_LAUNCH_CHECK("ppo_begin_update");
 }
 
 int ppo_plateau_step(ppo_ctrl* ctrl, float factor, int patience, void* stream) {
-  plateau_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ctrl, factor, patience);
+  launch_k(plateau_kernel, dim3(1), dim3(1), (cudaStream_t)stream, use_pdl(), ctrl, factor, patience);
   PPO_LAUNCH_CHECK("ppo_plateau_step");
 }
 

@@ -37,6 +37,7 @@ _SIGNATURES = {
     "ppo_policy_head_fused": (I, [P, P, P, P, P, P, P, F, F, P, P, P, P, P, P, P, P, I, I, I, P]),
     "ppo_value_head_fused": (I, [P, P, P, P, P, P, P, P, I, I, P]),
     "ppo_value_head": (I, [P, P, P, P, P, P, I, P]),
+    "ppo_pdl_probe": (I, [P, I, I, P]),
     "ppo_add_bias": (I, [P, P, P, I, P]),
     "ppo_sample_actions": (I, [P, P, P, P, P, P, P, I, I, P]),
     "ppo_prepare_batch": (I, [P, P, P, P, F, F, P, P, P, P, P, I, P]),

@@ -121,6 +121,10 @@ int ppo_value_head(const float* y4, const float* b4, const float* returns, float
 int ppo_value_head_fused(const float* a3, const float* w4, const float* b4, const float* returns, float* dv,
                          float* dA3, float* db4, ppo_ctrl* ctrl_dev, int B, int H3, void* stream);
 
+/* measurement probe: v[i] += 1, launched plainly (mode 0), with programmatic dependent launch (1), or with it
+ * and an early trigger (2) - the per-node cost of a dependent chain (tools/microbench_chain.py). */
+int ppo_pdl_probe(float* v, int n, int mode, void* stream);
+
 /* values[i] = y4[i] + b4 (critic inference on the whole batch). */
 int ppo_add_bias(const float* y4, const float* b4, float* out, int n, void* stream);
 

@@ -43,6 +43,10 @@ gw = torch.empty(H, H, device=dev)
 one = torch.zeros(1, device=dev)
 v = torch.zeros(B, device=dev)
 print("trivial kernel (add_bias, 128 elements)      %.2f us/node" % timed(lambda: lib.ppo_add_bias(v.data_ptr(), one.data_ptr(), v.data_ptr(), B, S())))
+big = torch.zeros(128 * 256, device=dev)
+for mode, name in ((0, "plain"), (1, "PDL"), (2, "PDL + early trigger")):
+    print("probe 128 elements, %-20s        %.2f us/node" % (name, timed(lambda: lib.ppo_pdl_probe(v.data_ptr(), B, mode, S()))))
+    print("probe 32768 elements, %-20s      %.2f us/node" % (name, timed(lambda: lib.ppo_pdl_probe(big.data_ptr(), 128 * 256, mode, S()))))
 print("mm fwd   [128,329] x [256,329]^T             %.2f us/node" % timed(lambda: torch.mm(x, w1.t(), out=y)))
 print("mm fwd   [128,256] x [256,256]^T (dependent) %.2f us/node" % timed(lambda: (torch.mm(a, w2.t(), out=y), torch.mm(y, w2.t(), out=a))) + "  (per pair / 2 below)")
 print("mm dA    [128,256] x [256,256]               %.2f us/node" % timed(lambda: torch.mm(a, w2, out=y2)))
