@@ -49,6 +49,11 @@ cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t
   return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
+#ifdef PPO_EARLY_TRIGGER
+#define PPO_PDL_SYNC() do { cudaTriggerProgrammaticLaunchCompletion(); cudaGridDependencySynchronize(); } while (0)
+#else
+#define PPO_PDL_SYNC() cudaGridDependencySynchronize()
+#endif
 bool use_pdl() {  // PPO_PDL=0 turns programmatic dependent launch off (A/B measurements)
   static const bool on = [] { const char* e = getenv("PPO_PDL"); return e == nullptr || e[0] != '0'; }();
   return on;
@@ -96,7 +101,7 @@ __global__ void __launch_bounds__(256) relu_ln_fwd_kernel(
     const float* __restrict__ beta, float* __restrict__ out, float* h_save, float* __restrict__ stats, int rows,
     int H, float p, const uint8_t* __restrict__ mask_in, uint8_t* __restrict__ mask_out, const ppo_ctrl* ctrl,
     uint32_t rng_stream) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int vpt = H >> 5;
@@ -147,7 +152,7 @@ __global__ void __launch_bounds__(256) relu_ln_bwd_dy_kernel(
     const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
     const float* __restrict__ gamma, const uint8_t* __restrict__ mask, float p, float* __restrict__ dy, int rows,
     int H) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int vpt = H >> 5;
@@ -183,7 +188,7 @@ __global__ void __launch_bounds__(256) relu_ln_colsums_kernel(
     const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
     const uint8_t* __restrict__ mask, float p, const float* __restrict__ dy, float* __restrict__ dbias,
     float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int H) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   __shared__ float red[3][8][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, c = blockIdx.x * 32 + lane;
   const float keep_scale = 1.f / (1.f - p);
@@ -219,7 +224,7 @@ __global__ void __launch_bounds__(256) relu_ln_colsums_kernel(
 // transposing butterfly (31 shuffles) that leaves output element l of the tile on lane l.
 __global__ void __launch_bounds__(128) gemm_nt_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
                                                       float* __restrict__ C, int M, int N, int K) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int m0 = blockIdx.y * 4, n0 = blockIdx.x * 32 + warp * 8;
   if (n0 >= N) return;
@@ -265,7 +270,7 @@ __global__ void __launch_bounds__(128) gemm_nt_kernel(const float* __restrict__ 
 // the 8 partial tiles are added through shared memory in warp order.
 __global__ void __launch_bounds__(256) gemm_nn_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
                                                       float* __restrict__ C, int M, int N, int K) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   __shared__ __align__(16) float As[8][256];  // reused for the partial tiles [8 warps][8 rows][32 k]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int k = blockIdx.x * 32 + lane, m0 = blockIdx.y * 8;
@@ -324,7 +329,7 @@ __global__ void __launch_bounds__(256) ln_bwd_gemm_nn_kernel(
     const float* __restrict__ dout, const float* __restrict__ hbuf, const float* __restrict__ stats,
     const float* __restrict__ gamma, const uint8_t* __restrict__ mask, float p, float* __restrict__ dy,
     const float* __restrict__ Bm, float* __restrict__ C, int M, int H, int K) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   __shared__ __align__(16) float As[8][256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int k = blockIdx.x * 32 + lane, m0 = blockIdx.y * 8;
@@ -406,7 +411,7 @@ __global__ void __launch_bounds__(256) ln_bwd_gemm_nn_kernel(
 // read coalesced), the 8 warps split the contraction index m; partial tiles added through shared memory.
 __global__ void __launch_bounds__(256) gemm_tn_kernel(const float* __restrict__ A, const float* __restrict__ Bm,
                                                       float* __restrict__ C, int M, int N, int K) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   __shared__ __align__(16) float As[256][8];  // reused for the partial tiles [8 warps][8 n][32 k]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int k = blockIdx.x * 32 + lane, n0 = blockIdx.y * 8;
@@ -470,7 +475,7 @@ __global__ void __launch_bounds__(256) policy_head_kernel(
     float clip_eps, float entropy_coef, float* __restrict__ dz, float* __restrict__ db4,
     float* __restrict__ dlog_std, float* __restrict__ logp_out, ppo_ctrl* ctrl, float* scratch, uint32_t* ticket,
     int B, int A, const float* __restrict__ a3, const float* __restrict__ W4, float* __restrict__ dA3, int H3) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   __shared__ float col_b[kHeadRows][64], col_s[kHeadRows][64], red[kHeadRows][2];
   __shared__ bool is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, row = blockIdx.x * kHeadRows + warp;
@@ -623,7 +628,7 @@ __global__ void __launch_bounds__(256) policy_head_kernel(
 __global__ void __launch_bounds__(1024) value_head_kernel(const float* __restrict__ y4, const float* __restrict__ b4,
                                                           const float* __restrict__ returns, float* __restrict__ dv,
                                                           float* __restrict__ db4, ppo_ctrl* ctrl, int B) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   __shared__ float red[32][3];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float sq = 0.f, sv = 0.f, sd = 0.f;
@@ -654,7 +659,7 @@ __global__ void __launch_bounds__(1024) value_head_fused_kernel(
     const float* __restrict__ a3, const float* __restrict__ w4, const float* __restrict__ b4,
     const float* __restrict__ returns, float* __restrict__ dv, float* __restrict__ dA3, float* __restrict__ db4,
     ppo_ctrl* ctrl, int B, int H3) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   __shared__ float red[32][3];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float wv[8];
@@ -691,7 +696,7 @@ __global__ void __launch_bounds__(1024) value_head_fused_kernel(
 
 __global__ void add_bias_kernel(const float* __restrict__ y, const float* __restrict__ b, float* __restrict__ out,
                                 int n) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = y[i] + b[0];
 }
@@ -701,7 +706,7 @@ __global__ void __launch_bounds__(256) sample_actions_kernel(
     const float* __restrict__ y4, const float* __restrict__ b4, const float* __restrict__ log_std,
     const float* __restrict__ noise_in, float* __restrict__ actions, float* __restrict__ logp,
     const ppo_ctrl* ctrl, int N, int A) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= N) return;
   float lp = 0.f;
@@ -745,7 +750,7 @@ __global__ void __launch_bounds__(1024) prepare_batch_kernel(
     const float* __restrict__ rewards, const float* __restrict__ dones, const float* __restrict__ values,
     const float* __restrict__ next_values, float gamma, float lam, float* __restrict__ rewards_n,
     float* __restrict__ returns, float* __restrict__ adv_raw, float* __restrict__ adv, ppo_ctrl* ctrl, int N) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   __shared__ double shd[32];
   __shared__ float sA[1024], sB[1024];
   const int tid = threadIdx.x;
@@ -863,7 +868,7 @@ __global__ void __launch_bounds__(128) gather_minibatch_kernel(
     int perm_epochs, const ppo_ctrl* ctrl, uint32_t salt, int N, int S, int A, float* __restrict__ b_states,
     float* __restrict__ b_actions, float* __restrict__ b_logp, float* __restrict__ b_adv,
     float* __restrict__ b_returns) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   const int r = blockIdx.x, pos = ctrl->cursor + r;
   int src;
   if (perm != nullptr)
@@ -879,7 +884,7 @@ __global__ void __launch_bounds__(128) gather_minibatch_kernel(
   }
 }
 __global__ void permutation_kernel(const ppo_ctrl* ctrl, uint32_t salt, int N, int32_t* out) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < N) out[i] = (int32_t)feistel_perm((uint32_t)i, (uint32_t)N, perm_key(ctrl, salt));
 }
@@ -887,7 +892,7 @@ __global__ void permutation_kernel(const ppo_ctrl* ctrl, uint32_t salt, int N, i
 // ---------------------------------------------------------------- clip_grad_norm_ + Adam
 __global__ void __launch_bounds__(256) grad_sumsq_kernel(const float* __restrict__ grad, int n, float* scratch,
                                                          uint32_t* ticket, ppo_ctrl* ctrl, int which) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   __shared__ float red[8];
   __shared__ bool is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -927,7 +932,7 @@ __global__ void __launch_bounds__(256) clip_adam_kernel(float4* __restrict__ the
                                                         float4* __restrict__ m, float4* __restrict__ v, int n4,
                                                         const ppo_ctrl* ctrl, int which, float max_norm,
                                                         float grad_scale, float b1, float b2, float eps) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n4) return;
   const float total = sqrtf(ctrl->norm2[which]) * grad_scale;
@@ -966,7 +971,7 @@ __global__ void ctrl_init_kernel(ppo_ctrl* c, uint64_t seed, float lr_a, float l
   *c = z;
 }
 __global__ void advance_kernel(ppo_ctrl* c, int N, int B) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   c->rng_counter += 1;
   if (B > 0) {
     c->cursor += B;
@@ -977,12 +982,12 @@ __global__ void advance_kernel(ppo_ctrl* c, int N, int B) {
   }
 }
 __global__ void begin_update_kernel(ppo_ctrl* c) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   c->cursor = 0;
 }
 
 __global__ void plateau_kernel(ppo_ctrl* c, float factor, int patience) {
-  cudaGridDependencySynchronize();  // programmatic dependent launch: see launch_k
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
   for (int which = 0; which < 2; ++which) {
     const float metric = which == 0 ? c->mean_reward_n : c->critic_loss;
     const float best = c->best[which];

@@ -5,7 +5,10 @@ from __future__ import annotations
 import ctypes
 from pathlib import Path
 
-LIB_PATH = Path(__file__).resolve().parents[1] / "libppo_kernels.so"
+import os
+
+# PPO_KERNELS_LIB: an alternative build of the same library (A/B measurements of kernel variants)
+LIB_PATH = Path(os.environ.get("PPO_KERNELS_LIB") or Path(__file__).resolve().parents[1] / "libppo_kernels.so")
 _lib = None
 
 P, I, F, U32, U64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_uint32, ctypes.c_uint64
