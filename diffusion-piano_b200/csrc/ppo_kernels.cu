@@ -957,6 +957,87 @@ __global__ void __launch_bounds__(256) clip_adam_kernel(float4* __restrict__ the
   theta[i] = p4;
 }
 
+// ---------------------------------------------------------------- gradient all-reduce over NVLink peer memory
+// One kernel per network and minibatch instead of NCCL all-reduce + grad_sumsq: every rank's gradient buffer lives in
+// symmetric memory (the same allocation mapped into every process; torch.distributed._symmetric_memory does the
+// IPC), `grads[p]` is rank p's buffer as seen from this GPU. Each CTA (1) tells the same CTA of every peer that this
+// rank's backward kernels are done and waits for theirs, (2) sums its slice over the ranks in rank order - so every
+// rank gets bit-identical sums - into the local `out` while accumulating the squared norm, (3) meets the peers again
+// before anyone may overwrite a gradient buffer. Flags are monotonically increasing epochs in symmetric memory
+// (flags[p] = rank p's flag array, layout [2 barriers][CTA][source rank]); the epoch lives on the device and is
+// bumped by the last CTA, so a CUDA-graph replay needs no host value. A wait that does not complete within ~2 s
+// sets ctrl-side error word `*error` instead of hanging the GPU.
+constexpr int kArCtas = 64, kArMaxWorld = 16;
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void peer_barrier(uint32_t* const* flags, int which_barrier, int rank, int world,
+                                             uint32_t epoch, uint32_t* error) {
+  __syncthreads();
+  if (threadIdx.x < world) {
+    const int slot = (which_barrier * kArCtas + blockIdx.x) * kArMaxWorld;
+    __threadfence_system();
+    st_release_sys(flags[threadIdx.x] + slot + rank, epoch);           // tell peer threadIdx.x
+    const uint32_t* mine = flags[rank] + slot + threadIdx.x;           // hear from peer threadIdx.x
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+      if (clock64() - t0 > 4000000000LL) { atomicExch(error, 1u); break; }  // ~2 s at 1.9 GHz
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) allreduce_sumsq_kernel(const float* const* grads, uint32_t* const* flags,
+                                                              float* __restrict__ out, int n, int rank, int world,
+                                                              uint32_t* epoch_dev, uint32_t* error, float* scratch,
+                                                              uint32_t* ticket, ppo_ctrl* ctrl, int which) {
+  PPO_PDL_SYNC();
+  __shared__ float red[8];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t epoch = *epoch_dev;
+  peer_barrier(flags, 0, rank, world, epoch, error);
+  const int n4 = n >> 2;
+  float s = 0.f;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < n4; i += gridDim.x * 256) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int p = 0; p < world; ++p) {
+      const float4 g = reinterpret_cast<const float4*>(grads[p])[i];
+      a.x += g.x; a.y += g.y; a.z += g.z; a.w += g.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = a;
+    s += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+  }
+  peer_barrier(flags, 1, rank, world, epoch, error);
+  s = warp_sum(s);
+  if (lane == 0) red[warp] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    scratch[blockIdx.x] = t;
+    __threadfence();
+    is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last || warp != 0) return;
+  __threadfence();
+  float t = 0.f;
+  for (int b = lane; b < (int)gridDim.x; b += 32) t += __ldcg(scratch + b);
+  t = warp_sum(t);
+  if (lane == 0) {
+    ctrl->norm2[which] = t;
+    ctrl->adam_t[which] += 1;
+    *epoch_dev = epoch + 1;
+    *ticket = 0;
+  }
+}
+
 // ---------------------------------------------------------------- control block
 __global__ void ctrl_init_kernel(ppo_ctrl* c, uint64_t seed, float lr_a, float lr_c) {
   ppo_ctrl z = {};
@@ -1190,6 +1271,17 @@ int ppo_grad_sumsq(const float* grad, int n, float* scratch, uint32_t* ticket, p
   launch_k(grad_sumsq_kernel, dim3(blocks), dim3(256), (cudaStream_t)stream, use_pdl(), grad, n, scratch, ticket, ctrl, which);
   PPO_LAUNCH_CHECK("ppo_grad_sumsq");
 }
+
+int ppo_allreduce_sumsq(const float* const* grads_dev, uint32_t* const* flags_dev, float* out, int n, int rank,
+                        int world, uint32_t* epoch_dev, uint32_t* error_dev, float* scratch, uint32_t* ticket,
+                        ppo_ctrl* ctrl, int which, void* stream) {
+  if (n <= 0 || (n & 3) != 0 || (which != 0 && which != 1)) return invalid("n (a multiple of 4) / which");
+  if (world < 1 || world > kArMaxWorld || rank < 0 || rank >= world) return invalid("rank / world (<= 16)");
+  launch_k(allreduce_sumsq_kernel, dim3(kArCtas), dim3(256), (cudaStream_t)stream, use_pdl(), grads_dev, flags_dev,
+           out, n, rank, world, epoch_dev, error_dev, scratch, ticket, ctrl, which);
+  PPO_LAUNCH_CHECK("ppo_allreduce_sumsq");
+}
+int ppo_allreduce_flag_words(void) { return 2 * kArCtas * kArMaxWorld; }
 
 int ppo_clip_adam(float* theta, const float* grad, float* m, float* v, int n, const ppo_ctrl* ctrl, int which,
                   float max_norm, float grad_scale, float beta1, float beta2, float eps, void* stream) {

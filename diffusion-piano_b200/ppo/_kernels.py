@@ -47,6 +47,8 @@ _SIGNATURES = {
     "ppo_gather_minibatch": (I, [P, P, P, P, P, P, I, P, U32, I, I, I, I, P, P, P, P, P, P]),
     "ppo_permutation": (I, [P, U32, I, P, P]),
     "ppo_grad_sumsq": (I, [P, I, P, P, P, I, P]),
+    "ppo_allreduce_sumsq": (I, [P, P, P, I, I, I, P, P, P, P, P, I, P]),
+    "ppo_allreduce_flag_words": (I, []),
     "ppo_clip_adam": (I, [P, P, P, P, I, P, I, F, F, F, F, F, P]),
     "ppo_advance": (I, [P, I, I, P]),
     "ppo_begin_update": (I, [P, P]),

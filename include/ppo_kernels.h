@@ -154,6 +154,18 @@ int ppo_permutation(const ppo_ctrl* ctrl_dev, uint32_t perm_salt, int N, int32_t
  * grad 16-byte aligned; scratch >= 592 floats, ticket as above. */
 int ppo_grad_sumsq(const float* grad, int n, float* scratch, uint32_t* ticket, ppo_ctrl* ctrl_dev, int which,
                    void* stream);
+/* Gradient all-reduce over NVLink peer memory fused with ppo_grad_sumsq (several GPUs, one process each):
+ * grads_dev [world] = every rank's gradient buffer as mapped into THIS process (symmetric memory), flags_dev
+ * [world] = every rank's zero-initialised flag array of ppo_allreduce_flag_words() uint32 (symmetric memory too),
+ * out [n] = sum over ranks (rank order, bit-identical on all ranks), ctrl->norm2[which] = |out|^2,
+ * ctrl->adam_t[which] += 1. epoch_dev: one uint32 initialised to 1; error_dev: one uint32, set to 1 if a peer did
+ * not arrive within ~2 s. Every rank must launch it the same number of times (replaces the NCCL all-reduce the
+ * reference's sharded form needs between `backward()` and `clip_grad_norm_`, ppo_v2.py:277-287). */
+int ppo_allreduce_sumsq(const float* const* grads_dev, uint32_t* const* flags_dev, float* out, int n, int rank,
+                        int world, uint32_t* epoch_dev, uint32_t* error_dev, float* scratch, uint32_t* ticket,
+                        ppo_ctrl* ctrl_dev, int which, void* stream);
+int ppo_allreduce_flag_words(void);
+
 /* n a multiple of 4, buffers 16-byte aligned.
  * g = grad * grad_scale * min(1, max_norm / (sqrt(norm2) * grad_scale + 1e-6)); Adam(b1, b2, eps) with
  * lr = ctrl->lr[which], t = ctrl->adam_t[which]. grad_scale = 1/world_size after a summing all-reduce. */
