@@ -967,27 +967,22 @@ __global__ void __launch_bounds__(256) clip_adam_kernel(float4* __restrict__ the
 // (flags[p] = rank p's flag array, layout [2 barriers][CTA][source rank]); the epoch lives on the device and is
 // bumped by the last CTA, so a CUDA-graph replay needs no host value. A wait that does not complete within ~2 s
 // sets ctrl-side error word `*error` instead of hanging the GPU.
-constexpr int kArCtas = 64, kArMaxWorld = 16;
+constexpr int kArCtas = 112, kArMaxWorld = 8;  // 112 CTAs x 256 threads x 2 float4 cover a 0.9 MB gradient
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
 }
 __device__ __forceinline__ void peer_barrier(uint32_t* const* flags, int which_barrier, int rank, int world,
                                              uint32_t epoch, uint32_t* error) {
   __syncthreads();
   if (threadIdx.x < world) {
     const int slot = (which_barrier * kArCtas + blockIdx.x) * kArMaxWorld;
-    __threadfence_system();
     st_release_sys(flags[threadIdx.x] + slot + rank, epoch);           // tell peer threadIdx.x
-    const uint32_t* mine = flags[rank] + slot + threadIdx.x;           // hear from peer threadIdx.x
+    const volatile uint32_t* mine = flags[rank] + slot + threadIdx.x;  // hear from peer threadIdx.x
     const long long t0 = clock64();
-    while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+    while ((int)(*mine - epoch) < 0) {
       if (clock64() - t0 > 4000000000LL) { atomicExch(error, 1u); break; }  // ~2 s at 1.9 GHz
     }
+    __threadfence_system();  // acquire: the peers' gradients written before their signal
   }
   __syncthreads();
 }
@@ -1004,16 +999,24 @@ __global__ void __launch_bounds__(256) allreduce_sumsq_kernel(const float* const
   peer_barrier(flags, 0, rank, world, epoch, error);
   const int n4 = n >> 2;
   float s = 0.f;
+  const float4* src[kArMaxWorld];
+#pragma unroll
+  for (int p = 0; p < kArMaxWorld; ++p) src[p] = reinterpret_cast<const float4*>(grads[p < world ? p : 0]);
   for (int i = blockIdx.x * 256 + threadIdx.x; i < n4; i += gridDim.x * 256) {
+    // all ranks' loads of this element are issued before the first add (remote latency paid once per element)
+    float4 g[kArMaxWorld];
+#pragma unroll
+    for (int p = 0; p < kArMaxWorld; ++p)
+      if (p < world) g[p] = src[p][i];
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int p = 0; p < world; ++p) {
-      const float4 g = reinterpret_cast<const float4*>(grads[p])[i];
-      a.x += g.x; a.y += g.y; a.z += g.z; a.w += g.w;
-    }
+#pragma unroll
+    for (int p = 0; p < kArMaxWorld; ++p)
+      if (p < world) { a.x += g[p].x; a.y += g[p].y; a.z += g[p].z; a.w += g[p].w; }
     reinterpret_cast<float4*>(out)[i] = a;
     s += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
   }
-  peer_barrier(flags, 1, rank, world, epoch, error);
+  if (!(which & 256)) peer_barrier(flags, 1, rank, world, epoch, error);
+  which &= 255;
   s = warp_sum(s);
   if (lane == 0) red[warp] = s;
   __syncthreads();
@@ -1275,8 +1278,8 @@ int ppo_grad_sumsq(const float* grad, int n, float* scratch, uint32_t* ticket, p
 int ppo_allreduce_sumsq(const float* const* grads_dev, uint32_t* const* flags_dev, float* out, int n, int rank,
                         int world, uint32_t* epoch_dev, uint32_t* error_dev, float* scratch, uint32_t* ticket,
                         ppo_ctrl* ctrl, int which, void* stream) {
-  if (n <= 0 || (n & 3) != 0 || (which != 0 && which != 1)) return invalid("n (a multiple of 4) / which");
-  if (world < 1 || world > kArMaxWorld || rank < 0 || rank >= world) return invalid("rank / world (<= 16)");
+  if (n <= 0 || (n & 3) != 0 || ((which & 255) != 0 && (which & 255) != 1)) return invalid("n (a multiple of 4) / which");
+  if (world < 1 || world > kArMaxWorld || rank < 0 || rank >= world) return invalid("rank / world (<= 8)");
   launch_k(allreduce_sumsq_kernel, dim3(kArCtas), dim3(256), (cudaStream_t)stream, use_pdl(), grads_dev, flags_dev,
            out, n, rank, world, epoch_dev, error_dev, scratch, ticket, ctrl, which);
   PPO_LAUNCH_CHECK("ppo_allreduce_sumsq");

@@ -159,8 +159,12 @@ int ppo_grad_sumsq(const float* grad, int n, float* scratch, uint32_t* ticket, p
  * [world] = every rank's zero-initialised flag array of ppo_allreduce_flag_words() uint32 (symmetric memory too),
  * out [n] = sum over ranks (rank order, bit-identical on all ranks), ctrl->norm2[which] = |out|^2,
  * ctrl->adam_t[which] += 1. epoch_dev: one uint32 initialised to 1; error_dev: one uint32, set to 1 if a peer did
- * not arrive within ~2 s. Every rank must launch it the same number of times (replaces the NCCL all-reduce the
- * reference's sharded form needs between `backward()` and `clip_grad_norm_`, ppo_v2.py:277-287). */
+ * not arrive within ~2 s. Every rank must launch it the same number of times (stands for the NCCL all-reduce the
+ * reference's sharded form needs between `backward()` and `clip_grad_norm_`, ppo_v2.py:277-287). `which | 256`
+ * skips the closing barrier - a TIMING experiment only (tools/probe_peer_allreduce.py), unsafe otherwise.
+ * Status: exact against NCCL on 2 x B200 and graph-replayable, but 27.9 us per call against 19.2 us for NCCL's
+ * all-reduce of the same 0.91 MB (+ ~3 us for ppo_grad_sumsq): each cross-GPU flag barrier costs ~9 us here, so
+ * the agent keeps NCCL (profiles/r01_ppo_summary.md). world <= 8. */
 int ppo_allreduce_sumsq(const float* const* grads_dev, uint32_t* const* flags_dev, float* out, int n, int rank,
                         int world, uint32_t* epoch_dev, uint32_t* error_dev, float* scratch, uint32_t* ticket,
                         ppo_ctrl* ctrl_dev, int which, void* stream);

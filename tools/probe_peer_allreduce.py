@@ -27,7 +27,7 @@ flags = symm.empty(lib.ppo_allreduce_flag_words(), dtype=torch.int32, device=dev
 flags.zero_()
 hg = symm.rendezvous(grad, td.group.WORLD)
 hf = symm.rendezvous(flags, td.group.WORLD)
-print(rank, "multicast", hg.has_multicast_support, "ptrs", [hex(p) for p in hg.buffer_ptrs][:2], flush=True)
+print(rank, "multicast_ptr", hex(hg.multicast_ptr), "ptrs", [hex(p) for p in hg.buffer_ptrs][:2], flush=True)
 out = torch.zeros(n, device=dev)
 epoch = torch.ones(1, dtype=torch.int32, device=dev)
 err = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -38,10 +38,13 @@ td.barrier()
 torch.cuda.synchronize()
 
 
+MODE = int(os.environ.get("PEER_AR_MODE", "0"))  # 256: timing experiment without the closing barrier (unsafe)
+
+
 def call():
     _kernels.check(lib.ppo_allreduce_sumsq(hg.buffer_ptrs_dev, hf.buffer_ptrs_dev, out.data_ptr(), n, rank, world,
                                            epoch.data_ptr(), err.data_ptr(), scratch.data_ptr(), ticket.data_ptr(),
-                                           ctrl.data_ptr(), 0, torch.cuda.current_stream().cuda_stream))
+                                           ctrl.data_ptr(), MODE, torch.cuda.current_stream().cuda_stream))
 
 
 g = torch.Generator(device=dev).manual_seed(rank)
