@@ -129,7 +129,8 @@ class PPOAgent:
     def __init__(self, state_dim, action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, entropy_coef=0.01, value_coef=1.0,
                  max_grad_norm=0.5, ppo_epochs=10, batch_size=64, device="cuda", checkpoint_dir="checkpoints",
                  use_wandb=False, seed: Optional[int] = 0, process_group=None, dropout_p: float = DROPOUT_P,
-                 use_graphs: bool = True, graph_scope: str = "update", gemm: str = "custom"):
+                 use_graphs: bool = True, graph_scope: str = "update", gemm: str = "custom",
+                 fuse_policy_head: bool = False, fuse_value_head: bool = True):
         if use_wandb:
             raise NotImplementedError("wandb logging is not part of the device path; read agent.stats() instead")
         if not torch.cuda.is_available():
@@ -150,9 +151,7 @@ class PPOAgent:
         # heads with the last Linear and its dA inside (ppo_*_head_fused). Measured on B200 (update, B = 4096):
         # neither 25.3 ms, value head only 25.0 ms, policy head only 29.9 ms (the 45-wide head does 2 x 360 loads
         # per warp on 16 CTAs: slower than the two GEMM launches it saves) - so only the value head by default
-        import os
-        self.fuse_policy_head = os.environ.get("PPO_FUSE_POLICY_HEAD", "0") == "1"
-        self.fuse_value_head = os.environ.get("PPO_FUSE_VALUE_HEAD", "1") == "1"
+        self.fuse_policy_head, self.fuse_value_head = bool(fuse_policy_head), bool(fuse_value_head)
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0

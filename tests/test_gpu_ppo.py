@@ -285,7 +285,7 @@ def test_update_matches_reference_and_oracle(torch_cuda):
     assert abs(c.actor_loss - al) < 2e-4 * max(1.0, abs(al))
 
 
-def test_fused_heads_match_unfused(torch_cuda, monkeypatch):
+def test_fused_heads_match_unfused(torch_cuda):
     """ppo_policy_head_fused / ppo_value_head_fused (last Linear and its dA inside the head kernel) against the
     three-launch path: same update on the reference's recorded permutations and masks."""
     torch = torch_cuda
@@ -293,11 +293,9 @@ def test_fused_heads_match_unfused(torch_cuda, monkeypatch):
     n_mb = epochs * ((n + batch - 1) // batch)
     dm = lambda m: torch.as_tensor(m.astype(np.uint8), device="cuda")  # noqa: E731
     results = []
-    for pol, val in (("0", "0"), ("1", "1")):
-        monkeypatch.setenv("PPO_FUSE_POLICY_HEAD", pol)
-        monkeypatch.setenv("PPO_FUSE_VALUE_HEAD", val)
-        ag = _agent(torch, sd, ad, actor, critic, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch, ppo_epochs=epochs)
-        assert ag.fuse_policy_head == (pol == "1") and ag.fuse_value_head == (val == "1")
+    for fused in (False, True):
+        ag = _agent(torch, sd, ad, actor, critic, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch, ppo_epochs=epochs,
+                    fuse_policy_head=fused, fuse_value_head=fused)
         ag.update(b["states"], b["actions"], b["rewards"].astype(np.float32), z["log_probs"], b["next_states"],
                   b["dones"], perms=z["perms"], value_masks=[dm(m) for m in masks[0:2]],
                   next_value_masks=[dm(m) for m in masks[2:4]],
