@@ -472,3 +472,24 @@ def test_reference_loop_with_numpy_api(torch_cuda):
     assert st["adam_steps"] == 3 * 2 * 2 and np.isfinite(st["actor_loss"]) and np.isfinite(episode_rewards).all()
     assert (agent.actor.theta - before).abs().max().item() > 0
     vec_env.batched.close()
+
+
+def test_large_minibatch_takes_the_cublas_path(torch_cuda):
+    """batch_size above the small-M limit (512): cuBLAS GEMMs and the unfused heads; same update rule."""
+    torch = torch_cuda
+    from make_ppo_golden import ppo_fixture_inputs
+    from oracle import ppo_oracle as po
+
+    sd, ad, n, batch = 33, 45, 1500, 1000
+    actor, critic, b = ppo_fixture_inputs(21, sd, ad, n)
+    ag = _agent(torch, sd, ad, actor, critic, batch_size=batch, ppo_epochs=1, dropout_p=0.0, seed=2, use_graphs=False)
+    assert batch > ag.small_m
+    ora = po.PPOOracle(actor, critic, batch_size=batch, ppo_epochs=1)
+    logp = (ora.log_prob(b["states"], b["actions"].astype(np.float64)) + 0.05).astype(np.float32)
+    perm = np.random.RandomState(1).permutation(n)[None].astype(np.int32)
+    rewards = b["rewards"].astype(np.float32)
+    ag.update(b["states"], b["actions"], rewards, logp, b["next_states"], b["dones"], perms=perm)
+    ora.update(b["states"], b["actions"], rewards, logp, b["next_states"], b["dones"], perms=perm)
+    for mine, theirs in ((ag.actor_state_dict(), ora.actor_state()), (ag.critic_state_dict(), ora.critic_state())):
+        for k, v in mine.items():
+            np.testing.assert_allclose(v.numpy(), theirs[k], atol=5e-6, err_msg=k)
