@@ -265,6 +265,112 @@ __global__ void __launch_bounds__(128) gemm_nt_kernel(const float* __restrict__ 
   if (mi < M && nj < N) C[(size_t)mi * N + nj] = acc[0];
 }
 
+// gemm_nt with the PREVIOUS block's epilogue as its prologue: A is not read but computed,
+// A[m,:] = dropout(LayerNorm(relu(Yp[m,:] + bias))) for the warp's 4 rows (K = the previous block's width, a multiple
+// of 32 and <= 256, so a lane holds its 8 values of each row in registers for the whole k loop), then C = A . B^T as
+// above. Every warp of a row group recomputes the same A rows (cheap next to the 8 x K weight loads); the warp with
+// blockIdx.x == 0, warp 0 also stores A, the post-ReLU values and the row statistics that the backward needs.
+// Dropout keep-masks come from `mask` [M,K] bytes (dropout_mask_kernel, off the dependent chain).
+__global__ void __launch_bounds__(128) ln_gemm_nt_kernel(const float* __restrict__ Yp, const float* __restrict__ bias,
+                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                         const uint8_t* __restrict__ mask, float p,
+                                                         float* __restrict__ Aout, float* __restrict__ Hout,
+                                                         float* __restrict__ stats, const float* __restrict__ Bm,
+                                                         float* __restrict__ C, int M, int N, int K) {
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int m0 = blockIdx.y * 4, n0 = blockIdx.x * 32 + warp * 8;
+  if (n0 >= N) return;
+  const int vpt = K >> 5;
+  const bool writer = blockIdx.x == 0 && warp == 0;
+  const float keep_scale = 1.f / (1.f - p);
+  float a[4][8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int row = min(m0 + i, M - 1);
+    float h[8], sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      h[j] = 0.f;
+      if (j < vpt) {
+        const int c = lane + 32 * j;
+        h[j] = fmaxf(Yp[(size_t)row * K + c] + bias[c], 0.f);
+        sum += h[j];
+      }
+    }
+    const float mu = warp_sum(sum) / K;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (j < vpt) q += (h[j] - mu) * (h[j] - mu);
+    const float rstd = rsqrtf(warp_sum(q) / K + kLnEps);
+    const bool store = writer && m0 + i < M;
+    if (store && lane == 0) {
+      stats[2 * row] = mu;
+      stats[2 * row + 1] = rstd;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      a[i][j] = 0.f;
+      if (j < vpt) {
+        const int c = lane + 32 * j;
+        float o = (h[j] - mu) * rstd * gamma[c] + beta[c];
+        if (p > 0.f) o = mask[(size_t)row * K + c] ? o * keep_scale : 0.f;
+        a[i][j] = o;
+        if (store) {
+          Aout[(size_t)row * K + c] = o;
+          Hout[(size_t)row * K + c] = h[j];
+        }
+      }
+    }
+  }
+  const float* bp[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) bp[j] = Bm + (size_t)min(n0 + j, N - 1) * K;
+  float acc[32];
+#pragma unroll
+  for (int t = 0; t < 32; ++t) acc[t] = 0.f;
+#pragma unroll
+  for (int kk = 0; kk < 8; ++kk)
+    if (kk < vpt) {
+      const int k = 32 * kk + lane;
+      float wv[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) wv[j] = bp[j][k];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i * 8 + j] = fmaf(a[i][kk], wv[j], acc[i * 8 + j]);
+    }
+#pragma unroll
+  for (int off = 16, n = 16; off >= 1; off >>= 1, n >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      if (t < n) {
+        const float send = up ? acc[t] : acc[t + n], keep = up ? acc[t + n] : acc[t];
+        acc[t] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      }
+  }
+  const int mi = m0 + (lane >> 3), nj = n0 + (lane & 7);
+  if (mi < M && nj < N) C[(size_t)mi * N + nj] = acc[0];
+}
+
+// Dropout keep-masks of one network forward (same Philox streams as relu_ln_fwd_kernel: stream id + block index).
+__global__ void __launch_bounds__(256) dropout_mask_kernel(uint8_t* __restrict__ mask, int rows, int H, float p,
+                                                           const ppo_ctrl* ctrl, uint32_t rng_stream) {
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
+  const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const uint4 r0 = rng4(ctrl, rng_stream, (uint32_t)(row * 64 + lane * 2));
+  const uint4 r1 = rng4(ctrl, rng_stream, (uint32_t)(row * 64 + lane * 2 + 1));
+  const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+  const int vpt = H >> 5;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j < vpt) mask[(size_t)row * H + lane + 32 * j] = u01(rr[j]) >= p;
+}
+
 // C[M,K] = A[M,N] . B[N,K] (dA = dY x W). CTA = 8 output rows x 32 output columns; lane = column k (B rows are read
 // coalesced), the 8 warps split the contraction index n, so that every warp has all its B loads in flight at once;
 // the 8 partial tiles are added through shared memory in warp order.
@@ -1109,6 +1215,23 @@ int ppo_gemm_nt(const float* A, const float* B, float* C, int M, int N, int K, v
   if (M <= 0 || N <= 0 || K <= 0) return invalid("gemm sizes");
   launch_k(gemm_nt_kernel, dim3(dim3((N + 31) / 32, (M + 3) / 4)), dim3(128), (cudaStream_t)stream, use_pdl(), A, B, C, M, N, K);
   PPO_LAUNCH_CHECK("ppo_gemm_nt");
+}
+int ppo_ln_gemm_nt(const float* y_prev, const float* bias, const float* gamma, const float* beta, const uint8_t* mask,
+                   float dropout_p, float* a_out, float* h_out, float* stats, const float* W, float* C, int M, int N,
+                   int K, void* stream) {
+  if (M <= 0 || N <= 0) return invalid("gemm sizes");
+  if (K % 32 != 0 || K > 256 || K <= 0) return invalid("K (the previous block's width) must be a multiple of 32, <= 256");
+  if (dropout_p > 0.f && mask == nullptr) return invalid("dropout needs the mask (ppo_dropout_mask)");
+  launch_k(ln_gemm_nt_kernel, dim3((N + 31) / 32, (M + 3) / 4), dim3(128), (cudaStream_t)stream, use_pdl(), y_prev,
+           bias, gamma, beta, mask, dropout_p, a_out, h_out, stats, W, C, M, N, K);
+  PPO_LAUNCH_CHECK("ppo_ln_gemm_nt");
+}
+int ppo_dropout_mask(uint8_t* mask, int rows, int H, float dropout_p, const ppo_ctrl* ctrl, uint32_t rng_stream,
+                     void* stream) {
+  if (H % 32 != 0 || H > 256 || H <= 0 || rows <= 0) return invalid("rows / H");
+  launch_k(dropout_mask_kernel, dim3((rows + 7) / 8), dim3(256), (cudaStream_t)stream, use_pdl(), mask, rows, H,
+           dropout_p, ctrl, rng_stream);
+  PPO_LAUNCH_CHECK("ppo_dropout_mask");
 }
 int ppo_gemm_nn(const float* A, const float* B, float* C, int M, int N, int K, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0) return invalid("gemm sizes");

@@ -117,6 +117,7 @@ class _Net:
             b = {"y": [f(rows, self.dims[i + 1]) for i in range(4)], "a": [f(rows, self.dims[i + 1]) for i in range(3)]}
             if training:
                 b["stats"] = [f(rows, 2) for _ in range(3)]
+                b["h"] = [f(rows, self.dims[i + 1]) for i in range(3)]  # post-ReLU values (LayerNorm backward)
                 b["mask"] = [torch.empty(rows, self.dims[i + 1], dtype=torch.uint8, device=self.device)
                              if self.dropout_after[i] else None for i in range(3)]
                 b["da"] = [f(rows, self.dims[i + 1]) for i in range(3)]
@@ -130,7 +131,7 @@ class PPOAgent:
                  max_grad_norm=0.5, ppo_epochs=10, batch_size=64, device="cuda", checkpoint_dir="checkpoints",
                  use_wandb=False, seed: Optional[int] = 0, process_group=None, dropout_p: float = DROPOUT_P,
                  use_graphs: bool = True, graph_scope: str = "update", gemm: str = "custom",
-                 fuse_policy_head: bool = False, fuse_value_head: bool = True):
+                 fuse_policy_head: bool = False, fuse_value_head: bool = True, fuse_ln: bool = False):
         if use_wandb:
             raise NotImplementedError("wandb logging is not part of the device path; read agent.stats() instead")
         if not torch.cuda.is_available():
@@ -152,6 +153,9 @@ class PPOAgent:
         # neither 25.3 ms, value head only 25.0 ms, policy head only 29.9 ms (the 45-wide head does 2 x 360 loads
         # per warp on 16 CTAs: slower than the two GEMM launches it saves) - so only the value head by default
         self.fuse_policy_head, self.fuse_value_head = bool(fuse_policy_head), bool(fuse_value_head)
+        # block epilogues as the prologue of the next GEMM (ppo_ln_gemm_nt): correct, but every warp of a row group
+        # redoes the LayerNorm of its 4 rows ahead of its k loop - update 26.6 ms against 21.1 ms, so off by default
+        self.fuse_ln = bool(fuse_ln)
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
@@ -213,7 +217,7 @@ class PPOAgent:
         self._mm_nt(x, net.p[f"network.{li}.weight"], buf["y"][blk])
         use_p = p if net.dropout_after[blk] else 0.0
         self._k(self.lib.ppo_relu_ln_fwd, buf["y"][blk], net.p[f"network.{li}.bias"], net.p[f"network.{ni}.weight"],
-                net.p[f"network.{ni}.bias"], buf["a"][blk], buf["y"][blk] if training else None,
+                net.p[f"network.{ni}.bias"], buf["a"][blk], buf["h"][blk] if training else None,
                 buf["stats"][blk] if training else None, x.shape[0], net.dims[blk + 1], use_p,
                 mask_in if use_p > 0 else None,
                 buf["mask"][blk] if (training and use_p > 0) else None, self.ctrl, rng_stream + blk)
@@ -224,6 +228,8 @@ class PPOAgent:
         """Three blocks + the last Linear (without its bias: the head kernels add it). Returns y4 (last=False: the
         fused head kernels compute the last Linear themselves)."""
         buf = net.buffers(x.shape[0], training)
+        if training and self.fuse_ln and self.gemm == "custom" and x.shape[0] <= self.small_m:
+            return self._forward_fused(net, x, buf, p, masks, rng_stream, last), buf
         a, mi = x, 0
         for blk in range(3):
             m = None
@@ -233,6 +239,43 @@ class PPOAgent:
         if last:
             self._mm_nt(a, net.p[f"network.{net.linears[3]}.weight"], buf["y"][3])
         return buf["y"][3], buf
+
+    def _forward_fused(self, net: _Net, x, buf, p: float, masks, rng_stream: int, last: bool):
+        """Training forward of a minibatch with every block's epilogue (bias, ReLU, LayerNorm, dropout) computed as
+        the prologue of the NEXT Linear's GEMM (ppo_ln_gemm_nt): 4 dependent launches instead of 7."""
+        rows = x.shape[0]
+        chain = torch.cuda.current_stream(self.device)
+        mi, wait_masks = 0, False
+        for blk in range(3):
+            if p > 0 and net.dropout_after[blk]:
+                if masks is not None:
+                    buf["mask"][blk].copy_(masks[mi])
+                    mi += 1
+                else:  # Philox keep-masks, generated off the chain while the first GEMM runs
+                    if not wait_masks:
+                        net.cstream.wait_stream(chain)
+                        wait_masks = True
+                    with torch.cuda.stream(net.cstream):
+                        self._k(self.lib.ppo_dropout_mask, buf["mask"][blk], rows, net.dims[blk + 1], p, self.ctrl,
+                                rng_stream + blk)
+        self._mm_nt(x, net.p[f"network.{net.linears[0]}.weight"], buf["y"][0])
+        if wait_masks:
+            chain.wait_stream(net.cstream)
+        for blk in range(3):  # epilogue of block blk + the Linear of block blk + 1
+            li, ni = net.linears[blk], net.norms[blk]
+            use_p = p if net.dropout_after[blk] else 0.0
+            mask = buf["mask"][blk] if use_p > 0 else None
+            if blk < 2 or last:
+                w_next = net.p[f"network.{net.linears[blk + 1]}.weight"]
+                self._k(self.lib.ppo_ln_gemm_nt, buf["y"][blk], net.p[f"network.{li}.bias"],
+                        net.p[f"network.{ni}.weight"], net.p[f"network.{ni}.bias"], mask, use_p, buf["a"][blk],
+                        buf["h"][blk], buf["stats"][blk], w_next, buf["y"][blk + 1], rows, w_next.shape[0],
+                        net.dims[blk + 1])
+            else:  # the fused head computes the last Linear itself: only the epilogue is left
+                self._k(self.lib.ppo_relu_ln_fwd, buf["y"][blk], net.p[f"network.{li}.bias"],
+                        net.p[f"network.{ni}.weight"], net.p[f"network.{ni}.bias"], buf["a"][blk], buf["h"][blk],
+                        buf["stats"][blk], rows, net.dims[blk + 1], use_p, mask, None, self.ctrl, rng_stream + blk)
+        return buf["y"][3]
 
     def _backward(self, net: _Net, x, buf, dz, p: float, da_ready: bool = False):
         """dz = gradient with respect to the last Linear's output; fills net.grad (except the head's bias).
@@ -251,18 +294,18 @@ class PPOAgent:
             mask = buf["mask"][blk] if use_p > 0 else None
             fused = blk > 0 and self.gemm == "custom" and x.shape[0] <= self.small_m
             if fused:  # dy of this block and dA for the block below in one launch
-                self._k(self.lib.ppo_ln_bwd_gemm_nn, buf["da"][blk], buf["y"][blk], buf["stats"][blk],
+                self._k(self.lib.ppo_ln_bwd_gemm_nn, buf["da"][blk], buf["h"][blk], buf["stats"][blk],
                         net.p[f"network.{ni}.weight"], mask, use_p, buf["dy"][blk], net.p[f"network.{li}.weight"],
                         buf["da"][blk - 1], x.shape[0], net.dims[blk + 1], net.dims[blk])
             else:
-                self._k(self.lib.ppo_relu_ln_bwd_dy, buf["da"][blk], buf["y"][blk], buf["stats"][blk],
+                self._k(self.lib.ppo_relu_ln_bwd_dy, buf["da"][blk], buf["h"][blk], buf["stats"][blk],
                         net.p[f"network.{ni}.weight"], mask, use_p, buf["dy"][blk], x.shape[0], net.dims[blk + 1])
             a_prev = x if blk == 0 else buf["a"][blk - 1]
             # parameter gradients of the block leave the chain: column sums and the weight-gradient GEMM
             wstream.wait_stream(chain)
             net.cstream.wait_stream(chain)
             with torch.cuda.stream(net.cstream):
-                self._k(self.lib.ppo_relu_ln_colsums, buf["da"][blk], buf["y"][blk], buf["stats"][blk], mask, use_p,
+                self._k(self.lib.ppo_relu_ln_colsums, buf["da"][blk], buf["h"][blk], buf["stats"][blk], mask, use_p,
                         buf["dy"][blk], net.g[f"network.{li}.bias"], net.g[f"network.{ni}.weight"],
                         net.g[f"network.{ni}.bias"], x.shape[0], net.dims[blk + 1])
             with torch.cuda.stream(wstream):

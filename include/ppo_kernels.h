@@ -71,6 +71,17 @@ int ppo_gemm_nt(const float* A, const float* B, float* C, int M, int N, int K, v
 int ppo_gemm_nn(const float* A, const float* B, float* C, int M, int N, int K, void* stream);
 int ppo_gemm_tn(const float* A, const float* B, float* C, int M, int N, int K, void* stream);
 
+/* ppo_gemm_nt with the previous block's epilogue as its prologue (one dependent launch instead of two):
+ * A = dropout(LayerNorm(relu(y_prev + bias))) [M,K] is computed on the fly (K = that block's width, a multiple of 32,
+ * <= 256), C [M,N] = A . W[N,K]^T; a_out / h_out [M,K] and stats [M,2] receive what ppo_relu_ln_fwd would have
+ * written (h_out must not alias y_prev here). dropout_p > 0 reads keep-masks from `mask` [M,K], made by
+ * ppo_dropout_mask with the Philox stream relu_ln_fwd would use (rng_stream + block index). */
+int ppo_ln_gemm_nt(const float* y_prev, const float* bias, const float* gamma, const float* beta,
+                   const uint8_t* mask, float dropout_p, float* a_out, float* h_out, float* stats, const float* W,
+                   float* C, int M, int N, int K, void* stream);
+int ppo_dropout_mask(uint8_t* mask, int rows, int H, float dropout_p, const ppo_ctrl* ctrl_dev, uint32_t rng_stream,
+                     void* stream);
+
 /* out = dropout(LayerNorm(relu(y + bias))); rows x H, H a multiple of 32 and <= 256. h_save (post-ReLU) and
  * stats [rows,2] = (mean, rstd) are what the backward needs (NULL at inference; h_save may alias y).
  * dropout_p > 0: keep-mask from mask_in [rows,H] bytes if given, else Philox(seed, rng_counter, rng_stream, i);

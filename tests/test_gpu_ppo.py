@@ -293,9 +293,9 @@ def test_fused_heads_match_unfused(torch_cuda):
     n_mb = epochs * ((n + batch - 1) // batch)
     dm = lambda m: torch.as_tensor(m.astype(np.uint8), device="cuda")  # noqa: E731
     results = []
-    for fused in (False, True):
+    for fused in (False, True):  # True: fused heads and the block epilogues as the next GEMM's prologue
         ag = _agent(torch, sd, ad, actor, critic, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch, ppo_epochs=epochs,
-                    fuse_policy_head=fused, fuse_value_head=fused)
+                    fuse_policy_head=fused, fuse_value_head=fused, fuse_ln=fused)
         ag.update(b["states"], b["actions"], b["rewards"].astype(np.float32), z["log_probs"], b["next_states"],
                   b["dones"], perms=z["perms"], value_masks=[dm(m) for m in masks[0:2]],
                   next_value_masks=[dm(m) for m in masks[2:4]],
