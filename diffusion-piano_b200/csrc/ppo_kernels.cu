@@ -3,6 +3,7 @@
 // Everything here is small-batch work (128-row minibatches, 256-wide layers): the kernels are sized so that
 // one minibatch update is a short chain of launches inside a CUDA graph, every reduction has a fixed order
 // (bit-reproducible runs), and all loop state lives in `ppo_ctrl` on the device.
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -263,6 +264,103 @@ __global__ void __launch_bounds__(128) gemm_nt_kernel(const float* __restrict__ 
   }
   const int mi = m0 + (lane >> 3), nj = n0 + (lane & 7);
   if (mi < M && nj < N) C[(size_t)mi * N + nj] = acc[0];
+}
+
+// One block forward in ONE launch: Linear + bias + ReLU + LayerNorm + dropout. The tiling is gemm_nt_kernel's (a CTA
+// = 4 rows x 32 columns, one warp per 4 x 8 tile); the N / 32 CTAs that share 4 rows form a thread-block CLUSTER and
+// exchange their per-row partial sums through distributed shared memory (two cluster barriers: mean, then the
+// centred second moment - the same two-pass variance as relu_ln_fwd_kernel), so that the 4 x N outputs are
+// normalised without leaving the chip and without a second kernel. N a multiple of 32, <= 256 (cluster <= 8).
+__global__ void __launch_bounds__(128) gemm_nt_ln_cluster_kernel(
+    const float* __restrict__ A, const float* __restrict__ Bm, const float* __restrict__ bias,
+    const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ out,
+    float* __restrict__ h_save, float* __restrict__ stats, int M, int N, int K, float p,
+    const uint8_t* __restrict__ mask_in, uint8_t* __restrict__ mask_out, const ppo_ctrl* ctrl, uint32_t rng_stream) {
+  PPO_PDL_SYNC();  // programmatic dependent launch: see launch_k
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  __shared__ float wpart[4][4];  // [warp][row]
+  __shared__ float cpart[2][4];  // this CTA's partial per row: pass 0 sum, pass 1 centred squares
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int m0 = blockIdx.y * 4, n0 = blockIdx.x * 32 + warp * 8;
+  const float* ap[4];
+  const float* bp[8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) ap[i] = A + (size_t)min(m0 + i, M - 1) * K;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) bp[j] = Bm + (size_t)min(n0 + j, N - 1) * K;
+  float acc[32];
+#pragma unroll
+  for (int t = 0; t < 32; ++t) acc[t] = 0.f;
+#pragma unroll 2
+  for (int k0 = 0; k0 < K; k0 += 32) {
+    const int k = k0 + lane;
+    const bool ok = k < K;
+    float xv[4], wv[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) xv[i] = ok ? ap[i][k] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) wv[j] = ok ? bp[j][k] : 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i * 8 + j] = fmaf(xv[i], wv[j], acc[i * 8 + j]);
+  }
+#pragma unroll
+  for (int off = 16, n = 16; off >= 1; off >>= 1, n >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      if (t < n) {
+        const float send = up ? acc[t] : acc[t + n], keep = up ? acc[t + n] : acc[t];
+        acc[t] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      }
+  }
+  // lane l holds the output (row l >> 3, column n0 + (l & 7))
+  const int r = lane >> 3, col = n0 + (lane & 7), row = m0 + r;
+  const float h = fmaxf(acc[0] + bias[col], 0.f);
+  const unsigned nranks = cluster.num_blocks();
+  float mu = 0.f, rstd = 0.f;
+#pragma unroll
+  for (int pass = 0; pass < 2; ++pass) {
+    float v = pass == 0 ? h : (h - mu) * (h - mu);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);  // sum over the warp's 8 columns of row r
+    if ((lane & 7) == 0) wpart[warp][r] = v;
+    __syncthreads();
+    if (threadIdx.x < 4) cpart[pass][threadIdx.x] = wpart[0][threadIdx.x] + wpart[1][threadIdx.x] +
+                                                    wpart[2][threadIdx.x] + wpart[3][threadIdx.x];
+    cluster.sync();  // every CTA's partial of this pass is in its shared memory
+    float t = 0.f;
+    for (unsigned c = 0; c < nranks; ++c) t += cluster.map_shared_rank(&cpart[pass][0], c)[r];  // rank order: same bits everywhere
+    if (pass == 0) mu = t / N;
+    else rstd = rsqrtf(t / N + kLnEps);
+  }
+  if (row < M) {
+    float o = (h - mu) * rstd * gamma[col] + beta[col];
+    const size_t i = (size_t)row * N + col;
+    if (p > 0.f) {
+      bool keep;
+      if (mask_in != nullptr) {
+        keep = mask_in[i] != 0;
+      } else {  // the Philox word relu_ln_fwd_kernel uses for (row, col)
+        const int j = col >> 5;
+        const uint4 rr = rng4(ctrl, rng_stream, (uint32_t)(row * 64 + (col & 31) * 2 + (j >> 2)));
+        const uint32_t w = (j & 3) == 0 ? rr.x : (j & 3) == 1 ? rr.y : (j & 3) == 2 ? rr.z : rr.w;
+        keep = u01(w) >= p;
+      }
+      if (mask_out != nullptr) mask_out[i] = keep;
+      o = keep ? o / (1.f - p) : 0.f;
+    }
+    out[i] = o;
+    if (h_save != nullptr) h_save[i] = h;
+    if (stats != nullptr && blockIdx.x == 0 && warp == 0 && (lane & 7) == 0) {
+      stats[2 * row] = mu;
+      stats[2 * row + 1] = rstd;
+    }
+  }
+  cluster.sync();  // no CTA may exit while a peer still reads its shared memory
 }
 
 // gemm_nt with the PREVIOUS block's epilogue as its prologue: A is not read but computed,
@@ -1215,6 +1313,31 @@ int ppo_gemm_nt(const float* A, const float* B, float* C, int M, int N, int K, v
   if (M <= 0 || N <= 0 || K <= 0) return invalid("gemm sizes");
   launch_k(gemm_nt_kernel, dim3(dim3((N + 31) / 32, (M + 3) / 4)), dim3(128), (cudaStream_t)stream, use_pdl(), A, B, C, M, N, K);
   PPO_LAUNCH_CHECK("ppo_gemm_nt");
+}
+int ppo_linear_relu_ln_fwd(const float* x, const float* W, const float* bias, const float* gamma, const float* beta,
+                           float* out, float* h_save, float* stats, int rows, int H, int K, float dropout_p,
+                           const uint8_t* mask_in, uint8_t* mask_out, const ppo_ctrl* ctrl, uint32_t rng_stream,
+                           void* stream) {
+  if (H % 32 != 0 || H > 256 || H <= 0) return invalid("H must be a multiple of 32, <= 256");
+  if (rows <= 0 || K <= 0) return invalid("rows / K");
+  if (dropout_p > 0.f && mask_in == nullptr && ctrl == nullptr) return invalid("dropout needs ctrl or mask_in");
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(H / 32, (rows + 3) / 4);
+  cfg.blockDim = dim3(128);
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = H / 32;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = use_pdl() ? 2 : 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_nt_ln_cluster_kernel, x, W, bias, gamma, beta, out, h_save, stats,
+                                     rows, H, K, dropout_p, mask_in, mask_out, ctrl, rng_stream);
+  if (e != cudaSuccess) return fail("ppo_linear_relu_ln_fwd", e);
+  PPO_LAUNCH_CHECK("ppo_linear_relu_ln_fwd");
 }
 int ppo_ln_gemm_nt(const float* y_prev, const float* bias, const float* gamma, const float* beta, const uint8_t* mask,
                    float dropout_p, float* a_out, float* h_out, float* stats, const float* W, float* C, int M, int N,

@@ -31,6 +31,7 @@ _SIGNATURES = {
     "ppo_gemm_nt": (I, [P, P, P, I, I, I, P]),
     "ppo_gemm_nn": (I, [P, P, P, I, I, I, P]),
     "ppo_gemm_tn": (I, [P, P, P, I, I, I, P]),
+    "ppo_linear_relu_ln_fwd": (I, [P, P, P, P, P, P, P, P, I, I, I, F, P, P, P, U32, P]),
     "ppo_ln_gemm_nt": (I, [P, P, P, P, P, F, P, P, P, P, P, I, I, I, P]),
     "ppo_dropout_mask": (I, [P, I, I, F, P, U32, P]),
     "ppo_relu_ln_fwd": (I, [P, P, P, P, P, P, P, I, I, F, P, P, P, U32, P]),

@@ -71,6 +71,14 @@ int ppo_gemm_nt(const float* A, const float* B, float* C, int M, int N, int K, v
 int ppo_gemm_nn(const float* A, const float* B, float* C, int M, int N, int K, void* stream);
 int ppo_gemm_tn(const float* A, const float* B, float* C, int M, int N, int K, void* stream);
 
+/* One block forward in one launch: out [rows,H] = dropout(LayerNorm(relu(x [rows,K] . W [H,K]^T + bias))), with
+ * h_save / stats / masks as ppo_relu_ln_fwd. The H / 32 CTAs that share 4 rows form a thread-block cluster and
+ * exchange their row partial sums through distributed shared memory. H a multiple of 32, <= 256. */
+int ppo_linear_relu_ln_fwd(const float* x, const float* W, const float* bias, const float* gamma, const float* beta,
+                           float* out, float* h_save, float* stats, int rows, int H, int K, float dropout_p,
+                           const uint8_t* mask_in, uint8_t* mask_out, const ppo_ctrl* ctrl_dev, uint32_t rng_stream,
+                           void* stream);
+
 /* ppo_gemm_nt with the previous block's epilogue as its prologue (one dependent launch instead of two):
  * A = dropout(LayerNorm(relu(y_prev + bias))) [M,K] is computed on the fly (K = that block's width, a multiple of 32,
  * <= 256), C [M,N] = A . W[N,K]^T; a_out / h_out [M,K] and stats [M,2] receive what ppo_relu_ln_fwd would have

@@ -24,6 +24,7 @@ def main():
                     help="torch: plain-PyTorch restatement of ppo_v2.update (tools/torch_ppo_baseline.py) on the same env")
     ap.add_argument("--graph-scope", default="update", choices=["update", "minibatch"])
     ap.add_argument("--schedule", default="auto", choices=["auto", "lockstep", "divergent"])
+    ap.add_argument("--cluster-ln", action="store_true", help="Linear + LayerNorm as one cluster kernel in the forward")
     ap.add_argument("--fuse-ln", action="store_true", help="block epilogues as the next GEMM's prologue (slower)")
     ap.add_argument("--gemm", default="custom", choices=["custom", "cublas"])
     ap.add_argument("--blas", default=None, help="torch.backends.cuda.preferred_blas_library (cublas / cublaslt)")
@@ -53,7 +54,7 @@ def main():
     if args.impl == "product":
         agent = PPOAgent(env.obs_dim, env.action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=args.batch_size,
                          ppo_epochs=args.epochs, device=f"cuda:{local}", seed=0, process_group=pg,
-                         use_graphs=not args.eager, graph_scope=args.graph_scope, gemm=args.gemm, fuse_ln=args.fuse_ln)
+                         use_graphs=not args.eager, graph_scope=args.graph_scope, gemm=args.gemm, fuse_ln=args.fuse_ln, cluster_ln=args.cluster_ln)
     else:
         sys.path.insert(0, str(ROOT / "tools"))
         from torch_ppo_baseline import TorchPPO
