@@ -156,7 +156,7 @@ def _add_piano(bld: _Builder, actuators: bool) -> None:
     bld.add_geom("piano/base", 0, GEOM_BOX, pm.BASE_POS, (1, 0, 0, 0), pm.BASE_SIZE, CLS_BASE)
 
 
-def _add_hand(bld: _Builder, side: str, position, quaternion, gravcomp: bool, tx_range) -> dict:
+def _add_hand(bld: _Builder, side: str, position, quaternion, gravcomp: bool, tx_range, remove_joints=()) -> dict:
     """Adds one hand; returns index bookkeeping for the task layer."""
     left = side == "left"
     prefix = "lh_" if left else "rh_"
@@ -186,7 +186,7 @@ def _add_hand(bld: _Builder, side: str, position, quaternion, gravcomp: bool, tx
                     model + dof_name, body, JNT_SLIDE, (0, 0, 0), spec["axis"], rng,
                     damping=0.0, armature=shm.HAND_JOINT_DEFAULT["armature"],
                     frictionloss=shm.HAND_JOINT_DEFAULT["frictionloss"])
-        elif node["joint"] is not None:
+        elif node["joint"] is not None and node["joint"]["name"] not in remove_joints:
             j = dict(shm.HAND_JOINT_DEFAULT)
             j.update(shm.JOINT_CLASS[node["joint"]["cls"]])
             info["dof"][node["joint"]["name"]] = bld.add_dof(
@@ -213,6 +213,8 @@ def _add_hand(bld: _Builder, side: str, position, quaternion, gravcomp: bool, tx
     # actuators: 20 menagerie + forearm_tx + forearm_ty
     a = bld.act
     for name, kind, joints, cls in shm.ACTUATORS:
+        if any(jn in remove_joints for jn in joints):
+            continue  # the reference deletes the actuator with its joint (shadow_hand.py:164-171)
         c = shm.ACT_CLASS[cls]
         a["trn0"].append(info["dof"][joints[0]])
         a["trn1"].append(info["dof"][joints[1]] if kind == "tendon" else -1)
@@ -321,14 +323,32 @@ def _mix(a, b):
     return tuple(0.5 * x + 0.5 * y for x, y in zip(a, b))
 
 
+REDUCED_EXCLUDED_JOINTS = ("THJ5", "THJ1", "LFJ5")  # shadow_hand.py:73-77 (actuators A_<joint>)
+REDUCED_THUMB_RANGE = (0.0, 0.698132)               # shadow_hand.py:79
+LOCKED_ARMATURE = 1e8
+
+
 def compile_scene(
     hands: bool = True,
     piano_actuators: bool = False,
     gravity_compensation: bool = False,
     disable_hand_collisions: bool = False,
     physics_timestep: float = 0.005,
+    reduced_action_space: bool = False,
+    reduced_by_removal: bool = False,
 ) -> CompiledModel:
-    """Builds the task scene the reference assembles in `suite/tasks/base.py:45-197`."""
+    """Builds the task scene the reference assembles in `suite/tasks/base.py:45-197`.
+
+    reduced_action_space (`shadow_hand.py:73-79,160-181`): the reference deletes the joints THJ5, THJ1, LFJ5 of
+    each hand together with their actuators (the bodies become welded at angle 0) and narrows THJ2 to
+    (0, 0.698132). The step kernel has a fixed 26-dof tree per hand, so the joints are LOCKED instead: an armature
+    of 1e8 kg m^2 (the dof's acceleration is below 1e-6 rad/s^2 for any force in the model and its coupling to the
+    other dofs below float32 resolution), a range it never reaches, no frictionloss row, no damping, a dead actuator; the constants
+    that MuJoCo derives from the mass matrix (meaninertia, invweight0) are computed on the matrix WITHOUT the
+    locked rows, as the reference's compiled model would have them. `model.locked_dofs` / `model.dead_actuators`
+    list them for the façade, which drops them from the action and observation specs.
+    reduced_by_removal=True builds the reference's own form instead (joints and actuators deleted, nv = 134): the
+    step kernel cannot run it, the oracle can - tests/test_scene_and_oracle.py compares the two."""
     bld = _Builder()
     _add_piano(bld, piano_actuators)
     infos = []
@@ -336,8 +356,26 @@ def compile_scene(
         half_w = pm.BASE_SIZE[1]  # piano.size[1], base.py:160
         for side, position in (("right", RIGHT_HAND_POSITION), ("left", LEFT_HAND_POSITION)):
             tx_range = (-half_w - position[1], half_w - position[1])
-            infos.append(_add_hand(bld, side, position, qnorm(HAND_QUATERNION),
-                                   gravity_compensation, tx_range))
+            infos.append(_add_hand(bld, side, position, qnorm(HAND_QUATERNION), gravity_compensation, tx_range,
+                                   REDUCED_EXCLUDED_JOINTS if reduced_action_space and reduced_by_removal else ()))
+    locked, dead = [], []
+    if hands and reduced_action_space and reduced_by_removal:  # the reference's own construction (oracle only)
+        for info in infos:
+            pre = "rh_" if info is infos[0] else "lh_"
+            d2 = next(i for i, n in enumerate(bld.dof["name"]) if n.endswith("/" + pre + "THJ2"))
+            a2 = next(i for i, n in enumerate(bld.act["name"]) if n.endswith("/" + pre + "A_THJ2"))
+            bld.dof["range"][d2] = REDUCED_THUMB_RANGE
+            bld.act["ctrlrange"][a2] = REDUCED_THUMB_RANGE
+    elif hands and reduced_action_space:
+        for info in infos:
+            pre = "rh_" if info is infos[0] else "lh_"
+            for jn in REDUCED_EXCLUDED_JOINTS:
+                locked.append(next(i for i, n in enumerate(bld.dof["name"]) if n.endswith("/" + pre + jn)))
+                dead.append(next(i for i, n in enumerate(bld.act["name"]) if n.endswith("/" + pre + "A_" + jn)))
+            d2 = next(i for i, n in enumerate(bld.dof["name"]) if n.endswith("/" + pre + "THJ2"))
+            a2 = next(i for i, n in enumerate(bld.act["name"]) if n.endswith("/" + pre + "A_THJ2"))
+            bld.dof["range"][d2] = REDUCED_THUMB_RANGE
+            bld.act["ctrlrange"][a2] = REDUCED_THUMB_RANGE
     M, jacs = _mass_matrix0(bld)
     if hands:
         # physics_utils.get_critical_damping_from_stiffness: 2*sqrt(dof_M0 * k)
@@ -345,7 +383,31 @@ def compile_scene(
             for dof_name, spec in shm.FOREARM_DOFS.items():
                 d = info["dof"][dof_name]
                 bld.dof["damping"][d] = 2.0 * np.sqrt(M[d, d] * spec["stiffness"])
-    dof_inv, body_inv = _invweights(bld, M, jacs)
+    mean_inertia = float(np.mean(np.diag(M)))
+    if locked:
+        keep = np.setdiff1d(np.arange(M.shape[0]), locked)
+        mean_inertia = float(np.mean(np.diag(M)[keep]))
+        M_lock = M.copy()
+        for d in locked:  # decouple and freeze: what deleting the joint does to every derived constant
+            M_lock[d, :] = 0.0
+            M_lock[:, d] = 0.0
+            M_lock[d, d] = LOCKED_ARMATURE
+            bld.dof["armature"][d] = LOCKED_ARMATURE
+            bld.dof["damping"][d] = 0.0
+            bld.dof["frictionloss"][d] = 0.0
+            bld.dof["range"][d] = (-1.0, 1.0)  # the kernel wants every hand joint limited: a range it never reaches
+        for a_ in dead:
+            bld.act["kp"][a_] = 0.0
+            bld.act["forcerange"][a_] = (0.0, 0.0)
+        jacs_lock = []
+        for jp, jr in jacs:
+            jp, jr = jp.copy(), jr.copy()
+            jp[:, locked] = 0.0
+            jr[:, locked] = 0.0
+            jacs_lock.append((jp, jr))
+        dof_inv, body_inv = _invweights(bld, M_lock, jacs_lock)
+    else:
+        dof_inv, body_inv = _invweights(bld, M, jacs)
     pairs = _hand_pairs(infos, disable_hand_collisions)
 
     f64 = lambda x, shape=None: np.ascontiguousarray(np.asarray(x, np.float64).reshape(shape) if shape else np.asarray(x, np.float64))
@@ -379,7 +441,7 @@ def compile_scene(
     opt = dict(
         timestep=physics_timestep, gravity=(0.0, 0.0, -9.81),
         impratio=shm.OPTION_IMPRATIO if hands else 1.0, tolerance=1e-8, iterations=100,
-        ls_iterations=50, meaninertia=float(np.mean(np.diag(M))),
+        ls_iterations=50, meaninertia=mean_inertia,
         limit_solref=DEFAULT_SOLREF, limit_solimp=DEFAULT_SOLIMP,
         friction_solref=DEFAULT_SOLREF, friction_solimp=DEFAULT_SOLIMP,
         # equal priority, solmix 1/1 -> plain average; friction = max = 1; margin 0
@@ -391,6 +453,7 @@ def compile_scene(
                  site=bld.site["name"], actuator=bld.act["name"])
     model = CompiledModel(opt=opt, a=a, names=names, has_hands=hands, piano_actuators=piano_actuators)
     model.hand_info = infos
+    model.locked_dofs, model.dead_actuators = sorted(locked), sorted(dead)
     return model
 
 

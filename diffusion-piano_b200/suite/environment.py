@@ -36,8 +36,21 @@ class BatchedEnvironment:
         self.device = torch.device("cuda", device)
         self.layout = task.observation_layout()
         self.obs_dim, self.action_dim = self.engine.obs_dim, self.engine.action_dim
+        # reduced_action_space: the engine keeps its 45 actions / full observation row; the removed joints' columns
+        # are dropped (observations) and zero-filled (actions: their actuators are dead) at this boundary
+        red = task.reduced_spec() if hasattr(task, "reduced_spec") else None
+        self._reduced = red is not None
+        self._full_obs_dim, self._full_action_dim = self.obs_dim, self.action_dim
+        if self._reduced:
+            self._act_keep, self._obs_keep = np.asarray(red[0]), np.asarray(red[1])
+            self.obs_dim, self.action_dim = len(self._obs_keep), len(self._act_keep)
         n = self.num_envs
-        self._obs = torch.zeros((n, self.obs_dim), dtype=torch.float32, device=self.device)
+        self._obs = torch.zeros((n, self._full_obs_dim), dtype=torch.float32, device=self.device)
+        if self._reduced:
+            self._act_keep_t = torch.as_tensor(self._act_keep, device=self.device)
+            self._obs_keep_t = torch.as_tensor(self._obs_keep, device=self.device)
+            self._obs_red = torch.zeros((n, self.obs_dim), dtype=torch.float32, device=self.device)
+            self._act_full = torch.zeros((n, self._full_action_dim), dtype=torch.float32, device=self.device)
         self._reward = torch.zeros(n, dtype=torch.float32, device=self.device)
         self._terms = torch.zeros((n, 5), dtype=torch.float32, device=self.device)
         self._discount = torch.ones(n, dtype=torch.float32, device=self.device)
@@ -50,12 +63,12 @@ class BatchedEnvironment:
             return t.numpy()
 
         self._pinned = []
-        self._h_obs = pinned((n, self.obs_dim), torch.float32)
+        self._h_obs = pinned((n, self._full_obs_dim), torch.float32)
         self._h_reward = pinned((n,), torch.float32)
         self._h_terms = pinned((n, 5), torch.float32)
         self._h_discount = pinned((n,), torch.float32, 1)
         self._h_done = pinned((n,), torch.uint8)
-        self._h_actions = pinned((n, self.action_dim), torch.float32)
+        self._h_actions = pinned((n, self._full_action_dim), torch.float32)
         # randomize_hand_positions (piano_with_shadow_hands.py:491-499): a uniform(-0.05, 0.05) y shift of
         # both hands, drawn per env and per episode from the environment's RandomState
         self._randomize = bool(getattr(task, "_randomize_hand_positions", False))
@@ -84,8 +97,10 @@ class BatchedEnvironment:
     def action_spec(self) -> specs.BoundedArray:
         if self._canonical:
             return specs.BoundedArray((self.action_dim,), np.float64, -1.0, 1.0, name="action")
-        return specs.BoundedArray((self.action_dim,), np.float64, self.engine.action_minimum,
-                                  self.engine.action_maximum, name="action")
+        lo, hi = self.engine.action_minimum, self.engine.action_maximum
+        if self._reduced:
+            lo, hi = lo[self._act_keep], hi[self._act_keep]
+        return specs.BoundedArray((self.action_dim,), np.float64, lo, hi, name="action")
 
     def observation_spec(self) -> "OrderedDict[str, specs.Array]":
         return OrderedDict((k, specs.Array((size,), np.float64, name=k)) for k, (_, size) in self.layout.items())
@@ -95,18 +110,29 @@ class BatchedEnvironment:
         self._draw_hand_offsets()
         stream = self._torch.cuda.current_stream(self.device).cuda_stream
         self.engine.reset(obs=self._obs, mask=mask, stream=stream)
-        return self._obs
+        return self._device_obs()
+
+    def _device_obs(self):
+        if not self._reduced:
+            return self._obs
+        self._torch.index_select(self._obs, 1, self._obs_keep_t, out=self._obs_red)
+        return self._obs_red
 
     def step_device(self, actions):
         """actions: float32 CUDA tensor (N, action_dim). Returns (obs, reward, done, terms, discount)."""
         if self._auto_reset:
             self._draw_hand_offsets()
         stream = self._torch.cuda.current_stream(self.device).cuda_stream
+        if self._reduced:
+            self._act_full.index_copy_(1, self._act_keep_t, actions)
+            actions = self._act_full
         self.engine.step(actions, self._obs, self._reward, self._done, self._terms, self._discount, stream)
-        return self._obs, self._reward, self._done, self._terms, self._discount
+        return self._device_obs(), self._reward, self._done, self._terms, self._discount
 
     # ---- numpy API (host buffers; copies inside pp_step_host)
     def _split(self, flat: np.ndarray) -> Dict[str, np.ndarray]:
+        if self._reduced:
+            flat = flat[:, self._obs_keep]
         return OrderedDict((k, flat[:, o:o + s].astype(np.float64)) for k, (o, s) in self.layout.items())
 
     def reset(self) -> Dict[str, np.ndarray]:
@@ -153,7 +179,10 @@ class BatchedEnvironment:
         a = np.asarray(actions)
         if a.shape != (self.num_envs, self.action_dim):
             raise ValueError(f"actions must have shape {(self.num_envs, self.action_dim)}, got {a.shape}")
-        self._h_actions[...] = a  # float64 -> float32 into the page-locked buffer
+        if self._reduced:
+            self._h_actions[:, self._act_keep] = a
+        else:
+            self._h_actions[...] = a  # float64 -> float32 into the page-locked buffer
         if self._auto_reset:
             self._draw_hand_offsets()
         was_done = self._h_done.astype(bool) if getattr(self, "_midi_modules", None) else None

@@ -108,8 +108,9 @@ class PianoWithShadowHands(_PianoTaskBase):
         del disable_colorization, change_color_on_activation  # visual only
         # primitive_fingertip_collisions: the mesh colliders are unavailable, capsules are always used
         del primitive_fingertip_collisions
-        if reduced_action_space or attachment_yaw != 0 or tuple(forearm_dofs) != ("forearm_tx", "forearm_ty"):
-            raise NotImplementedError("only the default hand configuration is built (SURVEY §8f rank 4)")
+        if attachment_yaw != 0 or tuple(forearm_dofs) != ("forearm_tx", "forearm_ty"):
+            raise NotImplementedError("only the default attachment_yaw / forearm_dofs are built (SURVEY §8f rank 4)")
+        self._reduced_action_space = bool(reduced_action_space)
         self._randomize_hand_positions = bool(randomize_hand_positions)
         if n_seconds_lookahead is not None:
             n_steps_lookahead = int(np.ceil(n_seconds_lookahead / control_timestep))
@@ -122,7 +123,8 @@ class PianoWithShadowHands(_PianoTaskBase):
         self._energy_penalty_coef = energy_penalty_coef
         self.model = scene_compile.compile_scene(
             hands=True, gravity_compensation=gravity_compensation,
-            disable_hand_collisions=disable_hand_collisions, physics_timestep=physics_timestep)
+            disable_hand_collisions=disable_hand_collisions, physics_timestep=physics_timestep,
+            reduced_action_space=self._reduced_action_space)
         names = ["key_press_reward", "sustain_reward", "energy_reward"]
         names.append("ot_fingering_reward" if self._disable_fingering_reward else "fingering_reward")
         if not disable_forearm_reward:
@@ -138,7 +140,33 @@ class PianoWithShadowHands(_PianoTaskBase):
             wrong_press_termination=self._wrong_press_termination,
             energy_penalty_coef=self._energy_penalty_coef, device=device)
 
-    def observation_layout(self) -> "OrderedDict[str, Tuple[int, int]]":
+    def reduced_spec(self):
+        """reduced_action_space (shadow_hand.py:160-181): (kept action columns of the engine's 45, kept observation
+        columns of the engine's row, layout of the compacted row) - the removed joints' three actuators and three
+        joint positions per hand leave both specs. None for the full hand."""
+        if not self._reduced_action_space:
+            return None
+        full = self.observation_layout(full=True)
+        act_keep = [i for i in range(45) if i not in self.model.dead_actuators]
+        drop = set()
+        for h, key in enumerate(("rh_shadow_hand/joints_pos", "lh_shadow_hand/joints_pos")):
+            off, _ = full[key]
+            for d in self.model.locked_dofs:
+                lane = d - NUM_KEYS - 26 * h
+                if 0 <= lane < 26:
+                    drop.add(off + (lane - 2 if lane >= 2 else 24 + lane))  # hand.joints order: 24 joints, then forearm
+        width = max(o + n for o, n in full.values())
+        obs_keep = [c for c in range(width) if c not in drop]
+        new_of = {c: i for i, c in enumerate(obs_keep)}
+        layout = OrderedDict()
+        for k, (o, n) in full.items():
+            cols = [new_of[c] for c in range(o, o + n) if c in new_of]
+            layout[k] = (cols[0], len(cols))
+        return act_keep, obs_keep, layout
+
+    def observation_layout(self, full: bool = False) -> "OrderedDict[str, Tuple[int, int]]":
+        if self._reduced_action_space and not full:
+            return self.reduced_spec()[2]
         g = (self._n_steps_lookahead + 1) * (NUM_KEYS + 1)
         f = 0 if self._disable_fingering_reward else 10
         o = g + f
