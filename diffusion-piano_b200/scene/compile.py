@@ -348,7 +348,7 @@ def compile_scene(
     locked rows, as the reference's compiled model would have them. `model.locked_dofs` / `model.dead_actuators`
     list them for the façade, which drops them from the action and observation specs.
     reduced_by_removal=True builds the reference's own form instead (joints and actuators deleted, nv = 134): the
-    step kernel cannot run it, the oracle can - tests/test_scene_and_oracle.py compares the two."""
+    step kernel cannot run it, the CPU checker can: the tests compare the two forms."""
     bld = _Builder()
     _add_piano(bld, piano_actuators)
     infos = []
@@ -359,7 +359,7 @@ def compile_scene(
             infos.append(_add_hand(bld, side, position, qnorm(HAND_QUATERNION), gravity_compensation, tx_range,
                                    REDUCED_EXCLUDED_JOINTS if reduced_action_space and reduced_by_removal else ()))
     locked, dead = [], []
-    if hands and reduced_action_space and reduced_by_removal:  # the reference's own construction (oracle only)
+    if hands and reduced_action_space and reduced_by_removal:  # the reference's own construction (for the CPU checker)
         for info in infos:
             pre = "rh_" if info is infos[0] else "lh_"
             d2 = next(i for i, n in enumerate(bld.dof["name"]) if n.endswith("/" + pre + "THJ2"))
