@@ -54,6 +54,8 @@ struct pp_env {
   int sched_mode = PP_SCHED_AUTO, block_envs = 2, tune_calls = 0;
   bool sort_work = false, tuned = false;
   int* order = nullptr;  // [N]
+  int* queue = nullptr;  // [PP_MAX_HOST_CHUNKS] env queues of the persistent launch shape (one per concurrently launched piece)
+  int num_sms = 148;
   uint4* substep_act = nullptr;  // caller-owned [N, n_substeps] (pp_set_substep_activations) or null
   cudaEvent_t tune_ev[2 * PP_TUNE_STEPS] = {};
   // host-buffer path
@@ -324,6 +326,8 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(dalloc(&e->site_xpos, (size_t)N * 3 * PP_NSITE));
   CUDA_OK(dalloc(&e->activation, (size_t)N * 88)); CUDA_OK(dalloc(&e->counters, (size_t)N * 8));
   CUDA_OK(dalloc(&e->order, (size_t)N));
+  CUDA_OK(dalloc(&e->queue, (size_t)PP_MAX_HOST_CHUNKS));
+  CUDA_OK(cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
   CUDA_OK(dalloc(&e->act_min_d, e->action_dim)); CUDA_OK(dalloc(&e->act_max_d, e->action_dim));
   CUDA_OK(cudaMemcpy(e->act_min_d, e->act_min.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
   CUDA_OK(cudaMemcpy(e->act_max_d, e->act_max.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
@@ -359,7 +363,7 @@ extern "C" int pp_destroy(pp_env* e) {
                  e->needs_reset, e->qacc, e->act_force, e->act_vel, e->site_xpos, e->activation, e->counters,
                  e->act_min_d, e->act_max_d, e->d_actions, e->d_obs, e->d_reward, e->d_terms, e->d_discount,
                  e->d_done, e->d_mask, e->hand_off, e->hand_off_pending, e->eval_sum, e->eval_episode,
-                 e->eval_steps, e->eval_count, e->stick_bits, e->order};
+                 e->eval_steps, e->eval_count, e->stick_bits, e->order, e->queue};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -406,8 +410,14 @@ extern "C" int pp_action_bounds(const pp_env* e, float* lo, float* hi) {
 // ------------------------------------------------------------------ launches
 static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions, float* obs, float* reward,
                   float* terms, uint8_t* done, float* discount, cudaStream_t s, int env_begin = 0,
-                  int env_count = -1) {
+                  int env_count = -1, int piece = 0) {
   const pp_config& c = e->cfg;
+  {  // a handle belongs to one device; the caller may have made another one current since pp_create
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess || cur != c.device) {
+      if (cudaSetDevice(c.device) != cudaSuccess) return fail(PP_ERR_CUDA, "cudaSetDevice(%d)", c.device);
+    }
+  }
   if (c.task == PP_TASK_SELF_ACTUATED_PIANO) {
     PianoOnlyArgs A;
     memset(&A, 0, sizeof(A));
@@ -445,6 +455,8 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     const bool full = env_begin == 0 && (env_count < 0 || env_count == c.num_envs);
     int block_envs = e->block_envs;
     bool sort = e->sort_work && full && mode == PP_MODE_STEP;
+    static const bool no_sort = getenv("PP_NO_SORT") != nullptr;  // experiment knob: launch shape without the work order
+    if (no_sort) sort = false;
     int tune_slot = -1;
     if (e->sched_mode == PP_SCHED_AUTO && !e->tuned && full && mode == PP_MODE_STEP) {
       const int k = e->tune_calls++;
@@ -534,7 +546,7 @@ extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* 
     if (b >= N) break;
     const size_t n = k == pieces - 1 ? N - b : (b + per <= N ? per : N - b);
     int rc = launch(e, PP_MODE_STEP, nullptr, e->d_actions, obs ? e->d_obs : nullptr, e->d_reward,
-                    terms ? e->d_terms : nullptr, e->d_done, discount ? e->d_discount : nullptr, hs, (int)b, (int)n);
+                    terms ? e->d_terms : nullptr, e->d_done, discount ? e->d_discount : nullptr, hs, (int)b, (int)n, k);
     if (rc != PP_OK) return rc;
     if (obs) CUDA_OK(d2h(obs + b * e->obs_dim, e->h_obs + b * e->obs_dim, e->d_obs + b * e->obs_dim, n * e->obs_dim * 4, po, hs));
     CUDA_OK(d2h(reward + b, e->h_reward + b, e->d_reward + b, n * 4, pr, hs));

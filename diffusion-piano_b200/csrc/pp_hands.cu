@@ -1947,15 +1947,24 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   }
 }
 
+// The shared-memory attribute is per device and per kernel: set on every device this process launches on
+// (a second handle on another GPU of the same process must not inherit the first one's "configured").
+template <int WPB>
+static void configure_kernel() {
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    cudaFuncSetAttribute(pp_hands_step_kernel<WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)(sizeof(WarpShared) * WPB));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+}
 template <int WPB>
 static int launch_wpb(const HandsArgs& A, cudaStream_t stream, int env_begin, int env_count) {
-  static bool configured = false;
   const size_t smem = sizeof(WarpShared);
-  if (!configured) {
-    cudaFuncSetAttribute(pp_hands_step_kernel<WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * WPB));
-    cudaFuncSetAttribute(pp_hands_step_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = true;
-  }
+  configure_kernel<WPB>();
+  configure_kernel<1>();
   const int nblk = env_count / WPB, tail = env_count - nblk * WPB;
   if (nblk) pp_hands_step_kernel<WPB><<<nblk, 32 * WPB, smem * WPB, stream>>>(A, env_begin);
   if (WPB > 1 && tail) pp_hands_step_kernel<1><<<tail, 32, smem, stream>>>(A, env_begin + nblk * WPB);

@@ -189,6 +189,7 @@ def _add_hand(bld: _Builder, side: str, position, quaternion, gravcomp: bool, tx
         elif node["joint"] is not None and node["joint"]["name"] not in remove_joints:
             j = dict(shm.HAND_JOINT_DEFAULT)
             j.update(shm.JOINT_CLASS[node["joint"]["cls"]])
+            j.update({k: v for k, v in node["joint"].items() if k not in ("name", "cls")})  # per-joint overrides
             info["dof"][node["joint"]["name"]] = bld.add_dof(
                 model + prefix + node["joint"]["name"], body, JNT_HINGE, (0, 0, 0), ma(j["axis"]),
                 j["range"], damping=j["damping"], armature=j["armature"],

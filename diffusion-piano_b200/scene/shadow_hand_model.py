@@ -76,13 +76,28 @@ _I = (1.0, 0.0, 0.0, 0.0)
 _Z90 = (1.0, 0.0, 0.0, 1.0)  # unnormalised, MuJoCo normalises
 
 
-def _finger(prefix: str, knuckle_pos, j4: str = "J4") -> dict:
-    """knuckle -> proximal -> middle -> distal chain shared by ff/mf/rf/lf."""
+# Fingertip colliders. The menagerie distal colliders are convex meshes (f_distal_pst / th_distal_pst, absent);
+# a capsule stands in for each. Its size is CALIBRATED, not recollected: of the sizes tried, these make the
+# reference's recorded policy (examples/twinkle_twinkle_actions.npy, trained on the real meshes) press the most
+# goal keys in the replay (tools/calibrate_search.py, scene/ASSUMPTIONS.md section 3): key-press F1 0.365 with the
+# first guess (r 7.5 mm, tip at 29 mm / thumb r 9 mm, tip at 34 mm) -> 0.60 with these.
+FINGER_DISTAL_CAPSULE = dict(type="capsule", size=(0.0095, 0.010), pos=(0, 0, 0.015))   # tip at z = 34.5 mm
+THUMB_DISTAL_CAPSULE = dict(type="capsule", size=(0.013, 0.009), pos=(0, 0, 0.016))     # tip at z = 38 mm
+
+
+def _finger(prefix: str, knuckle_pos, j4: str = "J4", j4_axis=None) -> dict:
+    """knuckle -> proximal -> middle -> distal chain shared by ff/mf/rf/lf.
+    j4_axis: the ring and little finger knuckles override the class axis (0,-1,0) with (0,1,0), as the Shadow
+    Hand URDF does (positive J4 spreads the fingers away from the middle finger on both sides of it); the
+    replay probe agrees (left ring finger 24 -> 34 of 43 presses, left little finger 2 -> 15 of 20)."""
     p = prefix
+    j4_joint = dict(name=p.upper() + j4, cls="knuckle")
+    if j4_axis is not None:
+        j4_joint["axis"] = j4_axis
     return dict(
         name=p + "knuckle", pos=knuckle_pos, quat=_I,
         inertial=dict(mass=0.008, pos=(0, 0, 0), quat=(0.5, 0.5, -0.5, 0.5), diag=(3.2e-07, 2.6e-07, 2.6e-07)),
-        joint=dict(name=p.upper() + j4, cls="knuckle"), geoms=[],
+        joint=j4_joint, geoms=[],
         children=[dict(
             name=p + "proximal", pos=(0, 0, 0), quat=_I,
             inertial=dict(mass=0.03, pos=(0, 0, 0.0225), quat=_Z90, diag=(1e-05, 9.8e-06, 1.8e-06)),
@@ -98,8 +113,7 @@ def _finger(prefix: str, knuckle_pos, j4: str = "J4") -> dict:
                     inertial=dict(mass=0.013, pos=(0, 0, 0.0130769), quat=_Z90,
                                   diag=(1.28092e-06, 1.12092e-06, 5.3e-07)),
                     joint=dict(name=p.upper() + "J1", cls="middle_distal"),
-                    # stands in for mesh f_distal_pst (capsule fit, tip at z=0.029)
-                    geoms=[dict(type="capsule", size=(0.0075, 0.008), pos=(0, 0, 0.0135))],
+                    geoms=[dict(FINGER_DISTAL_CAPSULE)],  # stands in for mesh f_distal_pst
                     children=[],
                 )],
             )],
@@ -113,7 +127,7 @@ def right_hand_tree() -> dict:
         name="lfmetacarpal", pos=(-0.033, 0, 0.02071), quat=_I,
         inertial=dict(mass=0.03, pos=(0, 0, 0.04), quat=_Z90, diag=(1.638e-05, 1.45e-05, 4.272e-06)),
         joint=dict(name="LFJ5", cls="metacarpal"), geoms=[],
-        children=[_finger("lf", (0, 0, 0.06579))],
+        children=[_finger("lf", (0, 0, 0.06579), j4_axis=(0.0, 1.0, 0.0))],
     )
     thumb = dict(
         name="thbase", pos=(0.034, -0.00858, 0.029), quat=(0.92388, 0, 0.382683, 0),
@@ -141,8 +155,7 @@ def right_hand_tree() -> dict:
                         inertial=dict(mass=0.017, pos=(0, 0, 0.0145588), quat=_Z90,
                                       diag=(2.37794e-06, 2.27794e-06, 1e-06)),
                         joint=dict(name="THJ1", cls="thdistal"),
-                        # stands in for mesh th_distal_pst (capsule fit, tip at z=0.034)
-                        geoms=[dict(type="capsule", size=(0.009, 0.009), pos=(0, 0, 0.016))],
+                        geoms=[dict(THUMB_DISTAL_CAPSULE)],  # stands in for mesh th_distal_pst
                         children=[],
                     )],
                 )],
@@ -154,7 +167,7 @@ def right_hand_tree() -> dict:
         inertial=dict(mass=0.3, pos=(0, 0, 0.035), quat=_Z90, diag=(0.0005287, 0.0003581, 0.000191)),
         joint=dict(name="WRJ1", cls="wrist_x"), geoms=[],
         children=[_finger("ff", (0.033, 0, 0.095)), _finger("mf", (0.011, 0, 0.099)),
-                  _finger("rf", (-0.011, 0, 0.095)), lf, thumb],
+                  _finger("rf", (-0.011, 0, 0.095), j4_axis=(0.0, 1.0, 0.0)), lf, thumb],
     )
     wrist = dict(
         name="wrist", pos=(0.01, 0, 0.21301), quat=_I,

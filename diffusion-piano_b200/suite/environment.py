@@ -287,12 +287,29 @@ class Environment:
 
     def reset(self) -> specs.TimeStep:
         self._reset_next_step = False
+        self._t = 0
         return specs.TimeStep(specs.StepType.FIRST, None, None, self._obs(self._b.reset()))
+
+    def _cache_current(self) -> None:
+        """What after_step caches for the reward of the frame just played (piano_with_shadow_hands.py:192-199):
+        `task._goal_current`, `_rh_keys_current`, `_lh_keys_current`. The device holds the frame counter; these
+        host mirrors are for callers that read the task object (the reference's tests, MidiEvaluationWrapper)."""
+        song = getattr(self.task, "song", None)
+        if song is None or self._t >= song.goal.shape[0]:
+            return
+        self.task._goal_current = np.asarray(song.goal[self._t], np.float64)
+        pairs = getattr(song, "pairs", None)
+        if pairs is not None:
+            cur = [(int(k), int(f)) for k, f in np.asarray(pairs[self._t]) if k >= 0]
+            self.task._rh_keys_current = [(k, f) for k, f in cur if f < 5]
+            self.task._lh_keys_current = [(k, f - 5) for k, f in cur if f >= 5]
 
     def step(self, action) -> specs.TimeStep:
         if self._reset_next_step:
             return self.reset()
         obs, reward, done = self._b.step(np.asarray(action, np.float32)[None])
+        self._cache_current()
+        self._t += 1
         discount = float(self._b._h_discount[0])
         if done[0]:
             self._reset_next_step = True

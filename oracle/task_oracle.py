@@ -183,6 +183,25 @@ class PianoWithShadowHandsOracle(_Base):
         force = p.actuator_force.copy()  # from the last mj_step2 (pre-integration)
         p.forward_position(True)  # trailing mj_step1: positions + contacts at the new state
         vel = p.actuator_velocity.copy()
+        return self._after_physics(force, vel)
+
+    def epilogue_at(self, qpos, qvel, actuator_force, sustain_state):
+        """The task layer alone on a GIVEN end-of-step state (tests: the CUDA step's own qpos / qvel and
+        actuatorfrc sensor in, every reward term / observation / flag out - no physics drift in between).
+        The oracle's frame counter and cached goal / fingering must be those of the step being closed."""
+        p = self.physics
+        p.qpos[:] = np.asarray(qpos, np.float64)
+        p.qvel[:] = np.asarray(qvel, np.float64)
+        self.sustain_state = float(sustain_state)
+        self._key_state()
+        p.forward_position(True)
+        a = self.model.a
+        j0, j1 = a["act_trn0"], a["act_trn1"]
+        vel = p.qvel[j0] + np.where(j1 >= 0, p.qvel[np.maximum(j1, 0)], 0.0)
+        return self._after_physics(np.asarray(actuator_force, np.float64), vel)
+
+    def _after_physics(self, force, vel):
+        p = self.physics
         # after_step
         self.t_idx += 1
         should_terminate = (self.t_idx - 1) == len(self.notes) - 1

@@ -87,7 +87,7 @@ def test_config3_guren_random_actions_parity(cuda_lib):
         obs, rew, done, obs_o, r_o, d_o = s.step(a)
         assert bool(done[0]) == d_o
         for k, v in obs_o.items():
-            tol = 0 if k in ("goal", "fingering") else 2e-4  # 10 free-running fp32 substeps after a U(-1,1) jump
+            tol = 0 if k in ("goal", "fingering") else 1e-4  # 10 free-running fp32 substeps after a U(-1,1) jump (measured 2.2e-5)
             np.testing.assert_allclose(obs[k][0], v, atol=tol, err_msg=f"{k} step {t}")
             worst[k] = max(worst.get(k, 0.0), float(np.abs(obs[k][0] - v).max()))
         for name, val in s.ora.reward_terms.items():
@@ -98,8 +98,9 @@ def test_config3_guren_random_actions_parity(cuda_lib):
 
 
 def test_config5_stress_parity(cuda_lib):
-    """config 5: all 88 keys requested, hands raking the keyboard. Steps in which the CUDA step had to drop
-    contacts (more than its caps) are excluded from the comparison and counted."""
+    """config 5: all 88 keys requested, hands raking the keyboard. Every step is compared: the sequence must
+    stay inside the kernel's contact caps (24 contacts, 16 touched keys per env) - a step that drops a contact
+    fails the test instead of being skipped."""
     task = _stress_task()
     s = _SyncedCanonical(task)
     assert s.env.obs_dim == 1130
@@ -110,9 +111,7 @@ def test_config5_stress_parity(cuda_lib):
         a = _rake_actions(rng, 1, t, names)[0]
         obs, rew, done, obs_o, r_o, d_o = s.step(a)
         max_con = max(max_con, int(s.cnt[0, 0])); dense += int(s.cnt[0, 6])
-        if int(s.cnt[0, 3]) > 0:
-            dropped += 1
-            continue
+        dropped += int(s.cnt[0, 3]) > 0
         compared += 1
         for k, v in obs_o.items():
             tol = 0 if k in ("goal", "fingering") else 5e-4
@@ -120,7 +119,7 @@ def test_config5_stress_parity(cuda_lib):
         np.testing.assert_allclose(rew[0], r_o, atol=5e-3, err_msg=f"reward step {t}")
     print(f"config 5: compared {compared} steps, {dropped} with dropped contacts, max contacts {max_con}, "
           f"dense-fallback substeps {dense}")
-    assert compared >= 8
+    assert compared == 16 and dropped == 0
     s.env.close()
 
 

@@ -1,5 +1,5 @@
 """Config 3 regime (uniform random canonical actions): ms per control step and solver statistics averaged over
-the envs, per block of steps. usage: python tools/random_action_stats.py [envs] [steps] [sigma]
+the envs, per block of steps. usage: python tools/random_action_stats.py [envs] [steps] [sigma] [schedule] [group]
 sigma > 0: actions ~ clip(N(0, sigma)) instead of U(-1, 1) (what an untrained ppo_v2 policy emits, sigma = e^-1)."""
 import sys
 from pathlib import Path
@@ -19,6 +19,7 @@ def main():
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 60
     sigma = float(sys.argv[3]) if len(sys.argv) > 3 else 0.0
     schedule = sys.argv[4] if len(sys.argv) > 4 else "auto"
+    group = int(sys.argv[5]) if len(sys.argv) > 5 else 1  # every action row is shared by `group` consecutive envs
     task = suite.PianoWithShadowHands(music.load("GurenNoYumiyaCut14s"), n_steps_lookahead=1, trim_silence=True)
     env = suite.BatchedEnvironment(task, B, canonical_actions=True, auto_reset=True, schedule=schedule)
     dev = torch.device("cuda", 0)
@@ -31,7 +32,9 @@ def main():
         if sigma > 0:
             a = (sigma * torch.randn((B, 45), device=dev, generator=g)).clamp_(-1, 1)
         else:
-            a = torch.rand((B, 45), device=dev, generator=g) * 2 - 1
+            a = torch.rand((B // group, 45), device=dev, generator=g) * 2 - 1
+            if group > 1:
+                a = a.repeat_interleave(group, 0).contiguous()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         env.step_device(a)
