@@ -10,10 +10,13 @@ replaying reference examples/twinkle_twinkle_actions.npy row t at step t, 4096 e
 A "step" is one control step of every env of the batch (one kernel launch per GPU).
 
 One JSON line is printed by rank 0. `value` = env-steps/s over all ranks with actions already
-in HBM (device timing, CUDA events on the launching stream, max over ranks); `e2e` = the same
-step through pp_step_host with HOST buffers (H2D of actions, D2H of obs/reward/done inside the
-timed region). MuJoCo itself is absent from this box ("unavailable on this box"), so the CPU
-arm is the fp64 restatement in oracle/ (kind "port"), OpenMP over envs.
+in HBM (device timing, CUDA events on the launching stream, max over ranks); `e2e` = the SAME
+control steps of the episode through pp_step_host with HOST buffers (H2D of actions, D2H of
+obs/reward/done inside the timed region). MuJoCo itself is absent from this box ("unavailable on
+this box"), so the CPU arm is the fp64 restatement in oracle/ (kind "port"), OpenMP over envs.
+`extra` carries the other BASELINE configs, each timed with its own CUDA events after the headline
+(--extras 3,5,4; "" to skip): config3 (random actions, B = 16384), config5 (contact stress,
+B = 65536), config4_ppo (rollout + PPO v2 update with the gradient all-reduce across ranks).
 """
 import argparse
 import ctypes
@@ -251,20 +254,22 @@ def run_product(args) -> None:
         keep.append(t)
         return t.numpy()
 
+    # the same control steps of the episode as the device-timed region: reset, Wm untimed host steps, K timed
     h_act = []
-    for i in range(K):
+    for i in range(Wm + K):
         buf = pinned((B, 45), torch.float32)
-        buf[...] = table[(Wm + K + i) % period]
+        buf[...] = table[i % period]
         h_act.append(buf)
     h_obs = pinned((B, env.obs_dim), torch.float32)
     h_rew = pinned((B,), torch.float32); h_done = pinned((B,), torch.uint8)
     h_terms = pinned((B, 5), torch.float32); h_disc = pinned((B,), torch.float32)
-    for i in range(2):
+    env.reset_device()
+    for i in range(Wm):
         env.engine.step_host(h_act[i], h_obs, h_rew, h_done, h_terms, h_disc)
     barrier()
     t0 = time.perf_counter()
     for i in range(K):
-        env.engine.step_host(h_act[i], h_obs, h_rew, h_done, h_terms, h_disc)
+        env.engine.step_host(h_act[Wm + i], h_obs, h_rew, h_done, h_terms, h_disc)
     barrier()
     e2e_s = time.perf_counter() - t0
     h2d = B * 45 * 4
@@ -278,11 +283,14 @@ def run_product(args) -> None:
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
         bpe = bytes_per_env_step(env.obs_dim)
-        traffic = None  # dram read + write of one launch from the committed ncu --set full capture
-        tpath = ROOT / "profiles" / "r01_traffic.json"
+        # from the committed `ncu --set full` capture of this kernel on this workload (profiles/): DRAM bytes of one
+        # launch, and the figures that say more than the HBM fraction about a latency-bound kernel
+        traffic, util = None, {}
+        tpath = ROOT / "profiles" / "ncu_bench_kernel.json"
         if tpath.exists() and B == 4096:
             tj = json.loads(tpath.read_text())
             traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / 1e9  # GB per launch, like achieved * kernel_s
+            util = {k: tj[k] for k in ("issue_slot_busy", "lanes_active", "achieved_occupancy", "capture") if k in tj}
         kern_ms = dev_ms / K  # one kernel launch per step: the step IS the dominant kernel
         achieved = bpe * B / (kern_ms * 1e-3) / 1e9
         line = {"metric": METRIC, "value": sharding.whole_job_throughput(shard, K, dev_ms), "unit": UNIT, "n_gpus": world,
@@ -296,7 +304,7 @@ def run_product(args) -> None:
                              "frac": achieved / peak, "traffic": traffic, "traffic_unit": "GB per launch (ncu)",
                              "algorithmic_gb_per_launch": bpe * B / 1e9, "peak_source": peak_src,
                              "bytes_per_env_step": bpe, "kernel": "pp_hands_step_kernel",
-                             "kernel_ms": kern_ms},
+                             "kernel_ms": kern_ms, **util},
                 "wall_ms_per_step_incl_flush": 1e3 * t_wall / K, "mean_reward_last_step": rew_mean, "solver": solver}
         if world == 1 and not args.no_cpu:
             cores = os.cpu_count() or 1
@@ -305,9 +313,36 @@ def run_product(args) -> None:
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"{n_envs} envs x {steps} control steps of the same workload, fp64 oracle "
                                               f"port (physics restatement), OpenMP over envs; MuJoCo unavailable on this box"}
-        print(json.dumps(line), flush=True)
     env.close()
+    del env, acts, flush
+    torch.cuda.empty_cache()
+    # ---- the other BASELINE configs, device-resident, each with its own CUDA-event timing (all ranks take part)
+    extra, agent = {}, None
+    sys.path.insert(0, str(ROOT / "tools"))
+    wanted = [c for c in args.extras.split(",") if c]
+    if "3" in wanted:
+        import bench_configs
+        extra["config3"] = bench_configs.measure(3, args.envs3, args.extra_steps, 20, local, world, rank)
+    if "5" in wanted:
+        import bench_configs
+        extra["config5"] = bench_configs.measure(5, args.envs5, args.extra_steps, 20, local, world, rank)
+    if "4" in wanted:
+        import bench_ppo
+        pg = dist.group.WORLD if world > 1 else None
+        extra["config4_ppo"], agent = bench_ppo.measure(args.envs, args.extra_steps, 18, local, world, rank, pg)
+    if rank == 0:
+        if extra:
+            line["extra"] = extra
+        print(json.dumps(line), flush=True)
     if world > 1:
+        if agent is not None:
+            # destroy_process_group() blocks after CUDA graphs that captured NCCL kernels were replayed on its
+            # communicators: release the graphs, meet at a barrier and leave without it
+            agent.close()
+            dist.barrier()
+            torch.cuda.synchronize()
+            sys.stdout.flush()
+            os._exit(0)
         dist.destroy_process_group()
 
 
@@ -320,6 +355,10 @@ def main():
     ap.add_argument("--envs", type=int, default=4096, help="envs per GPU")
     ap.add_argument("--cpu-steps", type=int, default=8, help="control steps of the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--extras", default="3,5,4", help="other BASELINE configs timed after the headline ('' = none)")
+    ap.add_argument("--extra-steps", type=int, default=10, help="timed control steps of each extra config")
+    ap.add_argument("--envs3", type=int, default=16384, help="envs per GPU of config 3")
+    ap.add_argument("--envs5", type=int, default=65536, help="envs per GPU of config 5")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -44,6 +44,7 @@ _SIGNATURES = {
     "pp_step": (c_int, [c_void_p] * 8),
     "pp_step_host": (c_int, [c_void_p] * 7),
     "pp_reset_host": (c_int, [c_void_p] * 3),
+    "pp_host_timeline": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
     "pp_get_state": (c_int, [c_void_p] * 7),
     "pp_set_state": (c_int, [c_void_p] * 7),
     "pp_set_qfrc_applied": (c_int, [c_void_p] * 3),

@@ -64,6 +64,10 @@ struct pp_env {
   cudaStream_t hstream = nullptr, hstream_more[PP_MAX_HOST_CHUNKS - 1] = {};
   int host_chunks = 6;  // e2e of config 2 (B = 4096, 40 steps): 2 pieces 1.224 M, 3: 1.243 M, 4: 1.244 M, 6: 1.256 M, 8: 1.254 M env-steps/s
   cudaEvent_t h_ready = nullptr;
+  // pp_host_timeline: CUDA events of the last pp_step_host (start, actions on the device, per piece: step done, results on the host)
+  bool timeline = false;
+  int tl_pieces = 0;
+  cudaEvent_t tl_start = nullptr, tl_h2d = nullptr, tl_step[PP_MAX_HOST_CHUNKS] = {}, tl_copy[PP_MAX_HOST_CHUNKS] = {};
   float *h_actions = nullptr, *h_obs = nullptr, *h_reward = nullptr, *h_terms = nullptr, *h_discount = nullptr;
   uint8_t* h_done = nullptr;
   float *d_actions = nullptr, *d_obs = nullptr, *d_reward = nullptr, *d_terms = nullptr, *d_discount = nullptr;
@@ -370,6 +374,9 @@ extern "C" int pp_destroy(pp_env* e) {
   if (e->hstream) cudaStreamDestroy(e->hstream);
   for (auto hs : e->hstream_more) if (hs) cudaStreamDestroy(hs);
   if (e->h_ready) cudaEventDestroy(e->h_ready);
+  if (e->tl_start) { cudaEventDestroy(e->tl_start); cudaEventDestroy(e->tl_h2d); }
+  for (auto ev : e->tl_step) if (ev) cudaEventDestroy(ev);
+  for (auto ev : e->tl_copy) if (ev) cudaEventDestroy(ev);
   for (auto ev : e->tune_ev) if (ev) cudaEventDestroy(ev);
   delete e;
   return PP_OK;
@@ -530,7 +537,9 @@ extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* 
   const bool pa = is_pinned(actions), po = is_pinned(obs), pr = is_pinned(reward), pt = is_pinned(terms),
              pd = is_pinned(done), pc = is_pinned(discount);
   if (!pa) memcpy(e->h_actions, actions, N * e->action_dim * 4);
+  if (e->timeline) CUDA_OK(cudaEventRecord(e->tl_start, s));
   CUDA_OK(cudaMemcpyAsync(e->d_actions, pa ? actions : e->h_actions, N * e->action_dim * 4, cudaMemcpyHostToDevice, s));
+  if (e->timeline) CUDA_OK(cudaEventRecord(e->tl_h2d, s));
   // pieces on their own streams (hands task, large batches): a piece's results travel to the host while the later
   // pieces are still stepping. All grids are resident together, so the device does the same work.
   const bool split = e->cfg.task == PP_TASK_PIANO_WITH_SHADOW_HANDS && N >= 1024 && e->host_chunks > 1;
@@ -548,11 +557,13 @@ extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* 
     int rc = launch(e, PP_MODE_STEP, nullptr, e->d_actions, obs ? e->d_obs : nullptr, e->d_reward,
                     terms ? e->d_terms : nullptr, e->d_done, discount ? e->d_discount : nullptr, hs, (int)b, (int)n, k);
     if (rc != PP_OK) return rc;
+    if (e->timeline) { CUDA_OK(cudaEventRecord(e->tl_step[k], hs)); e->tl_pieces = k + 1; }
     if (obs) CUDA_OK(d2h(obs + b * e->obs_dim, e->h_obs + b * e->obs_dim, e->d_obs + b * e->obs_dim, n * e->obs_dim * 4, po, hs));
     CUDA_OK(d2h(reward + b, e->h_reward + b, e->d_reward + b, n * 4, pr, hs));
     if (terms) CUDA_OK(d2h(terms + b * 5, e->h_terms + b * 5, e->d_terms + b * 5, n * 5 * 4, pt, hs));
     if (discount) CUDA_OK(d2h(discount + b, e->h_discount + b, e->d_discount + b, n * 4, pc, hs));
     CUDA_OK(d2h(done + b, e->h_done + b, e->d_done + b, n, pd, hs));
+    if (e->timeline) CUDA_OK(cudaEventRecord(e->tl_copy[k], hs));
   }
   for (int k = 1; k < pieces; k++) CUDA_OK(cudaStreamSynchronize(e->hstream_more[k - 1]));
   CUDA_OK(cudaStreamSynchronize(s));
@@ -561,6 +572,29 @@ extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* 
   if (terms && !pt) memcpy(terms, e->h_terms, N * 5 * 4);
   if (discount && !pc) memcpy(discount, e->h_discount, N * 4);
   if (!pd) memcpy(done, e->h_done, N);
+  return PP_OK;
+}
+
+// Diagnostic: where the time of a host-buffer step goes. enable != 0 arms the recording for the following
+// pp_step_host calls; with ms_out != NULL the times of the LAST call are returned in milliseconds from its start:
+// ms_out[0] = actions on the device, then per piece (step kernel done, results on the host). Returns the number
+// of pieces through *n_pieces. ms_out holds 1 + 2 * 8 floats.
+extern "C" int pp_host_timeline(pp_env* e, int enable, float* ms_out, int* n_pieces) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  if (enable && !e->tl_start) {
+    CUDA_OK(cudaEventCreate(&e->tl_start)); CUDA_OK(cudaEventCreate(&e->tl_h2d));
+    for (auto& ev : e->tl_step) CUDA_OK(cudaEventCreate(&ev));
+    for (auto& ev : e->tl_copy) CUDA_OK(cudaEventCreate(&ev));
+  }
+  if (ms_out && e->tl_pieces > 0) {
+    CUDA_OK(cudaEventElapsedTime(&ms_out[0], e->tl_start, e->tl_h2d));
+    for (int k = 0; k < e->tl_pieces; k++) {
+      CUDA_OK(cudaEventElapsedTime(&ms_out[1 + 2 * k], e->tl_start, e->tl_step[k]));
+      CUDA_OK(cudaEventElapsedTime(&ms_out[2 + 2 * k], e->tl_start, e->tl_copy[k]));
+    }
+  }
+  if (n_pieces) *n_pieces = e->tl_pieces;
+  e->timeline = enable != 0;
   return PP_OK;
 }
 

@@ -102,6 +102,14 @@ class BatchedPianoEngine:
         _lib.check(self.lib.pp_step_host(self._h, _ptr(actions), _ptr(obs), _ptr(reward),
                                          _ptr(reward_terms), _ptr(done), _ptr(discount)))
 
+    def host_timeline(self, enable: bool = True):
+        """CUDA-event times [ms from the call's start] of the last step_host: (actions on the device,
+        [(step done, results on the host) per piece]); arms / disarms the recording for later calls."""
+        ms = (ctypes.c_float * 17)()
+        n = ctypes.c_int(0)
+        _lib.check(self.lib.pp_host_timeline(self._h, int(enable), ctypes.addressof(ms), ctypes.addressof(n)))
+        return float(ms[0]), [(float(ms[1 + 2 * k]), float(ms[2 + 2 * k])) for k in range(n.value)]
+
     # ---- state / diagnostics (torch CUDA tensors)
     def get_state(self, qpos=None, qvel=None, warm=None, t_idx=None, sustain=None, stream: int = 0):
         _lib.check(self.lib.pp_get_state(self._h, _ptr(qpos), _ptr(qvel), _ptr(warm), _ptr(t_idx),

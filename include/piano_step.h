@@ -91,6 +91,11 @@ int pp_step(pp_env *env, const float *actions_dev, float *obs_dev, float *reward
 int pp_step_host(pp_env *env, const float *actions, float *obs, float *reward,
                  float *reward_terms, uint8_t *done, float *discount);
 int pp_reset_host(pp_env *env, const uint8_t *mask, float *obs);
+/* Diagnostic (no reference counterpart): CUDA-event timeline of a host-buffer step. enable != 0 arms the
+ * recording for the following pp_step_host calls; ms_out (1 + 2 * 8 floats, may be NULL) receives the times of
+ * the LAST call in ms from its start: [0] actions on the device, then per piece [step done, results on the
+ * host]; *n_pieces = pieces the batch was stepped in. */
+int pp_host_timeline(pp_env *env, int enable, float *ms_out, int *n_pieces);
 
 /* state: qpos/qvel/qacc_warmstart [N,nv] f32, t_idx [N] i32, sustain [N] f32 (device);
  * any pointer may be NULL */

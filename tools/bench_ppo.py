@@ -12,6 +12,71 @@ ROOT = Path(__file__).resolve().parents[1]
 sys.path.insert(0, str(ROOT))
 
 
+def measure(envs, steps, warmup, local, world, rank, pg, epochs=10, batch_size=128, impl="product", eager=False,
+            graph_scope="update", schedule="auto", gemm="custom", fuse_ln=False, cluster_ln=False):
+    """select_actions -> env step -> PPO update, `steps` control steps after `warmup`; returns (JSON-able dict, agent)."""
+    import torch
+
+    from diffusion_piano_b200 import music, suite
+    from diffusion_piano_b200.ppo import PPOAgent
+
+    task = suite.PianoWithShadowHands(music.load("CrossingFieldCut10s"), n_steps_lookahead=1, trim_silence=True)
+    env = suite.BatchedEnvironment(task, envs, device=local, canonical_actions=True, auto_reset=True, schedule=schedule)
+    if impl == "product":
+        agent = PPOAgent(env.obs_dim, env.action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch_size,
+                         ppo_epochs=epochs, device=f"cuda:{local}", seed=0, process_group=pg,
+                         use_graphs=not eager, graph_scope=graph_scope, gemm=gemm, fuse_ln=fuse_ln, cluster_ln=cluster_ln)
+    else:
+        sys.path.insert(0, str(ROOT / "tools"))
+        from torch_ppo_baseline import TorchPPO
+
+        torch.manual_seed(0)
+        agent = TorchPPO(env.obs_dim, env.action_dim, batch_size=batch_size, ppo_epochs=epochs,
+                         device=f"cuda:{local}", python_gae=impl == "torch")
+        agent.kernel_launches = 0
+        agent.stats = lambda: {}
+    n = envs
+    states = torch.empty((n, env.obs_dim), dtype=torch.float32, device=env.device)
+    obs = env.reset_device()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(steps)]
+    launches0 = 0
+    for it in range(warmup + steps):
+        if it == warmup:
+            if pg is not None:
+                torch.distributed.barrier()
+            torch.cuda.synchronize()
+            launches0 = agent.kernel_launches + env.engine.launch_count
+        e = ev[it - warmup] if it >= warmup else None
+        states.copy_(obs)
+        if e: e[0].record()
+        actions, logp = agent.select_actions(states)
+        if e: e[1].record()
+        obs, rewards, dones, _, _ = env.step_device(actions)
+        if e: e[2].record()
+        agent.update(states, actions, rewards, logp, obs, dones)
+        if e: e[3].record()
+    torch.cuda.synchronize()
+    launches = agent.kernel_launches + env.engine.launch_count - launches0
+    act = sum(a[0].elapsed_time(a[1]) for a in ev) / steps
+    step = sum(a[1].elapsed_time(a[2]) for a in ev) / steps
+    upd = sum(a[2].elapsed_time(a[3]) for a in ev) / steps
+    total = torch.tensor([ev[0][0].elapsed_time(ev[-1][3])], device=env.device)
+    if pg is not None:
+        torch.distributed.all_reduce(total, op=torch.distributed.ReduceOp.MAX)
+    total_ms = float(total.item())
+    mbs = epochs * ((n + batch_size - 1) // batch_size)
+    line = {
+        "metric": "PPO v2 rollout+update env steps/sec (config 4)", "value": n * world * steps / (total_ms * 1e-3),
+        "unit": "env-steps/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": total_ms / steps, "phases_ms": {"select_actions": act, "env_step": step, "update": upd},
+        "minibatches_per_update": mbs, "us_per_minibatch": 1e3 * upd / mbs, "gpu_launches": launches,
+        "impl": impl, "graphs": not eager, "schedule": env.engine.get_schedule(), "stats": agent.stats(),
+        "config": {"workload": "PianoWithShadowHands 'Crossing Field Cut 10s', ppo_v2 update every control step",
+                   "envs_per_gpu": n, "batch_size": batch_size, "ppo_epochs": epochs,
+                   "obs_dim": env.obs_dim, "parallelism": f"env-sharded x{world}, gradient all-reduce per minibatch"}}
+    return line, agent
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--envs", type=int, default=4096)
@@ -45,65 +110,11 @@ def main():
     if world > 1:
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
         pg = torch.distributed.group.WORLD
-    from diffusion_piano_b200 import music, suite
-    from diffusion_piano_b200.ppo import PPOAgent
-
-    task = suite.PianoWithShadowHands(music.load("CrossingFieldCut10s"), n_steps_lookahead=1, trim_silence=True)
-    env = suite.BatchedEnvironment(task, args.envs, device=local, canonical_actions=True, auto_reset=True,
-                                   schedule=args.schedule)
-    if args.impl == "product":
-        agent = PPOAgent(env.obs_dim, env.action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=args.batch_size,
-                         ppo_epochs=args.epochs, device=f"cuda:{local}", seed=0, process_group=pg,
-                         use_graphs=not args.eager, graph_scope=args.graph_scope, gemm=args.gemm, fuse_ln=args.fuse_ln, cluster_ln=args.cluster_ln)
-    else:
-        sys.path.insert(0, str(ROOT / "tools"))
-        from torch_ppo_baseline import TorchPPO
-
-        torch.manual_seed(0)
-        agent = TorchPPO(env.obs_dim, env.action_dim, batch_size=args.batch_size, ppo_epochs=args.epochs,
-                         device=f"cuda:{local}", python_gae=args.impl == "torch")
-        agent.kernel_launches = 0
-        agent.stats = lambda: {}
-    n = args.envs
-    states = torch.empty((n, env.obs_dim), dtype=torch.float32, device=env.device)
-    obs = env.reset_device()
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
-    launches0 = 0
-    for it in range(args.warmup + args.steps):
-        if it == args.warmup:
-            if pg is not None:
-                torch.distributed.barrier()
-            torch.cuda.synchronize()
-            launches0 = agent.kernel_launches + env.engine.launch_count
-        e = ev[it - args.warmup] if it >= args.warmup else None
-        states.copy_(obs)
-        if e: e[0].record()
-        actions, logp = agent.select_actions(states)
-        if e: e[1].record()
-        obs, rewards, dones, _, _ = env.step_device(actions)
-        if e: e[2].record()
-        agent.update(states, actions, rewards, logp, obs, dones)
-        if e: e[3].record()
-    torch.cuda.synchronize()
-    launches = agent.kernel_launches + env.engine.launch_count - launches0
-    act = sum(a[0].elapsed_time(a[1]) for a in ev) / args.steps
-    step = sum(a[1].elapsed_time(a[2]) for a in ev) / args.steps
-    upd = sum(a[2].elapsed_time(a[3]) for a in ev) / args.steps
-    total = torch.tensor([ev[0][0].elapsed_time(ev[-1][3])], device=env.device)
-    if pg is not None:
-        torch.distributed.all_reduce(total, op=torch.distributed.ReduceOp.MAX)
-    total_ms = float(total.item())
-    mbs = args.epochs * ((n + args.batch_size - 1) // args.batch_size)
+    line, agent = measure(args.envs, args.steps, args.warmup, local, world, rank, pg, epochs=args.epochs,
+                          batch_size=args.batch_size, impl=args.impl, eager=args.eager, graph_scope=args.graph_scope,
+                          schedule=args.schedule, gemm=args.gemm, fuse_ln=args.fuse_ln, cluster_ln=args.cluster_ln)
     if rank == 0:
-        print(json.dumps({
-            "metric": "PPO v2 rollout+update env steps/sec (config 4)", "value": n * world * args.steps / (total_ms * 1e-3),
-            "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_ms / args.steps, "phases_ms": {"select_actions": act, "env_step": step, "update": upd},
-            "minibatches_per_update": mbs, "us_per_minibatch": 1e3 * upd / mbs, "gpu_launches": launches,
-            "impl": args.impl, "graphs": not args.eager, "schedule": env.engine.get_schedule(), "stats": agent.stats(),
-            "config": {"workload": "PianoWithShadowHands 'Crossing Field Cut 10s', ppo_v2 update every control step",
-                       "envs_per_gpu": n, "batch_size": args.batch_size, "ppo_epochs": args.epochs,
-                       "obs_dim": env.obs_dim, "parallelism": f"env-sharded x{world}, gradient all-reduce per minibatch"}}))
+        print(json.dumps(line))
     if pg is not None:
         # destroy_process_group() blocks when CUDA graphs that captured NCCL kernels were replayed on its
         # communicators (seen on 2 x B200): release the graphs, meet at a barrier and leave without it
