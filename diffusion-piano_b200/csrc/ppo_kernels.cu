@@ -1560,3 +1560,48 @@ int ppo_plateau_step(ppo_ctrl* ctrl, float factor, int patience, void* stream) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------- ppo_grad_sumsq without caller scratch
+// No counterpart in the reference: added for callers that cannot allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). The scratch of grad_sumsq_kernel
+// (592 block partial sums + the ticket word) lives in this file-scope device array instead of caller buffers:
+// 640 words = 2560 bytes on every GPU that loads the library, until the process exits.
+// In HOST code the name g_sumsq_static is only a stand-in for the symbol, not a device address: the address is
+// resolved once per device, with that device current, by cudaGetSymbolAddress below and that pointer goes to the
+// kernel. Every call on a device shares the array: two calls that overlap on the GPU (different streams) race.
+constexpr int kStaticPartials = 592;  // the grid cap of ppo_grad_sumsq
+constexpr int kStaticWords = 640;     // partial sums [0, 592), ticket at word 592, padding
+static __device__ __align__(256) float g_sumsq_static[kStaticWords];
+
+extern "C" int ppo_grad_sumsq_static(const float* grad, int n, ppo_ctrl* ctrl, int which, void* stream) {
+  static float* base[64] = {};  // device address of g_sumsq_static, per device ordinal
+  if (grad == nullptr || ctrl == nullptr) return invalid("grad / ctrl");
+  if (n <= 0 || (which != 0 && which != 1)) return invalid("n / which");
+  if (n > PPO_GRAD_SUMSQ_STATIC_MAX_N) {
+    snprintf(g_err, sizeof(g_err), "ppo_grad_sumsq_static: n = %d exceeds PPO_GRAD_SUMSQ_STATIC_MAX_N = %d "
+             "(use ppo_grad_sumsq with caller scratch)", n, PPO_GRAD_SUMSQ_STATIC_MAX_N);
+    return -1;
+  }
+  if ((reinterpret_cast<uintptr_t>(grad) & 15) != 0) return invalid("grad must be 16-byte aligned");
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail("ppo_grad_sumsq_static: cudaGetDevice", e);
+  if (dev < 0 || dev >= 64) return invalid("device ordinal beyond 63");
+  if (base[dev] == nullptr) {  // set-up, once per device, with that device current
+    float* ptr = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_sumsq_static);
+    if (e != cudaSuccess || ptr == nullptr) return fail("ppo_grad_sumsq_static: cudaGetSymbolAddress", e);
+    base[dev] = ptr;
+  }
+  float* scratch = base[dev];
+  uint32_t* ticket = reinterpret_cast<uint32_t*>(base[dev] + kStaticPartials);
+  // the array keeps the last call's contents: the ticket must start at zero (an aborted call may have left it
+  // counting); the partial sums are overwritten before they are read
+  e = cudaMemsetAsync(ticket, 0, sizeof(uint32_t), (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail("ppo_grad_sumsq_static: cudaMemsetAsync", e);
+  int blocks = (n / 4 + 2 * 256 - 1) / (2 * 256);  // the launch shape of ppo_grad_sumsq: same partials, same order
+  if (blocks > kStaticPartials) blocks = kStaticPartials;
+  if (blocks < 1) blocks = 1;
+  launch_k(grad_sumsq_kernel, dim3(blocks), dim3(256), (cudaStream_t)stream, false, grad, n, scratch, ticket, ctrl, which);
+  PPO_LAUNCH_CHECK("ppo_grad_sumsq_static");
+}

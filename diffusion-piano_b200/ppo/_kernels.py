@@ -50,6 +50,7 @@ _SIGNATURES = {
     "ppo_gather_minibatch": (I, [P, P, P, P, P, P, I, P, U32, I, I, I, I, P, P, P, P, P, P]),
     "ppo_permutation": (I, [P, U32, I, P, P]),
     "ppo_grad_sumsq": (I, [P, I, P, P, P, I, P]),
+    "ppo_grad_sumsq_static": (I, [P, I, P, I, P]),
     "ppo_allreduce_sumsq": (I, [P, P, P, I, I, I, P, P, P, P, P, I, P]),
     "ppo_allreduce_flag_words": (I, []),
     "ppo_clip_adam": (I, [P, P, P, P, I, P, I, F, F, F, F, F, P]),

@@ -173,6 +173,18 @@ int ppo_permutation(const ppo_ctrl* ctrl_dev, uint32_t perm_salt, int N, int32_t
  * grad 16-byte aligned; scratch >= 592 floats, ticket as above. */
 int ppo_grad_sumsq(const float* grad, int n, float* scratch, uint32_t* ticket, ppo_ctrl* ctrl_dev, int which,
                    void* stream);
+/* ppo_grad_sumsq for callers that cannot allocate device memory (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+ * Same kernel, same launch shape, same result (bit for bit) as ppo_grad_sumsq; the scratch (592 block
+ * partial sums + the ticket word) is a file-scope device array inside the library - 2560 bytes on every GPU that
+ * loads it, until the process exits - so the call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine). Limit: n <= PPO_GRAD_SUMSQ_STATIC_MAX_N, larger n is rejected (-1, ppo_last_error() names the
+ * limit). The array is shared by every call on that GPU and keeps the last call's contents (the call clears the
+ * ticket on `stream` first): calls that overlap on the GPU - different streams, or graphs replayed concurrently -
+ * RACE; serialise them. The first call on a device resolves the array's address (cudaGetSymbolAddress): make it
+ * before any stream capture. */
+#define PPO_GRAD_SUMSQ_STATIC_MAX_N (1 << 22) /* floats: 16 MiB of gradient, 10x both PPO networks together */
+int ppo_grad_sumsq_static(const float* grad, int n, ppo_ctrl* ctrl_dev, int which, void* stream);
 /* Gradient all-reduce over NVLink peer memory fused with ppo_grad_sumsq (several GPUs, one process each):
  * grads_dev [world] = every rank's gradient buffer as mapped into THIS process (symmetric memory), flags_dev
  * [world] = every rank's zero-initialised flag array of ppo_allreduce_flag_words() uint32 (symmetric memory too),
