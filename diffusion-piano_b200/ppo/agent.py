@@ -510,6 +510,8 @@ class PPOAgent:
         else:
             for B in sizes:
                 self._replay((n, B, adv.data_ptr(), returns.data_ptr()), [B], bb, n, adv, returns)
+        if self.world > 1:  # one critic-loss value for all ranks: the schedulers must step identically everywhere
+            dist.sync_scheduler_metric(self.ctrl, _kernels.PPOCtrl.critic_loss.offset, self.world, self.pg)
         self._k(self.lib.ppo_plateau_step, self.ctrl, 0.5, 100)
         return bb
 

@@ -31,3 +31,23 @@ def clip_coefficient(summed_grad_norm2: float, world: int, max_norm: float) -> f
     scale = 1.0 / world
     total = summed_grad_norm2 ** 0.5 * scale
     return min(max_norm / (total + 1e-6), 1.0) * scale
+
+
+def sync_scheduler_metric(ctrl: torch.Tensor, byte_offset: int, world: int, group) -> None:
+    """Mean over ranks, in place, of ONE float32 inside the device control block (`ctrl`: uint8 tensor).
+    The critic's ReduceLROnPlateau (`ppo_v2.py:305-308`) steps on the critic loss of the LAST minibatch, which each
+    rank computes on its own shard with its own dropout draws: without this the ranks' `best` / `num_bad` / `lr`
+    drift apart and the critic replicas then apply one averaged gradient with different learning rates. After the
+    all-reduce every rank holds the same bits, so the scheduler state stays identical on all ranks."""
+    view = ctrl[byte_offset:byte_offset + 4].view(torch.float32)
+    torch.distributed.all_reduce(view, group=group)
+    view.mul_(1.0 / world)
+
+
+def all_ranks_agree(flag: bool, device, group) -> bool:
+    """True only when EVERY rank passes True (all-reduce MIN of one integer). The training loop's `if all(dones):
+    break` (`parallelized_base_v2.py:163`) must be one decision for all ranks: `agent.update` holds collectives,
+    and a rank that left the loop alone would leave the others waiting in them."""
+    t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=device)
+    torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MIN, group=group)
+    return bool(t.item())

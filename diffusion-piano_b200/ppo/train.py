@@ -18,6 +18,7 @@ from typing import Callable, List, Optional
 
 import torch
 
+from . import dist
 from .agent import PPOAgent
 
 
@@ -72,9 +73,16 @@ def train(env, cfg: TrainConfig, process_group=None, agent: Optional[PPOAgent] =
             # all envs play the same song in lockstep: they are done together after `frames` steps, so the
             # reference's `if all(dones): break` needs a device read only then (or every step when a wrong press
             # may end an env early)
-            may_be_done = step >= frames or bool(getattr(env.task, "_wrong_press_termination", False))
-            if may_be_done and bool(dones.all()):
-                break
+            # With several ranks the decision is global (every rank evaluates `may_be_done` alike, so all of them
+            # enter the all-reduce together): a rank leaving alone would strand the others in update's collectives.
+            # `step % frames == 0` also catches envs that ended early, auto-reset and are done again later.
+            may_be_done = step % frames == 0 or bool(getattr(env.task, "_wrong_press_termination", False))
+            if may_be_done:
+                done_here = bool(dones.all())
+                if process_group is not None:
+                    done_here = dist.all_ranks_agree(done_here, env.device, process_group)
+                if done_here:
+                    break
             obs = next_obs
         # statistics of the episode: one small all-reduce outside the step
         total = torch.stack([episode_rewards.sum(), torch.tensor(float(n), device=env.device)])

@@ -92,3 +92,75 @@ def test_clip_coefficient_single_rank_is_clip_grad_norm():
         g = {"g": np.array([norm])}
         po.clip_grad_norm(g, 0.5)
         assert abs(dist.clip_coefficient(norm * norm, 1, 0.5) * norm - g["g"][0]) < 1e-12
+
+
+def _plateau(state, metric, patience=100, factor=0.5):
+    """plateau_kernel of csrc/ppo_kernels.cu for the critic ('min' mode, relative threshold 1e-4), in float32."""
+    lr, best, bad = state
+    metric = np.float32(metric)
+    if metric < best * np.float32(1.0 - 1e-4):
+        best, bad = metric, 0
+    else:
+        bad += 1
+    if bad > patience:
+        nlr = np.float32(lr * np.float32(factor))
+        if lr - nlr > 1e-8:
+            lr = nlr
+        bad = 0
+    return lr, best, bad
+
+
+def _sched_worker(rank: int, world: int, port: int, q):
+    import ctypes
+
+    import torch
+    import torch.distributed as td
+
+    from diffusion_piano_b200.ppo import _kernels, dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    td.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        off = _kernels.PPOCtrl.critic_loss.offset
+        ctrl = torch.zeros(ctypes.sizeof(_kernels.PPOCtrl), dtype=torch.uint8)
+        loss = ctrl[off:off + 4].view(torch.float32)
+        rng = np.random.RandomState(100 + rank)  # every rank's own shard and dropout draws: its own critic loss
+        synced = (np.float32(2e-4), np.float32(np.inf), 0)
+        local = synced
+        for step in range(260):  # more than two patience windows of a loss that stops improving after step 20
+            mine = 1.0 + 5.0 / (1 + min(step, 20)) + 0.05 * rng.standard_normal()
+            local = _plateau(local, mine)
+            loss.fill_(float(mine))
+            dist.sync_scheduler_metric(ctrl, off, world, td.group.WORLD)
+            synced = _plateau(synced, float(loss.item()))
+        # the loop-exit decision: rank 1 alone sees an early termination
+        agree_mixed = dist.all_ranks_agree(rank == 1, torch.device("cpu"), td.group.WORLD)
+        agree_all = dist.all_ranks_agree(True, torch.device("cpu"), td.group.WORLD)
+        q.put((rank, [float(x) for x in synced], [float(x) for x in local], agree_mixed, agree_all,
+               bytes(ctrl.numpy().tobytes())))
+    finally:
+        td.destroy_process_group()
+
+
+def test_two_rank_scheduler_state_stays_identical():
+    """the critic's plateau scheduler steps on a per-rank metric. With the metric averaged over
+    ranks first (`dist.sync_scheduler_metric`, used by PPOAgent.update) lr / best / num_bad are bit-identical on
+    all ranks after more than `patience` non-improving updates; without it they are not (same draws). Also the
+    training loop's global break decision (`dist.all_ranks_agree`)."""
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sched_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, s0, l0, mixed0, all0, c0), (_, s1, l1, mixed1, all1, c1) = out
+    assert s0 == s1 and c0 == c1          # synchronised metric: identical scheduler state and control-block bytes
+    assert s0[0] < 2e-4                   # the learning rate did halve at least once (patience 100 exceeded)
+    assert l0 != l1                       # the unsynchronised schedulers drifted apart (best differs)
+    assert mixed0 is False and mixed1 is False and all0 is True and all1 is True
