@@ -107,7 +107,9 @@ class _Net:
             self.p[k].copy_(torch.as_tensor(np.asarray(params[k], np.float32)).view(self.shapes[k]))
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
-        return {k: v.detach().cpu().clone() for k, v in self.p.items()}
+        """Keys in the reference modules' `state_dict()` order: a module's own parameters (`log_std`) first."""
+        keys = [k for k in self.p if not k.startswith("network.")] + [k for k in self.p if k.startswith("network.")]
+        return {k: self.p[k].detach().cpu().clone() for k in keys}
 
     def buffers(self, rows: int, training: bool) -> dict:
         """Activation buffers for `rows` rows (allocated once per distinct row count)."""
@@ -525,6 +527,10 @@ class PPOAgent:
         raw = self.ctrl.cpu().numpy().tobytes()
         return _kernels.PPOCtrl.from_buffer_copy(raw)
 
+    def write_ctrl(self, c: "_kernels.PPOCtrl") -> None:
+        torch.cuda.synchronize(self.device)
+        self.ctrl.copy_(torch.frombuffer(bytearray(bytes(c)), dtype=torch.uint8))
+
     def stats(self) -> Dict[str, float]:
         c = self.read_ctrl()
         return dict(actor_loss=c.actor_loss, critic_loss=c.critic_loss, entropy=c.entropy, mean_ratio=c.mean_ratio,
@@ -539,15 +545,53 @@ class PPOAgent:
     def critic_state_dict(self):
         return self.critic.state_dict()
 
+    # ---- checkpoints in the reference's layout (ppo_v2.py:311-336)
+    _SCHED = (("actor", 0, "max"), ("critic", 1, "min"))
+
+    @staticmethod
+    def _param_order(net: "_Net") -> List[str]:
+        """`module.parameters()` order of the reference's Actor / Critic: a module's own parameters (`log_std`)
+        come before its children's (`network.*`, in Sequential order)."""
+        own = [k for k in net.shapes if not k.startswith("network.")]
+        return own + [k for k in net.shapes if k.startswith("network.")]
+
+    def _torch_optimizer(self, net: "_Net", which: int, c: "_kernels.PPOCtrl"):
+        """A torch Adam + ReduceLROnPlateau pair carrying this network's state: their `state_dict()`s are what the
+        reference's `load_checkpoint` feeds to `load_state_dict` (same torch, same keys)."""
+        order = self._param_order(net)
+        params = [torch.nn.Parameter(net.p[k].detach().cpu().clone()) for k in order]
+        opt = torch.optim.Adam(params, lr=float(c.lr[which]), betas=(0.9, 0.999), eps=1e-5)
+        if c.adam_t[which] > 0:
+            for prm, k in zip(params, order):
+                opt.state[prm] = {"step": torch.tensor(float(c.adam_t[which])),
+                                  "exp_avg": net._view(net.m, k).detach().cpu().clone(),
+                                  "exp_avg_sq": net._view(net.v, k).detach().cpu().clone()}
+        mode = self._SCHED[which][2]
+        sched = torch.optim.lr_scheduler.ReduceLROnPlateau(opt, mode=mode, factor=0.5, patience=100)
+        sched.best = float(c.best[which])
+        sched.num_bad_epochs = int(c.num_bad[which])
+        sched._last_lr = [float(c.lr[which])]
+        return opt, sched
+
     def save_checkpoint(self, episode, rewards):
-        """Same keys for the networks as the reference's checkpoint (ppo_v2.py:311-325); the optimiser and
-        scheduler states are this implementation's flat buffers and control block."""
+        """The reference's checkpoint (ppo_v2.py:311-325), key for key: network state_dicts, torch Adam state_dicts
+        (per-parameter `step` / `exp_avg` / `exp_avg_sq`, `param_groups` with the current lr) and
+        ReduceLROnPlateau state_dicts (`best`, `num_bad_epochs`), so that `ppo_v2.PPOAgent.load_checkpoint` reads
+        it. One extra key, `b200_state`, holds what the reference does not save and an exact resume here needs
+        (reward normaliser, RNG counter, epoch cursor); the rank-specific seed is NOT part of it."""
         self.checkpoint_dir.mkdir(parents=True, exist_ok=True)
+        c = self.read_ctrl()
         ckpt = {"episode": episode, "actor_state_dict": self.actor_state_dict(),
-                "critic_state_dict": self.critic_state_dict(),
-                "actor_optimizer_state_dict": {"m": self.actor.m.cpu(), "v": self.actor.v.cpu()},
-                "critic_optimizer_state_dict": {"m": self.critic.m.cpu(), "v": self.critic.v.cpu()},
-                "control_block": self.ctrl.cpu(), "rewards": rewards}
+                "critic_state_dict": self.critic_state_dict()}
+        pairs = [(name, self._torch_optimizer(net, which, c))
+                 for (name, which, _), net in zip(self._SCHED, (self.actor, self.critic))]
+        for name, (opt, _) in pairs:  # the reference's key order: both optimisers, then both schedulers
+            ckpt[f"{name}_optimizer_state_dict"] = opt.state_dict()
+        for name, (_, sched) in pairs:
+            ckpt[f"{name}_scheduler_state_dict"] = sched.state_dict()
+        ckpt["rewards"] = rewards
+        ckpt["b200_state"] = {"rms_mean": c.rms_mean, "rms_var": c.rms_var, "rms_count": c.rms_count,
+                              "rng_counter": int(c.rng_counter), "epoch": int(c.epoch)}
         path = self.checkpoint_dir / f"checkpoint_episode_{episode}.pt"
         torch.save(ckpt, path)
         return path
@@ -556,13 +600,45 @@ class PPOAgent:
         torch.save({"actor_state_dict": self.actor_state_dict(), "critic_state_dict": self.critic_state_dict()}, path)
 
     def load_checkpoint(self, path):
+        """Reads a checkpoint written by `save_checkpoint` here OR by the reference's `ppo_v2.PPOAgent` (same
+        keys): networks, Adam moments and step counts, learning rates, plateau-scheduler state. Optimiser state
+        that is present but cannot be mapped onto the flat buffers raises instead of being dropped. The control
+        block's seed stays this rank's own (ranks must not share noise / dropout / permutation streams)."""
         ckpt = torch.load(path, map_location="cpu", weights_only=False)
         self.actor.load({k: v.numpy() for k, v in ckpt["actor_state_dict"].items()})
         self.critic.load({k: v.numpy() for k, v in ckpt["critic_state_dict"].items()})
-        if "control_block" in ckpt:
-            self.actor.m.copy_(ckpt["actor_optimizer_state_dict"]["m"])
-            self.actor.v.copy_(ckpt["actor_optimizer_state_dict"]["v"])
-            self.critic.m.copy_(ckpt["critic_optimizer_state_dict"]["m"])
-            self.critic.v.copy_(ckpt["critic_optimizer_state_dict"]["v"])
-            self.ctrl.copy_(ckpt["control_block"])
+        c = self.read_ctrl()
+        for (name, which, _), net in zip(self._SCHED, (self.actor, self.critic)):
+            osd = ckpt.get(f"{name}_optimizer_state_dict")
+            if osd is not None:
+                order = self._param_order(net)
+                ids = osd["param_groups"][0]["params"]
+                if len(osd["param_groups"]) != 1 or len(ids) != len(order):
+                    raise ValueError(f"{name} optimiser state: {len(ids)} parameters in {len(osd['param_groups'])} "
+                                     f"groups, expected {len(order)} in one group")
+                c.lr[which] = float(osd["param_groups"][0]["lr"])
+                net.m.zero_(); net.v.zero_()
+                steps = set()
+                for pid, k in zip(ids, order):
+                    st = osd["state"].get(pid)
+                    if st is None:
+                        continue
+                    if tuple(st["exp_avg"].shape) != tuple(net.shapes[k]):
+                        raise ValueError(f"{name} optimiser state of {k}: shape {tuple(st['exp_avg'].shape)}, "
+                                         f"expected {net.shapes[k]}")
+                    net._view(net.m, k).copy_(st["exp_avg"])
+                    net._view(net.v, k).copy_(st["exp_avg_sq"])
+                    steps.add(int(float(st["step"])))
+                if len(steps) > 1:
+                    raise ValueError(f"{name} optimiser state: parameters at different Adam steps {sorted(steps)}")
+                c.adam_t[which] = steps.pop() if steps else 0
+            ssd = ckpt.get(f"{name}_scheduler_state_dict")
+            if ssd is not None:
+                c.best[which] = float(ssd["best"])
+                c.num_bad[which] = int(ssd["num_bad_epochs"])
+        extra = ckpt.get("b200_state")
+        if extra is not None:
+            c.rms_mean, c.rms_var, c.rms_count = extra["rms_mean"], extra["rms_var"], extra["rms_count"]
+            c.rng_counter, c.epoch = extra["rng_counter"], extra["epoch"]
+        self.write_ctrl(c)
         return ckpt.get("episode", 0), ckpt.get("rewards")

@@ -481,7 +481,13 @@ def test_train_loop_config4_smoke(torch_cuda):
         other = PPOAgent(env.obs_dim, env.action_dim, device="cuda:0", seed=99, checkpoint_dir=d)
         other.load_checkpoint(path)
         assert torch.equal(other.actor.theta, agent.actor.theta) and torch.equal(other.critic.m, agent.critic.m)
-        assert bytes(other.read_ctrl()) == bytes(agent.read_ctrl())
+        # optimiser, scheduler, normaliser and RNG position are restored; the seed stays the loading rank's own
+        mine, theirs = other.read_ctrl(), agent.read_ctrl()
+        for f in ("lr", "adam_t", "best", "num_bad"):
+            assert list(getattr(mine, f)) == list(getattr(theirs, f)), f
+        for f in ("rms_mean", "rms_var", "rms_count", "rng_counter", "epoch"):
+            assert getattr(mine, f) == getattr(theirs, f), f
+        assert mine.seed != theirs.seed
     env.close()
 
 
@@ -545,3 +551,83 @@ def test_large_minibatch_takes_the_cublas_path(torch_cuda):
     for mine, theirs in ((ag.actor_state_dict(), ora.actor_state()), (ag.critic_state_dict(), ora.critic_state())):
         for k, v in mine.items():
             np.testing.assert_allclose(v.numpy(), theirs[k], atol=5e-6, err_msg=k)
+
+
+def test_checkpoint_is_the_reference_layout_and_round_trips(tmp_path):
+    """`save_checkpoint` writes what the reference's `ppo_v2.PPOAgent.load_checkpoint`
+    (ppo_v2.py:327-336) reads - same top-level keys, state_dict keys and order, torch Adam / ReduceLROnPlateau
+    state_dicts (layout recorded from the reference itself: tests/golden/ppo_checkpoint_layout.json,
+    tools/make_ppo_checkpoint_layout.py) - torch's own load_state_dict accepts it, and loading it back restores
+    moments, step counts, learning rates and scheduler state while the rank-specific seed stays the loader's."""
+    import json
+    import torch
+    from diffusion_piano_b200.ppo import PPOAgent
+    lay = json.loads((ROOT / "tests" / "golden" / "ppo_checkpoint_layout.json").read_text())
+    S, A, N = lay["state_dim"], lay["action_dim"], 64
+    sys.path.insert(0, str(ROOT / "tools"))
+    from make_ppo_golden import ppo_fixture_inputs
+    _, _, b = ppo_fixture_inputs(3, S, A, N)
+    agent = PPOAgent(S, A, batch_size=32, ppo_epochs=1, device="cuda:0", seed=5, checkpoint_dir=tmp_path, use_graphs=False)
+    for _ in range(2):
+        agent.update(b["states"], b["actions"], b["rewards"].astype(np.float32), b["log_probs"], b["next_states"], b["dones"])
+    path = agent.save_checkpoint(7, {"mean_rewards": [1.0]})
+    ck = torch.load(path, map_location="cpu", weights_only=False)
+    assert list(ck)[:len(lay["keys"])] == lay["keys"] and set(ck) - set(lay["keys"]) == {"b200_state"}
+    for net in ("actor", "critic"):
+        assert [[k, list(v.shape)] for k, v in ck[f"{net}_state_dict"].items()] == lay[f"{net}_state_dict"]
+        osd, ol = ck[f"{net}_optimizer_state_dict"], lay[f"{net}_optimizer"]
+        g = osd["param_groups"][0]
+        assert len(osd["param_groups"]) == ol["n_groups"] and sorted(g) == ol["group_keys"] and g["params"] == ol["params"]
+        assert list(g["betas"]) == ol["betas"] and g["eps"] == ol["eps"] and g["weight_decay"] == ol["weight_decay"]
+        assert [list(osd["state"][i]["exp_avg"].shape) for i in g["params"]] == ol["shapes"]
+        st = osd["state"][g["params"][0]]
+        assert sorted(st) == ol["state_keys"] and torch.is_tensor(st["step"]) and float(st["step"]) == 4.0  # 2 updates x 2 minibatches
+        assert sorted(ck[f"{net}_scheduler_state_dict"]) == lay[f"{net}_scheduler_keys"]
+        for k in ("mode", "factor", "patience"):
+            assert ck[f"{net}_scheduler_state_dict"][k] == lay[f"{net}_scheduler"][k]
+    # what the reference's load_checkpoint does with the file: torch modules of its architecture + load_state_dict
+    h = 256
+    seq = lambda dims, drop: torch.nn.Sequential(*[m for i in range(3) for m in (
+        [torch.nn.Linear(dims[i], dims[i + 1]), torch.nn.ReLU(), torch.nn.LayerNorm(dims[i + 1])]
+        + ([torch.nn.Dropout(0.1)] if drop[i] else []))] + [torch.nn.Linear(dims[3], dims[4])])
+
+    class Actor(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.network = torch.nn.Sequential(*list(seq((S, h, h, h, A), (0, 0, 0))), torch.nn.Tanh())
+            self.log_std = torch.nn.Parameter(torch.ones(A) * -1.0)
+
+    class Critic(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.network = seq((S, h, h, h // 2, 1), (1, 1, 0))
+
+    ref_a, ref_c = Actor(), Critic()
+    ref_a.load_state_dict(ck["actor_state_dict"]); ref_c.load_state_dict(ck["critic_state_dict"])
+    for mod, net, mode in ((ref_a, "actor", "max"), (ref_c, "critic", "min")):
+        opt = torch.optim.Adam(mod.parameters(), lr=1e-4, betas=(0.9, 0.999), eps=1e-5)
+        sch = torch.optim.lr_scheduler.ReduceLROnPlateau(opt, mode=mode, factor=0.5, patience=100)
+        opt.load_state_dict(ck[f"{net}_optimizer_state_dict"]); sch.load_state_dict(ck[f"{net}_scheduler_state_dict"])
+        mine = agent.actor if net == "actor" else agent.critic
+        for name, prm in mod.named_parameters():
+            np.testing.assert_array_equal(opt.state[prm]["exp_avg"].numpy(), mine._view(mine.m, name).cpu().numpy())
+            np.testing.assert_array_equal(opt.state[prm]["exp_avg_sq"].numpy(), mine._view(mine.v, name).cpu().numpy())
+            np.testing.assert_array_equal(prm.detach().numpy(), mine.p[name].cpu().numpy())
+    # and back: a fresh agent of another "rank" resumes with identical optimiser / scheduler state, its own seed
+    c0 = agent.read_ctrl()
+    other = PPOAgent(S, A, batch_size=32, ppo_epochs=1, device="cuda:0", seed=9, checkpoint_dir=tmp_path, use_graphs=False)
+    seed_before = other.read_ctrl().seed
+    episode, rewards = other.load_checkpoint(path)
+    c1 = other.read_ctrl()
+    assert episode == 7 and rewards == {"mean_rewards": [1.0]}
+    assert c1.seed == seed_before != c0.seed
+    for f in ("lr", "adam_t", "best", "num_bad"):
+        assert list(getattr(c1, f)) == list(getattr(c0, f)), f
+    assert (c1.rms_mean, c1.rms_var, c1.rms_count, c1.rng_counter) == (c0.rms_mean, c0.rms_var, c0.rms_count, c0.rng_counter)
+    for mine, theirs in ((agent.actor, other.actor), (agent.critic, other.critic)):
+        for buf in ("theta", "m", "v"):
+            assert torch.equal(getattr(mine, buf), getattr(theirs, buf)), buf
+    # the next update from the restored state gives the same parameters as continuing the original (same seed needed:
+    # compare the deterministic part only - Adam step counts and learning rates advance alike)
+    other.update(b["states"], b["actions"], b["rewards"].astype(np.float32), b["log_probs"], b["next_states"], b["dones"])
+    assert list(other.read_ctrl().adam_t) == [6, 6]
