@@ -73,9 +73,12 @@ def workload_config(envs_per_gpu: int, n_gpus: int, task) -> dict:
 # ------------------------------------------------------------------ CPU arm (oracle port)
 class CpuPort:
     """n independent fp64 oracle envs stepped with OpenMP over envs (oracle/piano_oracle.c).
-    Physics only: the task epilogue (rewards, observation gather) is < 1 % of a CPU env step."""
+    Physics only: the task epilogue (rewards, observation gather) is < 1 % of a CPU env step.
+    sparse=True (the timed baseline): po_step_sparse - sparse constraint rows, one dense block over the coupled
+    dofs, no allocation in the step; same results as the dense clarity-first po_step to 1e-12
+    (tests/test_scene_and_oracle.py) and ~8x faster."""
 
-    def __init__(self, task, n_envs: int):
+    def __init__(self, task, n_envs: int, sparse: bool = True):
         from oracle import oracle_physics as op
 
         self.op = op
@@ -86,6 +89,7 @@ class CpuPort:
         a = task.model.a
         self.lo, self.hi = a["act_ctrlrange"][:, 0].copy(), a["act_ctrlrange"][:, 1].copy()
         self.nsub = task.physics_steps_per_control_step
+        self.batch = op.lib().po_step_batch_sparse if sparse else op.lib().po_step_batch
         # all host cores, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1)
         op.lib().po_set_num_threads(os.cpu_count() or 1)
 
@@ -93,12 +97,12 @@ class CpuPort:
         ctrl = self.lo + 0.5 * (canonical_action[:44].astype(np.float64) + 1.0) * (self.hi - self.lo)
         for e in self.envs:
             e.ctrl[:] = ctrl
-        self.op.lib().po_step_batch(self.mp, self.ptrs, self.n, self.nsub)
+        self.batch(self.mp, self.ptrs, self.n, self.nsub)
 
 
-def time_cpu_port(task, actions: np.ndarray, n_envs: int, steps: int, warmup: int) -> float:
+def time_cpu_port(task, actions: np.ndarray, n_envs: int, steps: int, warmup: int, sparse: bool = True) -> float:
     """env-steps/s of the oracle port on the host cores."""
-    port = CpuPort(task, n_envs)
+    port = CpuPort(task, n_envs, sparse)
     for i in range(warmup):
         port.step(actions[i % len(actions)])
     t0 = time.perf_counter()
@@ -113,12 +117,13 @@ def run_reference(args) -> None:
         return
     task = build_task()
     cores = os.cpu_count() or 1
-    n_envs = 2 * cores
+    n_envs = 8 * cores
     os.environ.setdefault("OMP_NUM_THREADS", str(cores))
     t0 = time.perf_counter()
     v = time_cpu_port(task, recorded_actions(), n_envs, args.steps, max(1, min(args.warmup, 2)))
     sample = (f"{n_envs} envs x {args.steps} control steps of the workload (10 fp64 substeps each), "
-              f"OpenMP over envs, physics restatement only; MuJoCo itself unavailable on this box")
+              f"OpenMP over envs, po_step_sparse (block-structured physics restatement, no allocation in the step); "
+              f"MuJoCo itself unavailable on this box")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * n_envs / v,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -308,11 +313,16 @@ def run_product(args) -> None:
                 "wall_ms_per_step_incl_flush": 1e3 * t_wall / K, "mean_reward_last_step": rew_mean, "solver": solver}
         if world == 1 and not args.no_cpu:
             cores = os.cpu_count() or 1
-            n_envs, steps = 2 * cores, args.cpu_steps
+            n_envs, steps = 8 * cores, args.cpu_steps
             v = time_cpu_port(task, table, n_envs, steps, 1)
+            v_dense = time_cpu_port(task, table, 2 * cores, max(2, steps // 4), 1, sparse=False)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"{n_envs} envs x {steps} control steps of the same workload, fp64 oracle "
-                                              f"port (physics restatement), OpenMP over envs; MuJoCo unavailable on this box"}
+                                              f"port po_step_sparse (block-structured, no allocation in the step), OpenMP "
+                                              f"over envs; MuJoCo unavailable on this box",
+                                    "dense_port_value": v_dense,
+                                    "dense_port_note": "the clarity-first dense 140x140 po_step (round 1's baseline), "
+                                                       "same results to 1e-12"}
     env.close()
     del env, acts, flush
     torch.cuda.empty_cache()
@@ -353,7 +363,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--envs", type=int, default=4096, help="envs per GPU")
-    ap.add_argument("--cpu-steps", type=int, default=8, help="control steps of the bounded CPU sample")
+    ap.add_argument("--cpu-steps", type=int, default=16, help="control steps of the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--extras", default="3,5,4", help="other BASELINE configs timed after the headline ('' = none)")
     ap.add_argument("--extra-steps", type=int, default=10, help="timed control steps of each extra config")

@@ -542,7 +542,12 @@ extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* 
   if (e->timeline) CUDA_OK(cudaEventRecord(e->tl_h2d, s));
   // pieces on their own streams (hands task, large batches): a piece's results travel to the host while the later
   // pieces are still stepping. All grids are resident together, so the device does the same work.
-  const bool split = e->cfg.task == PP_TASK_PIANO_WITH_SHADOW_HANDS && N >= 1024 && e->host_chunks > 1;
+  // Unsplit while the launch-shape tuner (pp_set_schedule, PP_SCHED_AUTO) still has to time full-batch steps, and
+  // whenever the divergent shape is in force: its work order spans the whole batch, and it is worth more there
+  // (~10 %) than the copy overlap of the pieces (~5 %).
+  const bool tuning = e->sched_mode == PP_SCHED_AUTO && !e->tuned;
+  const bool split = e->cfg.task == PP_TASK_PIANO_WITH_SHADOW_HANDS && N >= 1024 && e->host_chunks > 1 && !tuning &&
+                     !e->sort_work;
   const int pieces = split ? e->host_chunks : 1;
   const size_t per = split ? ((N / pieces + 9) / 10) * 10 : N;  // a multiple of both block shapes (2 and 10 envs)
   if (split) {

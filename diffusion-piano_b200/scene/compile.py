@@ -337,6 +337,8 @@ def compile_scene(
     physics_timestep: float = 0.005,
     reduced_action_space: bool = False,
     reduced_by_removal: bool = False,
+    attachment_yaw: float = 0.0,
+    forearm_dofs=("forearm_tx", "forearm_ty"),
 ) -> CompiledModel:
     """Builds the task scene the reference assembles in `suite/tasks/base.py:45-197`.
 
@@ -349,7 +351,18 @@ def compile_scene(
     locked rows, as the reference's compiled model would have them. `model.locked_dofs` / `model.dead_actuators`
     list them for the façade, which drops them from the action and observation specs.
     reduced_by_removal=True builds the reference's own form instead (joints and actuators deleted, nv = 134): the
-    step kernel cannot run it, the CPU checker can: the tests compare the two forms."""
+    step kernel cannot run it, the CPU checker can: the tests compare the two forms.
+
+    attachment_yaw [degrees] (`tasks/base.py:103,175-183`): the forearms are rotated about world z by +yaw (right
+    hand) / -yaw (left hand) before the hand's own root quaternion.
+    forearm_dofs (`tasks/base.py:104`, `shadow_hand.py:41-69,272-311`): which forearm joints exist. Subsets of the
+    default pair are built by LOCKING the missing slide exactly as above (the kernel's tree keeps 26 dofs per hand);
+    the reference's other four (forearm_tz / roll / pitch / yaw) would add dofs to that tree and are not built."""
+    forearm_dofs = tuple(forearm_dofs)
+    extra = [n for n in forearm_dofs if n not in shm.FOREARM_DOFS]
+    if extra:
+        raise NotImplementedError(f"forearm dofs {extra} are not built: the step kernel's hand tree has the two "
+                                  "default slides only (forearm_tx, forearm_ty) - SURVEY 8f rank 4")
     bld = _Builder()
     _add_piano(bld, piano_actuators)
     infos = []
@@ -357,7 +370,9 @@ def compile_scene(
         half_w = pm.BASE_SIZE[1]  # piano.size[1], base.py:160
         for side, position in (("right", RIGHT_HAND_POSITION), ("left", LEFT_HAND_POSITION)):
             tx_range = (-half_w - position[1], half_w - position[1])
-            infos.append(_add_hand(bld, side, position, qnorm(HAND_QUATERNION), gravity_compensation, tx_range,
+            sign = -1.0 if side == "left" else 1.0
+            quat = qmul(axis_angle((0.0, 0.0, 1.0), np.radians(sign * attachment_yaw)), qnorm(HAND_QUATERNION))
+            infos.append(_add_hand(bld, side, position, qnorm(quat), gravity_compensation, tx_range,
                                    REDUCED_EXCLUDED_JOINTS if reduced_action_space and reduced_by_removal else ()))
     locked, dead = [], []
     if hands and reduced_action_space and reduced_by_removal:  # the reference's own construction (for the CPU checker)
@@ -377,6 +392,13 @@ def compile_scene(
             a2 = next(i for i, n in enumerate(bld.act["name"]) if n.endswith("/" + pre + "A_THJ2"))
             bld.dof["range"][d2] = REDUCED_THUMB_RANGE
             bld.act["ctrlrange"][a2] = REDUCED_THUMB_RANGE
+    if hands and not reduced_by_removal:
+        for info in infos:  # forearm slides the task does not ask for: locked, their actuators dead
+            model = "lh_shadow_hand/" if info is infos[1] else "rh_shadow_hand/"
+            for dof_name in shm.FOREARM_DOFS:
+                if dof_name not in forearm_dofs:
+                    locked.append(info["dof"][dof_name])
+                    dead.append(bld.act["name"].index(model + dof_name))
     M, jacs = _mass_matrix0(bld)
     if hands:
         # physics_utils.get_critical_damping_from_stiffness: 2*sqrt(dof_M0 * k)

@@ -108,8 +108,7 @@ class PianoWithShadowHands(_PianoTaskBase):
         del disable_colorization, change_color_on_activation  # visual only
         # primitive_fingertip_collisions: the mesh colliders are unavailable, capsules are always used
         del primitive_fingertip_collisions
-        if attachment_yaw != 0 or tuple(forearm_dofs) != ("forearm_tx", "forearm_ty"):
-            raise NotImplementedError("only the default attachment_yaw / forearm_dofs are built (SURVEY §8f rank 4)")
+        # attachment_yaw: any angle; forearm_dofs: subsets of the default pair (others raise in compile_scene)
         self._reduced_action_space = bool(reduced_action_space)
         self._randomize_hand_positions = bool(randomize_hand_positions)
         if n_seconds_lookahead is not None:
@@ -124,7 +123,8 @@ class PianoWithShadowHands(_PianoTaskBase):
         self.model = scene_compile.compile_scene(
             hands=True, gravity_compensation=gravity_compensation,
             disable_hand_collisions=disable_hand_collisions, physics_timestep=physics_timestep,
-            reduced_action_space=self._reduced_action_space)
+            reduced_action_space=self._reduced_action_space, attachment_yaw=float(attachment_yaw),
+            forearm_dofs=tuple(forearm_dofs))
         names = ["key_press_reward", "sustain_reward", "energy_reward"]
         names.append("ot_fingering_reward" if self._disable_fingering_reward else "fingering_reward")
         if not disable_forearm_reward:
@@ -141,10 +141,10 @@ class PianoWithShadowHands(_PianoTaskBase):
             energy_penalty_coef=self._energy_penalty_coef, device=device)
 
     def reduced_spec(self):
-        """reduced_action_space (shadow_hand.py:160-181): (kept action columns of the engine's 45, kept observation
+        """reduced_action_space (shadow_hand.py:160-181) and forearm_dofs subsets (shadow_hand.py:272-311): (kept action columns of the engine's 45, kept observation
         columns of the engine's row, layout of the compacted row) - the removed joints' three actuators and three
         joint positions per hand leave both specs. None for the full hand."""
-        if not self._reduced_action_space:
+        if not self.model.locked_dofs:
             return None
         full = self.observation_layout(full=True)
         act_keep = [i for i in range(45) if i not in self.model.dead_actuators]
@@ -165,7 +165,7 @@ class PianoWithShadowHands(_PianoTaskBase):
         return act_keep, obs_keep, layout
 
     def observation_layout(self, full: bool = False) -> "OrderedDict[str, Tuple[int, int]]":
-        if self._reduced_action_space and not full:
+        if self.model.locked_dofs and not full:
             return self.reduced_spec()[2]
         g = (self._n_steps_lookahead + 1) * (NUM_KEYS + 1)
         f = 0 if self._disable_fingering_reward else 10

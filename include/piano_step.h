@@ -86,8 +86,13 @@ int pp_step(pp_env *env, const float *actions_dev, float *obs_dev, float *reward
 /* Host-buffer variant: H2D of actions, step, D2H of obs/reward/done inside the call; returns
  * after the results are on the host. Page-locked caller buffers (cudaHostAlloc, cudaHostRegister,
  * torch pin_memory) are the DMA endpoints themselves; pageable ones go through pinned staging
- * owned by the handle plus one host memcpy each. Large two-hand batches are stepped as two halves on
- * two internal streams so that the first half's D2H overlaps the second half's step (same results). */
+ * owned by the handle plus one host memcpy each. Large two-hand batches are stepped in pieces on internal
+ * streams so that a piece's D2H overlaps the later pieces' steps (same results); while the schedule tuner is still
+ * measuring, and under the divergent schedule, the batch is stepped whole. */
+/* Stream contract: the *_host entry points run on the handle's own non-blocking streams and return with the
+ * results on the host. They are NOT ordered against work the caller queued earlier through the device entry points
+ * (pp_step, pp_reset, pp_set_state, pp_set_hand_offsets, pp_set_qfrc_applied) on the caller's streams: synchronise
+ * those streams before mixing the two families on one handle. */
 int pp_step_host(pp_env *env, const float *actions, float *obs, float *reward,
                  float *reward_terms, uint8_t *done, float *discount);
 int pp_reset_host(pp_env *env, const uint8_t *mask, float *obs);

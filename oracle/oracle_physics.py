@@ -33,7 +33,7 @@ class _Data(ctypes.Structure):
                               "actuator_velocity", "qfrc_actuator", "qfrc_smooth", "qacc_smooth")]
         + [("ncon", ctypes.c_int), ("nefc", ctypes.c_int), ("ncon_dropped", ctypes.c_int),
            ("contact", _Contact * 256), ("qacc", _PD), ("qfrc_constraint", _PD),
-           ("solver_iter", ctypes.c_int), ("solver_cost", ctypes.c_double)]
+           ("solver_iter", ctypes.c_int), ("solver_cost", ctypes.c_double), ("ws", ctypes.c_void_p)]
     )
 
 
@@ -58,6 +58,9 @@ def lib():
         _LIB.po_step_batch.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.POINTER(_Data)),
                                        ctypes.c_int, ctypes.c_int]
         _LIB.po_set_num_threads.argtypes = [ctypes.c_int]
+        _LIB.po_step_sparse.argtypes = [ctypes.c_void_p, ctypes.POINTER(_Data)]
+        _LIB.po_step_batch_sparse.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.POINTER(_Data)),
+                                              ctypes.c_int, ctypes.c_int]
     return _LIB
 
 
@@ -113,6 +116,11 @@ class OraclePhysics:
     def step(self, nsub: int = 1):
         for _ in range(nsub):
             lib().po_step(self._mp, self._d)
+
+    def step_sparse(self, nsub: int = 1):
+        """po_step_sparse: the same step with the model's block structure exploited (the timed CPU baseline)."""
+        for _ in range(nsub):
+            lib().po_step_sparse(self._mp, self._d)
 
     def forward_position(self, with_collision: bool = True):
         lib().po_forward_position(self._mp, self._d, int(with_collision))

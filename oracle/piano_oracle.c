@@ -90,6 +90,7 @@ void po_data_free(po_data *d) {
                  d->actuator_velocity, d->qfrc_actuator, d->qfrc_smooth, d->qacc_smooth, d->qacc,
                  d->qfrc_constraint};
   for (size_t i = 0; i < sizeof(p) / sizeof(p[0]); i++) free(p[i]);
+  free(d->ws); /* one block: see ws_get */
   free(d);
 }
 
@@ -217,9 +218,8 @@ static double v6dot(const double *a, const double *b) {
 }
 
 /* mj_crb: composite rigid body algorithm -> dense qM (armature included) */
-static void crb(const pp_model *m, po_data *d) {
+static void crb_buf(const pp_model *m, po_data *d, double *Ic) {
   int nb = m->nbody, nv = m->nv;
-  double *Ic = (double *)malloc(sizeof(double) * 36 * nb);
   for (int b = 0; b < nb; b++) body_inertia6(m, d, b, Ic + 36 * b);
   for (int b = nb - 1; b > 0; b--) {
     int p = m->body_parent[b];
@@ -236,15 +236,17 @@ static void crb(const pp_model *m, po_data *d) {
       d->qM[i * nv + j] = d->qM[j * nv + i] = v6dot(Sj, F);
     }
   }
+}
+static void crb(const pp_model *m, po_data *d) {
+  double *Ic = (double *)malloc(sizeof(double) * 36 * m->nbody);
+  crb_buf(m, d, Ic);
   free(Ic);
 }
 
 /* mj_rne(flg_acc=0): Coriolis, centrifugal and gravity forces */
-static void rne_bias(const pp_model *m, po_data *d) {
+static void rne_bias_buf(const pp_model *m, po_data *d, double *vel, double *acc, double *frc) {
   int nb = m->nbody;
-  double *vel = (double *)calloc(6 * nb, sizeof(double));
-  double *acc = (double *)calloc(6 * nb, sizeof(double));
-  double *frc = (double *)calloc(6 * nb, sizeof(double));
+  memset(vel, 0, sizeof(double) * 6 * nb); memset(acc, 0, sizeof(double) * 6 * nb); memset(frc, 0, sizeof(double) * 6 * nb);
   for (int k = 0; k < 3; k++) acc[3 + k] = -m->gravity[k];
   for (int b = 1; b < nb; b++) {
     int p = m->body_parent[b];
@@ -275,7 +277,12 @@ static void rne_bias(const pp_model *m, po_data *d) {
     int p = m->body_parent[b];
     for (int i = 0; i < 6; i++) frc[6 * p + i] += frc[6 * b + i];
   }
-  free(vel); free(acc); free(frc);
+}
+static void rne_bias(const pp_model *m, po_data *d) {
+  int nb = m->nbody;
+  double *buf = (double *)malloc(sizeof(double) * 18 * nb);
+  rne_bias_buf(m, d, buf, buf + 6 * nb, buf + 12 * nb);
+  free(buf);
 }
 
 /* translational Jacobian row block: jac[3][nv] of a world point attached to body b */
@@ -300,11 +307,10 @@ static void jac_point(const pp_model *m, const po_data *d, int b, const double *
 }
 
 /* mj_passive: joint springs, dampers, gravity compensation */
-static void passive(const pp_model *m, po_data *d) {
+static void passive_buf(const pp_model *m, po_data *d, double *jac) {
   int nv = m->nv;
   for (int j = 0; j < nv; j++)
     d->qfrc_passive[j] = -m->jnt_stiffness[j] * (d->qpos[j] - m->jnt_springref[j]) - m->dof_damping[j] * d->qvel[j];
-  double *jac = (double *)malloc(sizeof(double) * 3 * nv);
   for (int b = 1; b < m->nbody; b++) {
     if (m->body_gravcomp[b] == 0) continue;
     double f[3];
@@ -312,6 +318,10 @@ static void passive(const pp_model *m, po_data *d) {
     jac_point(m, d, b, d->xipos + 3 * b, jac);
     for (int j = 0; j < nv; j++) d->qfrc_passive[j] += jac[j] * f[0] + jac[nv + j] * f[1] + jac[2 * nv + j] * f[2];
   }
+}
+static void passive(const pp_model *m, po_data *d) {
+  double *jac = (double *)malloc(sizeof(double) * 3 * m->nv);
+  passive_buf(m, d, jac);
   free(jac);
 }
 
@@ -896,4 +906,325 @@ void po_step_batch(const pp_model *m, po_data **d, int nenv, int nsub) {
 #pragma omp parallel for schedule(dynamic, 1)
   for (int i = 0; i < nenv; i++)
     for (int s = 0; s < nsub; s++) po_step(m, d[i]);
+}
+
+
+/* ====================================================================== po_step_sparse
+ * The same pipeline with this model's structure exploited and no allocation inside the step (piano_oracle.h).
+ * Dof sets: T = dofs of kinematic trees with more than one dof (the two hands; fixed per model), C = T plus the
+ * 1-dof joints that share a constraint row with another dof in this substep (keys under a finger). M and the
+ * Newton Hessian are dense over T / C and diagonal elsewhere. */
+typedef struct {
+  int nv, cap_rows, cap_nnz, nt, nc, nrows, nnz;
+  int *tlist, *tidx;            /* T and dof -> position in T (-1: isolated 1-dof joint) */
+  int *clist, *cidx;            /* C and dof -> position in C (-1: scalar) */
+  int *rowptr, *col, *type;     /* constraint rows, CSR */
+  double *val, *D, *aref, *floss, *force, *curv, *jar, *jp;
+  double *H, *LM, *Hd, *grad, *p, *Mp, *Ma, *a, *t1, *t2, *j1, *j2;
+  double *Ic, *vel, *acc, *frc; /* crb / rne scratch */
+} po_ws;
+
+static po_ws *ws_get(const pp_model *m, po_data *d) {
+  if (d->ws) return (po_ws *)d->ws;
+  int nv = m->nv, nb = m->nbody;
+  int cap_rows = 3 * nv + 4 * PO_MAXCON + 1, cap_nnz = 3 * nv + 4 * PO_MAXCON * 64;
+  size_t ni = (size_t)4 * nv + (cap_rows + 1) + cap_nnz + cap_rows;
+  size_t nd = (size_t)cap_nnz + 7 * (size_t)cap_rows + 2 * (size_t)nv * nv + 8 * (size_t)nv + 6 * (size_t)nv +
+              (size_t)36 * nb + 18 * (size_t)nb;
+  char *blk = (char *)calloc(1, sizeof(po_ws) + ni * sizeof(int) + 8 + nd * sizeof(double));
+  po_ws *w = (po_ws *)blk;
+  int *ip = (int *)(blk + sizeof(po_ws));
+  w->nv = nv; w->cap_rows = cap_rows; w->cap_nnz = cap_nnz;
+  w->tlist = ip; ip += nv; w->tidx = ip; ip += nv; w->clist = ip; ip += nv; w->cidx = ip; ip += nv;
+  w->rowptr = ip; ip += cap_rows + 1; w->col = ip; ip += cap_nnz; w->type = ip; ip += cap_rows;
+  double *dp = (double *)(((uintptr_t)ip + 7) & ~(uintptr_t)7);
+  w->val = dp; dp += cap_nnz;
+  w->D = dp; dp += cap_rows; w->aref = dp; dp += cap_rows; w->floss = dp; dp += cap_rows; w->force = dp; dp += cap_rows;
+  w->curv = dp; dp += cap_rows; w->jar = dp; dp += cap_rows; w->jp = dp; dp += cap_rows;
+  w->H = dp; dp += (size_t)nv * nv; w->LM = dp; dp += (size_t)nv * nv;
+  w->Hd = dp; dp += nv; w->grad = dp; dp += nv; w->p = dp; dp += nv; w->Mp = dp; dp += nv; w->Ma = dp; dp += nv;
+  w->a = dp; dp += nv; w->t1 = dp; dp += nv; w->t2 = dp; dp += nv;
+  w->j1 = dp; dp += 3 * nv; w->j2 = dp; dp += 3 * nv;
+  w->Ic = dp; dp += 36 * nb; w->vel = dp; dp += 6 * nb; w->acc = dp; dp += 6 * nb; w->frc = dp; dp += 6 * nb;
+  /* T: a dof with a parent dof, or that is some dof's parent */
+  for (int j = 0; j < nv; j++) w->tidx[j] = -1;
+  for (int j = 0; j < nv; j++)
+    if (m->dof_parent[j] >= 0) { w->tidx[j] = 0; w->tidx[m->dof_parent[j]] = 0; }
+  for (int j = 0; j < nv; j++)
+    if (w->tidx[j] == 0) { w->tidx[j] = w->nt; w->tlist[w->nt++] = j; }
+  d->ws = w;
+  return w;
+}
+
+/* y = M x with M dense over T and diagonal elsewhere */
+static void ws_matvecM(const po_ws *w, const po_data *d, const double *x, double *y) {
+  int nv = w->nv;
+  for (int j = 0; j < nv; j++) if (w->tidx[j] < 0) y[j] = d->qM[(size_t)j * nv + j] * x[j];
+  for (int a = 0; a < w->nt; a++) {
+    int i = w->tlist[a];
+    const double *Mi = d->qM + (size_t)i * nv;
+    double s = 0;
+    for (int b = 0; b < w->nt; b++) s += Mi[w->tlist[b]] * x[w->tlist[b]];
+    y[i] = s;
+  }
+}
+
+/* x <- (M + diag(extra))^-1 x : Cholesky over T, scalars elsewhere (extra may be NULL) */
+static void ws_solveM(po_ws *w, const po_data *d, const double *extra, double *x) {
+  int nv = w->nv, nt = w->nt;
+  for (int j = 0; j < nv; j++)
+    if (w->tidx[j] < 0) x[j] /= d->qM[(size_t)j * nv + j] + (extra ? extra[j] : 0.0);
+  for (int a = 0; a < nt; a++) {
+    int i = w->tlist[a];
+    for (int b = 0; b < nt; b++) w->LM[a * nt + b] = d->qM[(size_t)i * nv + w->tlist[b]];
+    if (extra) w->LM[a * nt + a] += extra[i];
+    w->t1[a] = x[i];
+  }
+  chol_factor(w->LM, nt);
+  chol_solve(w->LM, nt, w->t1);
+  for (int a = 0; a < nt; a++) x[w->tlist[a]] = w->t1[a];
+}
+
+static int ws_new_row(po_ws *w, int type, double D, double floss) {
+  int r = w->nrows++;
+  w->rowptr[r] = w->nnz;
+  w->type[r] = type; w->D[r] = D; w->floss[r] = floss;
+  return r;
+}
+static void ws_push(po_ws *w, int col, double val) { w->col[w->nnz] = col; w->val[w->nnz] = val; w->nnz++; }
+static double ws_rowdot(const po_ws *w, int r, const double *x) {
+  double s = 0;
+  for (int k = w->rowptr[r]; k < w->rowptr[r + 1]; k++) s += w->val[k] * x[w->col[k]];
+  return s;
+}
+static void ws_row_eval(const po_ws *w, int r, double x, double *cost, double *force, double *curv) {
+  double D = w->D[r];
+  if (w->type[r] == ROW_INEQ) {
+    if (x < 0) { *cost = 0.5 * D * x * x; *force = -D * x; *curv = D; }
+    else { *cost = 0; *force = 0; *curv = 0; }
+  } else {
+    double f = w->floss[r], rf = f / D;
+    if (x <= -rf) { *cost = -0.5 * rf * f - f * x; *force = f; *curv = 0; }
+    else if (x >= rf) { *cost = -0.5 * rf * f + f * x; *force = -f; *curv = 0; }
+    else { *cost = 0.5 * D * x * x; *force = -D * x; *curv = D; }
+  }
+}
+
+/* mj_makeConstraint with sparse rows (same rows, same order, same numbers as make_constraint) */
+static void ws_make_constraint(const pp_model *m, po_data *d, po_ws *w) {
+  int nv = m->nv;
+  w->nrows = 0; w->nnz = 0;
+  double K, B;
+  stiffness_damping(m, m->friction_solref, m->friction_solimp, &K, &B);
+  double impf = impedance(m->friction_solimp, 0, 0);
+  for (int j = 0; j < nv; j++) {
+    if (m->dof_frictionloss[j] <= 0) continue;
+    double R = fmax(MINVAL, (1 - impf) * m->dof_invweight0[j] / impf);
+    int r = ws_new_row(w, ROW_FRICTION, 1 / R, m->dof_frictionloss[j]);
+    ws_push(w, j, 1.0);
+    w->aref[r] = -B * d->qvel[j];
+  }
+  stiffness_damping(m, m->limit_solref, m->limit_solimp, &K, &B);
+  for (int j = 0; j < nv; j++) {
+    if (!m->jnt_limited[j]) continue;
+    for (int side = 0; side < 2; side++) {
+      double sgn = side == 0 ? 1.0 : -1.0;
+      double dist = side == 0 ? d->qpos[j] - m->jnt_range[2 * j] : m->jnt_range[2 * j + 1] - d->qpos[j];
+      if (dist >= 0) continue;
+      double imp = impedance(m->limit_solimp, dist, 0);
+      double R = fmax(MINVAL, (1 - imp) * m->dof_invweight0[j] / imp);
+      int r = ws_new_row(w, ROW_INEQ, 1 / R, 0);
+      ws_push(w, j, sgn);
+      w->aref[r] = -B * sgn * d->qvel[j] - K * imp * dist;
+    }
+  }
+  for (int c = 0; c < d->ncon; c++) {
+    const po_contact *con = &d->contact[c];
+    int cls1 = m->geom_cls[con->geom1], cls2 = m->geom_cls[con->geom2];
+    int pc = (cls1 <= PP_CLS_BASE || cls2 <= PP_CLS_BASE) ? PP_PAIRCLS_PIANO : PP_PAIRCLS_HAND;
+    const double *solref = m->pair_solref[pc], *solimp = m->pair_solimp[pc];
+    double mu = m->pair_friction[pc], margin = m->pair_margin[pc];
+    int b1 = m->geom_body[con->geom1], b2 = m->geom_body[con->geom2];
+    /* columns: the dofs above either body; w->t1 marks them */
+    int ncol = 0, cols[128];
+    for (int side = 0; side < 2; side++)
+      for (int b = side ? b2 : b1; b > 0; b = m->body_parent[b])
+        for (int k = 0; k < m->body_dofnum[b]; k++) {
+          int j = m->body_dofadr[b] + k, seen = 0;
+          for (int q = 0; q < ncol; q++) if (cols[q] == j) { seen = 1; break; }
+          if (!seen && ncol < 128) cols[ncol++] = j;
+        }
+    /* ascending dof order, like a dense row read left to right */
+    for (int a = 1; a < ncol; a++) { int v = cols[a], b = a - 1; while (b >= 0 && cols[b] > v) { cols[b + 1] = cols[b]; b--; } cols[b + 1] = v; }
+    jac_point(m, d, b1, con->pos, w->j1);
+    jac_point(m, d, b2, con->pos, w->j2);
+    stiffness_damping(m, solref, solimp, &K, &B);
+    double imp = impedance(solimp, con->dist, margin);
+    double tran = m->body_invweight0[2 * b1] + m->body_invweight0[2 * b2];
+    double diag = tran + mu * mu * tran;
+    double R0 = fmax(MINVAL, (1 - imp) * diag / imp);
+    double mureg = mu * sqrt(1 / m->impratio);
+    double R = 2 * mureg * mureg * R0;
+    for (int k = 0; k < 4; k++) {
+      int r = ws_new_row(w, ROW_INEQ, 1 / R, 0);
+      const double *n = con->frame, *t = con->frame + 3 * (1 + k / 2);
+      double sg = (k % 2 == 0) ? mu : -mu;
+      for (int q = 0; q < ncol; q++) {
+        int j = cols[q];
+        double dn = 0, dt = 0;
+        for (int i = 0; i < 3; i++) {
+          double dj = w->j2[i * nv + j] - w->j1[i * nv + j];
+          dn += n[i] * dj; dt += t[i] * dj;
+        }
+        double v = dn + sg * dt;
+        if (v != 0) ws_push(w, j, v);
+      }
+      w->rowptr[r + 1] = w->nnz;
+      w->aref[r] = -B * ws_rowdot(w, r, d->qvel) - K * imp * (con->dist - margin);
+    }
+  }
+  w->rowptr[w->nrows] = w->nnz;
+  d->nefc = w->nrows;
+  /* C = T + isolated dofs that share a row with another dof */
+  w->nc = 0;
+  for (int j = 0; j < nv; j++) w->cidx[j] = -1;
+  for (int a = 0; a < w->nt; a++) { w->cidx[w->tlist[a]] = w->nc; w->clist[w->nc++] = w->tlist[a]; }
+  for (int r = 0; r < w->nrows; r++) {
+    if (w->rowptr[r + 1] - w->rowptr[r] < 2) continue;
+    for (int k = w->rowptr[r]; k < w->rowptr[r + 1]; k++) {
+      int j = w->col[k];
+      if (w->cidx[j] < 0) { w->cidx[j] = w->nc; w->clist[w->nc++] = j; }
+    }
+  }
+}
+
+static double ws_total_cost(const pp_model *m, const po_data *d, po_ws *w, const double *a, double *grad,
+                            double *force, double *curv) {
+  int nv = m->nv;
+  ws_matvecM(w, d, a, w->Ma);
+  double cost = 0;
+  for (int j = 0; j < nv; j++) cost += 0.5 * (w->Ma[j] - d->qfrc_smooth[j]) * (a[j] - d->qacc_smooth[j]);
+  if (grad) for (int j = 0; j < nv; j++) grad[j] = w->Ma[j] - d->qfrc_smooth[j];
+  for (int r = 0; r < w->nrows; r++) {
+    double x = ws_rowdot(w, r, a) - w->aref[r], c, f, cu;
+    ws_row_eval(w, r, x, &c, &f, &cu);
+    cost += c;
+    if (force) force[r] = f;
+    if (curv) curv[r] = cu;
+    if (grad) for (int k = w->rowptr[r]; k < w->rowptr[r + 1]; k++) grad[w->col[k]] -= w->val[k] * f;
+  }
+  return cost;
+}
+
+/* mj_solNewton, same iterates as solve_newton: the linear solve is dense over C, scalar elsewhere */
+static void ws_solve_newton(const pp_model *m, po_data *d, po_ws *w) {
+  int nv = m->nv, ne = w->nrows;
+  double *a = d->qacc;
+  double cw = ws_total_cost(m, d, w, d->qacc_warmstart, NULL, NULL, NULL);
+  double cs = ws_total_cost(m, d, w, d->qacc_smooth, NULL, NULL, NULL);
+  memcpy(a, cw < cs ? d->qacc_warmstart : d->qacc_smooth, sizeof(double) * nv);
+  d->solver_iter = 0;
+  if (ne == 0) { memcpy(a, d->qacc_smooth, sizeof(double) * nv); memset(d->qfrc_constraint, 0, sizeof(double) * nv); return; }
+  double *grad = w->grad, *p = w->p, *Mp = w->Mp, *H = w->H;
+  double scale = 1 / (m->meaninertia * (nv > 1 ? nv : 1));
+  double cost = ws_total_cost(m, d, w, a, grad, w->force, w->curv);
+  for (int iter = 0; iter < m->iterations; iter++) {
+    int nc = w->nc;
+    for (int j = 0; j < nv; j++) w->Hd[j] = d->qM[(size_t)j * nv + j];
+    for (int x = 0; x < nc; x++) {
+      const double *Mi = d->qM + (size_t)w->clist[x] * nv;
+      for (int y = 0; y < nc; y++) H[x * nc + y] = Mi[w->clist[y]];
+    }
+    for (int r = 0; r < ne; r++) {
+      double cu = w->curv[r];
+      if (cu == 0) continue;
+      int k0 = w->rowptr[r], k1 = w->rowptr[r + 1];
+      if (k1 - k0 == 1 && w->cidx[w->col[k0]] < 0) { w->Hd[w->col[k0]] += cu * w->val[k0] * w->val[k0]; continue; }
+      for (int ka = k0; ka < k1; ka++) {
+        double s = cu * w->val[ka];
+        double *Hx = H + (size_t)w->cidx[w->col[ka]] * nc;
+        for (int kb = k0; kb < k1; kb++) Hx[w->cidx[w->col[kb]]] += s * w->val[kb];
+      }
+    }
+    chol_factor(H, nc);
+    for (int x = 0; x < nc; x++) w->t1[x] = -grad[w->clist[x]];
+    chol_solve(H, nc, w->t1);
+    for (int j = 0; j < nv; j++) if (w->cidx[j] < 0) p[j] = -grad[j] / w->Hd[j];
+    for (int x = 0; x < nc; x++) p[w->clist[x]] = w->t1[x];
+    ws_matvecM(w, d, p, Mp);
+    double g1 = 0, g2 = 0, gauss1 = 0;
+    ws_matvecM(w, d, a, w->Ma);
+    for (int j = 0; j < nv; j++) { g1 += grad[j] * p[j]; g2 += p[j] * Mp[j]; gauss1 += (w->Ma[j] - d->qfrc_smooth[j]) * p[j]; }
+    for (int r = 0; r < ne; r++) { w->jar[r] = ws_rowdot(w, r, a) - w->aref[r]; w->jp[r] = ws_rowdot(w, r, p); }
+    double alpha = 0, lo = 0, hi = -1, d0 = g1;
+    for (int ls = 0; ls < m->ls_iterations; ls++) {
+      double dphi = gauss1 + alpha * g2, ddphi = g2;
+      for (int r = 0; r < ne; r++) {
+        double c, f, cu;
+        ws_row_eval(w, r, w->jar[r] + alpha * w->jp[r], &c, &f, &cu);
+        dphi -= f * w->jp[r];
+        ddphi += cu * w->jp[r] * w->jp[r];
+      }
+      if (fabs(dphi) <= 1e-14 * fabs(d0) || ddphi <= 0) break;
+      if (dphi < 0) lo = alpha; else hi = alpha;
+      double next = alpha - dphi / ddphi;
+      if (hi >= 0 && (next <= lo || next >= hi)) next = 0.5 * (lo + hi);
+      if (next == alpha) break;
+      alpha = next;
+    }
+    for (int j = 0; j < nv; j++) a[j] += alpha * p[j];
+    double newcost = ws_total_cost(m, d, w, a, grad, w->force, w->curv);
+    double improvement = scale * (cost - newcost), gnorm = 0;
+    cost = newcost;
+    for (int j = 0; j < nv; j++) gnorm += grad[j] * grad[j];
+    gnorm = scale * sqrt(gnorm);
+    d->solver_iter = iter + 1;
+    if (improvement < m->tolerance || gnorm < m->tolerance) break;
+  }
+  d->solver_cost = cost;
+  memset(d->qfrc_constraint, 0, sizeof(double) * nv);
+  for (int r = 0; r < ne; r++)
+    for (int k = w->rowptr[r]; k < w->rowptr[r + 1]; k++) d->qfrc_constraint[w->col[k]] += w->val[k] * w->force[r];
+}
+
+
+void po_step_sparse(const pp_model *m, po_data *d) {
+  int nv = m->nv;
+  po_ws *w = ws_get(m, d);
+  /* mj_fwdPosition */
+  kinematics(m, d);
+  crb_buf(m, d, w->Ic);
+  collision(m, d);
+  ws_make_constraint(m, d, w);
+  /* mj_fwdVelocity, mj_fwdActuation */
+  rne_bias_buf(m, d, w->vel, w->acc, w->frc);
+  passive_buf(m, d, w->j1);
+  actuation(m, d);
+  /* mj_fwdAcceleration */
+  for (int j = 0; j < nv; j++) {
+    d->qfrc_smooth[j] = d->qfrc_passive[j] - d->qfrc_bias[j] + d->qfrc_actuator[j] + d->qfrc_applied[j];
+    d->qacc_smooth[j] = d->qfrc_smooth[j];
+  }
+  ws_solveM(w, d, NULL, d->qacc_smooth);
+  /* mj_fwdConstraint */
+  ws_solve_newton(m, d, w);
+  /* mj_Euler with implicit joint damping */
+  double h = m->timestep;
+  for (int j = 0; j < nv; j++) { w->t2[j] = h * m->dof_damping[j]; w->a[j] = d->qfrc_smooth[j] + d->qfrc_constraint[j]; }
+  ws_solveM(w, d, w->t2, w->a);
+  for (int j = 0; j < nv; j++) {
+    d->qvel[j] += h * w->a[j];
+    d->qpos[j] += h * d->qvel[j];
+    d->qacc_warmstart[j] = d->qacc[j];
+  }
+  actuator_velocity(m, d);
+}
+
+void po_step_batch_sparse(const pp_model *m, po_data **d, int nenv, int nsub) {
+#ifdef _OPENMP
+  if (po_threads > 0) omp_set_num_threads(po_threads);
+#endif
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int i = 0; i < nenv; i++)
+    for (int s = 0; s < nsub; s++) po_step_sparse(m, d[i]);
 }

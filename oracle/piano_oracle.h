@@ -56,6 +56,7 @@ typedef struct po_data {
   double *qacc, *qfrc_constraint;
   int solver_iter;
   double solver_cost;
+  void *ws; /* workspace of po_step_sparse (allocated at its first call, freed by po_data_free) */
 } po_data;
 
 po_data *po_data_create(const pp_model *m);
@@ -65,8 +66,15 @@ void po_reset(const pp_model *m, po_data *d);
 void po_forward_position(const pp_model *m, po_data *d, int with_collision);
 /* one full mj_step: forward dynamics at (qpos,qvel,ctrl), constraint solve, Euler */
 void po_step(const pp_model *m, po_data *d);
+/* The same mj_step with the structure of THIS model exploited, as an engine written for speed would (MuJoCo's own
+ * data structures are sparse): constraint rows as sparse lists, the Newton Hessian and the mass matrix as one dense
+ * block over the coupled dofs (kinematic trees with more than one dof + the 1-dof joints a contact touches) plus
+ * scalars for every other 1-dof joint, no allocation inside the step. Same Newton iterates as po_step, so the
+ * results agree to rounding (tests/test_scene_and_oracle.py); it exists to be the honest timed CPU baseline. */
+void po_step_sparse(const pp_model *m, po_data *d);
 /* n env-independent steps over a batch, OpenMP over envs; for the CPU baseline */
 void po_step_batch(const pp_model *m, po_data **d, int nenv, int nsub);
+void po_step_batch_sparse(const pp_model *m, po_data **d, int nenv, int nsub);
 void po_set_num_threads(int n); /* threads used by po_step_batch (0 = OpenMP default) */
 
 #ifdef __cplusplus
