@@ -49,6 +49,8 @@ _SIGNATURES = {
     "pp_set_state": (c_int, [c_void_p] * 7),
     "pp_set_qfrc_applied": (c_int, [c_void_p] * 3),
     "pp_set_hand_offsets": (c_int, [c_void_p] * 3),
+    "pp_set_song_bank": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int]),
+    "pp_set_song_ids": (c_int, [c_void_p] * 3),
     "pp_set_substep_activations": (c_int, [c_void_p] * 2),
     "pp_get_metrics": (c_int, [c_void_p] * 4),
     "pp_get_diag": (c_int, [c_void_p] * 8),

@@ -54,8 +54,9 @@ struct pp_env {
   int sched_mode = PP_SCHED_AUTO, block_envs = 2, tune_calls = 0;
   bool sort_work = false, tuned = false;
   int* order = nullptr;  // [N]
-  int* queue = nullptr;  // [PP_MAX_HOST_CHUNKS] env queues of the persistent launch shape (one per concurrently launched piece)
-  int num_sms = 148;
+  // song bank (pp_set_song_bank): goal / pairs then hold n_songs songs back to back
+  int n_songs = 0, bank_pmax = 0;
+  int *song_id = nullptr, *song_id_pending = nullptr, *song_off = nullptr, *song_T = nullptr;
   uint4* substep_act = nullptr;  // caller-owned [N, n_substeps] (pp_set_substep_activations) or null
   cudaEvent_t tune_ev[2 * PP_TUNE_STEPS] = {};
   // host-buffer path
@@ -330,8 +331,7 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(dalloc(&e->site_xpos, (size_t)N * 3 * PP_NSITE));
   CUDA_OK(dalloc(&e->activation, (size_t)N * 88)); CUDA_OK(dalloc(&e->counters, (size_t)N * 8));
   CUDA_OK(dalloc(&e->order, (size_t)N));
-  CUDA_OK(dalloc(&e->queue, (size_t)PP_MAX_HOST_CHUNKS));
-  CUDA_OK(cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
+  CUDA_OK(dalloc(&e->song_id, (size_t)N)); CUDA_OK(dalloc(&e->song_id_pending, (size_t)N));
   CUDA_OK(dalloc(&e->act_min_d, e->action_dim)); CUDA_OK(dalloc(&e->act_max_d, e->action_dim));
   CUDA_OK(cudaMemcpy(e->act_min_d, e->act_min.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
   CUDA_OK(cudaMemcpy(e->act_max_d, e->act_max.data(), e->action_dim * 4, cudaMemcpyHostToDevice));
@@ -367,7 +367,8 @@ extern "C" int pp_destroy(pp_env* e) {
                  e->needs_reset, e->qacc, e->act_force, e->act_vel, e->site_xpos, e->activation, e->counters,
                  e->act_min_d, e->act_max_d, e->d_actions, e->d_obs, e->d_reward, e->d_terms, e->d_discount,
                  e->d_done, e->d_mask, e->hand_off, e->hand_off_pending, e->eval_sum, e->eval_episode,
-                 e->eval_steps, e->eval_count, e->stick_bits, e->order, e->queue};
+                 e->eval_steps, e->eval_count, e->stick_bits, e->order, e->song_id, e->song_id_pending,
+                 e->song_off, e->song_T};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -443,6 +444,10 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     memset(&A, 0, sizeof(A));
     A.dm = e->dm; A.num_envs = c.num_envs; A.mode = mode; A.n_substeps = c.n_substeps;
     A.n_frames = c.n_frames; A.lookahead = c.n_steps_lookahead; A.obs_dim = e->obs_dim; A.pmax = c.pmax;
+    if (e->n_songs > 0) {
+      A.pmax = e->bank_pmax; A.n_songs = e->n_songs; A.song_id = e->song_id; A.song_id_pending = e->song_id_pending;
+      A.song_off = e->song_off; A.song_T = e->song_T;
+    }
     A.canonical = c.canonical_actions; A.has_fingering = c.has_fingering;
     A.disable_forearm_reward = c.disable_forearm_reward;
     A.wrong_press_termination = c.wrong_press_termination; A.auto_reset = c.auto_reset;
@@ -669,6 +674,50 @@ extern "C" int pp_set_substep_activations(pp_env* e, uint32_t* buf_dev) {
     return fail(PP_ERR_UNSUPPORTED, "per-substep activations are recorded by the two-hands step only");
   if (buf_dev && (reinterpret_cast<uintptr_t>(buf_dev) & 15) != 0) return fail(PP_ERR_INVALID, "buffer must be 16-byte aligned");
   e->substep_act = reinterpret_cast<uint4*>(buf_dev);
+  return PP_OK;
+}
+
+// MIDI augmentations (reference suite/variations.py, piano_with_shadow_hands.py:151-165): n_songs songs resident on
+// the device, every env plays the one whose id it was handed before its reset.
+extern "C" int pp_set_song_bank(pp_env* e, const uint8_t* goal, const int16_t* pairs, const int32_t* song_frames,
+                                int n_songs, int pmax) {
+  if (!e || !goal || !song_frames) return fail(PP_ERR_INVALID, "null argument");
+  if (e->cfg.task != PP_TASK_PIANO_WITH_SHADOW_HANDS) return fail(PP_ERR_UNSUPPORTED, "song banks: two-hands task only");
+  if (n_songs < 1 || n_songs > 65536) return fail(PP_ERR_INVALID, "n_songs %d", n_songs);
+  if (e->cfg.has_fingering && (!pairs || pmax < 1)) return fail(PP_ERR_INVALID, "a fingered task needs the pairs of every song");
+  std::vector<int> off(n_songs), T(n_songs);
+  size_t total = 0;
+  for (int k = 0; k < n_songs; k++) {
+    if (song_frames[k] < 1) return fail(PP_ERR_INVALID, "song %d has %d frames", k, song_frames[k]);
+    off[k] = (int)total; T[k] = song_frames[k]; total += (size_t)song_frames[k];
+  }
+  CUDA_OK(cudaSetDevice(e->cfg.device));
+  CUDA_OK(cudaDeviceSynchronize());  // no step may still be reading the old tables
+  uint8_t* g = nullptr; int16_t* p = nullptr; int *o = nullptr, *t = nullptr;
+  CUDA_OK(dalloc(&g, total * 89));
+  CUDA_OK(cudaMemcpy(g, goal, total * 89, cudaMemcpyHostToDevice));
+  if (pairs && pmax > 0) {
+    CUDA_OK(dalloc(&p, total * pmax * 2));
+    CUDA_OK(cudaMemcpy(p, pairs, total * pmax * 2 * sizeof(int16_t), cudaMemcpyHostToDevice));
+  }
+  CUDA_OK(dalloc(&o, (size_t)n_songs)); CUDA_OK(dalloc(&t, (size_t)n_songs));
+  CUDA_OK(cudaMemcpy(o, off.data(), n_songs * sizeof(int), cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy(t, T.data(), n_songs * sizeof(int), cudaMemcpyHostToDevice));
+  cudaFree(e->goal); cudaFree(e->pairs); cudaFree(e->song_off); cudaFree(e->song_T);
+  e->goal = g; e->pairs = p; e->song_off = o; e->song_T = t;
+  e->n_songs = n_songs; e->bank_pmax = pmax > 0 ? pmax : 1;
+  // envs in the middle of an episode fall back to song 0 of the new bank until their next reset; the caller
+  // resets after a bank change (suite/environment.py does)
+  CUDA_OK(cudaMemset(e->song_id, 0, (size_t)e->cfg.num_envs * sizeof(int)));
+  CUDA_OK(cudaMemset(e->song_id_pending, 0, (size_t)e->cfg.num_envs * sizeof(int)));
+  return PP_OK;
+}
+
+extern "C" int pp_set_song_ids(pp_env* e, const int32_t* ids_dev, void* stream) {
+  if (!e || !ids_dev) return fail(PP_ERR_INVALID, "null argument");
+  if (e->n_songs < 1) return fail(PP_ERR_INVALID, "no song bank: call pp_set_song_bank first");
+  cudaStream_t s = (cudaStream_t)stream;
+  COPY_IF(e->song_id_pending, ids_dev, (size_t)e->cfg.num_envs * sizeof(int));
   return PP_OK;
 }
 

@@ -54,6 +54,12 @@ struct HandsArgs {
   const int* order;  // [N] launch slot -> env (null: identity); envs of similar expected work share a block
   uint4* substep_act;  // [N, n_substeps] or null: key activation bits 0-31 / 32-63 / 64-87 and the pedal after every substep
   EvalAccum eval;  // musical metrics accumulators
+  // song bank (MIDI augmentations, suite/variations.py): goal / pairs hold n_songs songs back to back; null = one song
+  int* song_id;                // [N] song each env is playing
+  const int* song_id_pending;  // [N] song an env takes at its next reset
+  const int* song_off;         // [n_songs] first frame of the song inside goal / pairs
+  const int* song_T;           // [n_songs] frames of the song
+  int n_songs;
 };
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);

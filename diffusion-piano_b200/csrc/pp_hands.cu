@@ -551,7 +551,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   const Options& o = dm.opt;
   const HandTables& ht = dm.hand;
   const KeyTables& kt = dm.key;
-  const int T = A.n_frames, Lk = A.lookahead, OD = A.obs_dim;
+  const int Lk = A.lookahead, OD = A.obs_dim;
   LaneCtx L; L.lane = lane; L.dof = lane < PP_HD; L.ni = node_info(L.dof ? lane : 25);
   const int l = L.dof ? lane : 25;  // safe table index
 
@@ -573,6 +573,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   const size_t sbase = (size_t)env * PP_NV;
   const int mc_ = A.max_contacts & 255;
   const bool dbg_all_lr = (A.max_contacts & 256) != 0;  // test hook: every contact through the low-rank path
+  const bool dbg_dense = (A.max_contacts & 512) != 0;   // test hook: every substep through the dense factorisation
   const int cap = mc_ > 0 && mc_ < NC ? mc_ : NC;
   const int ngh = ht.ngeom >> 1;
   // _randomize_initial_hand_positions (piano_with_shadow_hands.py:491-499): one y shift of both hands per episode
@@ -935,7 +936,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         my_lr = lane < ncon && my_slot != -2 && (kind == 1 || dbg_all_lr || (wants && owner != my_front));
         lrb = __ballot_sync(FULL, my_lr);
         nlr = __popc(lrb);
-        dense_mode = nlr > LRC;  // too many cross-finger contacts for the low-rank path
+        dense_mode = nlr > LRC || dbg_dense;  // too many cross-finger contacts for the low-rank path
       }
       __syncwarp();
       if (lane < ncon && my_slot != -2) {
@@ -1795,9 +1796,18 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
     normalized[i] = 0.f; active[i] = false;
     if (k < PP_NKEY) pp_key_state(qk[i], kt.hi[k], normalized[i], active[i]);
   }
+  // the env's song (looked up here, after the substeps: nothing before needs it): one of the bank's (MIDI augmentations: an env takes its pending song at a reset), or the only one
+  int T = A.n_frames, song_off = 0;  // frames of the env's song, its first frame inside A.goal / A.pairs
+  if (A.song_id) {
+    int sid = do_reset ? A.song_id_pending[env] : A.song_id[env];
+    sid = min(max(sid, 0), A.n_songs - 1);
+    if (do_reset && lane == 0) A.song_id[env] = sid;
+    song_off = A.song_off[sid];
+    T = A.song_T[sid];
+  }
   const bool sustain_on = sustain >= 0.5f;
   const int t_cur = t_idx > 0 ? t_idx - 1 : 0;  // frame just played (goal_current)
-  const uint8_t* goal_cur = A.goal + (size_t)t_cur * 89;
+  const uint8_t* goal_cur = A.goal + (size_t)(song_off + t_cur) * 89;
   // key_press reward (piano_with_shadow_hands.py:279-298)
   float kp_sum = 0.f; int kp_on = 0; bool wrong = false;
 #pragma unroll
@@ -1819,7 +1829,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
     for (int p0 = 0; p0 < A.pmax; p0 += 32) {
       int key = -1, finger = 0;
       if (p0 + lane < A.pmax && !do_reset) {
-        const int16_t* pr = A.pairs + ((size_t)t_cur * A.pmax + p0 + lane) * 2;
+        const int16_t* pr = A.pairs + ((size_t)(song_off + t_cur) * A.pmax + p0 + lane) * 2;
         key = pr[0]; finger = pr[1];
       }
       const bool has = key >= 0;
@@ -1919,14 +1929,14 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
     const int ng = (Lk + 1) * 89;
     for (int i = lane; i < ng; i += 32) {
       const int f = t0 + i / 89;
-      obs[i] = f < T ? (float)A.goal[(size_t)f * 89 + (i % 89)] : 0.f;
+      obs[i] = f < T ? (float)A.goal[(size_t)(song_off + f) * 89 + (i % 89)] : 0.f;
     }
     int off = ng;
     if (A.has_fingering) {
       // (2,5) flags of the fingers used in frame t0 (:391-412)
       unsigned used = 0u;
       for (int p = 0; p < A.pmax; p++) {
-        const int16_t* pr = A.pairs + ((size_t)t0 * A.pmax + p) * 2;
+        const int16_t* pr = A.pairs + ((size_t)(song_off + t0) * A.pmax + p) * 2;
         if (pr[0] >= 0) {
           const int f = pr[1];
           const int slot = f < 5 ? (f < 0 ? f + 5 : f) : 5 + min(f - 5, 4);  // python negative index wraps

@@ -126,6 +126,25 @@ class BatchedPianoEngine:
         """y shift [N] of both hands that each env takes at its next reset (None: zero again)."""
         _lib.check(self.lib.pp_set_hand_offsets(self._h, _ptr(y_off), stream))
 
+    def set_song_bank(self, songs) -> None:
+        """songs: sequence of `SongTables` (MIDI augmentations): uploaded back to back; every env plays the one
+        whose id `set_song_ids` hands it before its reset. Synchronises the device; reset afterwards."""
+        pmax = max(t.pmax for t in songs)
+        goal = np.ascontiguousarray(np.concatenate([t.goal for t in songs], 0), np.uint8)
+        pairs = np.full((goal.shape[0], pmax, 2), -1, np.int16)
+        off = 0
+        for t in songs:
+            pairs[off:off + t.n_frames, :t.pmax] = t.pairs
+            off += t.n_frames
+        frames = np.ascontiguousarray([t.n_frames for t in songs], np.int32)
+        self._bank = (goal, pairs, frames)
+        _lib.check(self.lib.pp_set_song_bank(self._h, goal.ctypes.data, pairs.ctypes.data, frames.ctypes.data,
+                                             len(songs), pmax))
+
+    def set_song_ids(self, ids, stream: int = 0) -> None:
+        """ids: int32 CUDA tensor [N] - the bank entry each env takes at its next reset."""
+        _lib.check(self.lib.pp_set_song_ids(self._h, _ptr(ids), stream))
+
     def set_substep_activations(self, buf):
         """uint32 CUDA tensor [N, n_substeps, 4] that every later step fills with the key / pedal activation bits
         after each substep (None: stop). The caller keeps the tensor alive."""

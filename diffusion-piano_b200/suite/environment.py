@@ -20,7 +20,8 @@ from . import specs
 
 class BatchedEnvironment:
     def __init__(self, task, num_envs: int, device: int = 0, canonical_actions: bool = False,
-                 auto_reset: bool = True, max_contacts: int = 0, random_state=None, schedule: str = "auto"):
+                 auto_reset: bool = True, max_contacts: int = 0, random_state=None, schedule: str = "auto",
+                 augmentation_bank_size: int = 64):
         import torch  # device memory + streams only
 
         self._torch = torch
@@ -80,7 +81,42 @@ class BatchedEnvironment:
             self._h_offsets = pinned((n,), torch.float32)
             self._d_offsets = torch.zeros(n, dtype=torch.float32, device=self.device)
 
+        # MIDI augmentations (piano_with_shadow_hands.py:151-165, suite/variations.py): a bank of K augmented songs
+        # is drawn and uploaded at every explicit reset; every env takes one of them (an env that resets itself
+        # between two explicit resets draws again from the same bank)
+        self._augment = bool(getattr(task, "_augmentations", None))
+        if self._augment:
+            if not hasattr(self, "random_state"):
+                self.random_state = (random_state if isinstance(random_state, np.random.RandomState)
+                                     else np.random.RandomState(random_state))
+            self._bank_size = max(1, min(int(augmentation_bank_size), n))
+            self._d_song_ids = torch.zeros(n, dtype=torch.int32, device=self.device)
+            self.songs = []  # the bank in force: [(midi, notes, sustains, SongTables)]
+            self.song_ids = np.zeros(n, np.int32)  # bank entry of every env's current episode
+
     _POSITION_OFFSET = 0.05
+
+    def _draw_songs(self, new_bank: bool):
+        """new_bank: draw K fresh augmented songs (explicit reset). Always: hand every env the bank entry it takes
+        at its next reset - env i plays entry i of a fresh bank when the bank is as large as the batch (the
+        reference's one independent draw per env and episode), a uniformly drawn entry otherwise."""
+        if not self._augment:
+            return
+        stream = self._torch.cuda.current_stream(self.device)
+        if new_bank:
+            self.songs = [self.task.draw_song(self.random_state) for _ in range(self._bank_size)]
+            stream.synchronize()
+            self.engine.set_song_bank([s[3] for s in self.songs])
+        if new_bank and self._bank_size == self.num_envs:
+            ids = np.arange(self.num_envs, dtype=np.int32)
+        else:
+            ids = self.random_state.randint(0, self._bank_size, self.num_envs).astype(np.int32)
+        self._pending_song_ids = ids
+        self._d_song_ids.copy_(self._torch.from_numpy(ids))
+        self.engine.set_song_ids(self._d_song_ids, stream.cuda_stream)
+        stream.synchronize()
+        if new_bank:
+            self.song_ids = ids.copy()
 
     def _draw_hand_offsets(self):
         """Offsets the envs take at their NEXT reset; redrawn before every call that can reset an env."""
@@ -108,6 +144,7 @@ class BatchedEnvironment:
     # ---- device API: everything stays in HBM; returned tensors are reused between calls
     def reset_device(self, mask=None):
         self._draw_hand_offsets()
+        self._draw_songs(new_bank=mask is None)
         stream = self._torch.cuda.current_stream(self.device).cuda_stream
         self.engine.reset(obs=self._obs, mask=mask, stream=stream)
         return self._device_obs()
@@ -137,6 +174,7 @@ class BatchedEnvironment:
 
     def reset(self) -> Dict[str, np.ndarray]:
         self._draw_hand_offsets()
+        self._draw_songs(new_bank=True)
         self.engine.reset_host(obs=self._h_obs)
         for i, m in getattr(self, "_midi_modules", {}).items():
             m.initialize_episode()
@@ -288,7 +326,11 @@ class Environment:
     def reset(self) -> specs.TimeStep:
         self._reset_next_step = False
         self._t = 0
-        return specs.TimeStep(specs.StepType.FIRST, None, None, self._obs(self._b.reset()))
+        obs = self._b.reset()
+        if self._b._augment:  # the task object shows the episode's own song, as `_maybe_change_midi` leaves it
+            midi, notes, sustains, tables = self._b.songs[int(self._b.song_ids[0])]
+            self.task._midi, self.task._notes, self.task._sustains, self.task.song = midi, notes, sustains, tables
+        return specs.TimeStep(specs.StepType.FIRST, None, None, self._obs(obs))
 
     def _cache_current(self) -> None:
         """What after_step caches for the reward of the frame just played (piano_with_shadow_hands.py:192-199):

@@ -36,8 +36,7 @@ class _PianoTaskBase:
 
     def __init__(self, midi, n_steps_lookahead, trim_silence, physics_timestep, control_timestep,
                  initial_buffer_time=0.0, augmentations=None):
-        if augmentations is not None:
-            raise NotImplementedError("MIDI augmentations are outside the hot-path scope (SURVEY §2)")
+        self._augmentations = list(augmentations) if augmentations is not None else None
         if trim_silence:
             midi = midi.trim_silence()
         self._midi = midi
@@ -58,6 +57,17 @@ class _PianoTaskBase:
         self._notes = traj.notes
         self._sustains = traj.sustains
         self.song = SongTables.from_trajectory(traj)
+
+    def draw_song(self, random_state: np.random.RandomState):
+        """`_maybe_change_midi` + `_reset_trajectory` of the reference (piano_with_shadow_hands.py:151-165) for ONE
+        episode: the augmentations applied in order to the initial MIDI -> (midi, notes, sustains, SongTables).
+        The batched environment draws a bank of these per reset and assigns one to every env."""
+        midi = self._initial_midi
+        for var in self._augmentations or ():
+            midi = var(initial_value=midi, random_state=random_state)
+        traj = NoteTrajectory.from_midi(midi, self.control_timestep)
+        traj.add_initial_buffer_time(self._initial_buffer_time)
+        return midi, traj.notes, traj.sustains, SongTables.from_trajectory(traj)
 
     @property
     def midi(self):

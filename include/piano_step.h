@@ -123,6 +123,16 @@ int pp_get_metrics(pp_env *env, float *episode_metrics_dev, int32_t *episode_cou
  * uniform(-0.05, 0.05)); it stays in force until the reset after. NULL: zero shift from the next reset on. */
 int pp_set_hand_offsets(pp_env *env, const float *y_off_dev, void *stream);
 
+/* MIDI augmentations at episode start (robopianist/suite/variations.py:27-184 applied by
+ * piano_with_shadow_hands.py:151-165 `_maybe_change_midi` / `_reset_trajectory`): n_songs note trajectories resident
+ * on the device, back to back. goal [sum frames, 89] u8 and pairs [sum frames, pmax, 2] i16 (NULL for an unfingered
+ * task) are HOST pointers, song_frames [n_songs] the length of each song; the call synchronises the device and
+ * replaces the handle's tables (reset afterwards). pp_set_song_ids: ids_dev [N] int32 (device) = the song each env
+ * takes at its NEXT reset (explicit or automatic); ids are clamped to the bank. Two-hands task only. */
+int pp_set_song_bank(pp_env *env, const uint8_t *goal, const int16_t *pairs, const int32_t *song_frames,
+                     int n_songs, int pmax);
+int pp_set_song_ids(pp_env *env, const int32_t *ids_dev, void *stream);
+
 /* Piano.after_substep -> MidiModule.after_substep (robopianist/models/piano/piano.py:154-162,
  * midi_module.py:47-98): the reference turns the key / pedal activations after EVERY physics substep into MIDI
  * note-on / note-off / sustain events. buf_dev: caller-owned uint32 [N, n_substeps, 4], 16-byte aligned, written

@@ -31,7 +31,7 @@ class _ParityLog:
     """Per-substep qacc / qpos errors of the CUDA step against the oracle, with the exception bookkeeping."""
 
     def __init__(self):
-        self.rel, self.qpos, self.impact, self.stiff, self.row_mismatch = [], [], [], [], 0
+        self.rel, self.qpos, self.impact, self.stiff, self.rows_equal, self.row_mismatch = [], [], [], [], [], 0
         self._prev = None
 
     def add(self, s, ctrl_jump=False):
@@ -49,22 +49,27 @@ class _ParityLog:
         self.qpos.append(float(np.abs(s.qpos[0].cpu().numpy() - p.qpos).max()))
         self.impact.append(bool(grazing or changed or ctrl_jump or rows_differ))
         self.stiff.append(int(s.cnt[0, 0]) >= 3)
+        self.rows_equal.append(not rows_differ)
         return rel
 
     def check(self, name, max_over_frac):
         rel, imp, stiff = np.array(self.rel), np.array(self.impact), np.array(self.stiff)
+        same, qpos = np.array(self.rows_equal), np.array(self.qpos)
         over = rel > QACC_REL
         hist = np.histogram(np.log10(np.maximum(rel, 1e-9)), bins=[-9, -7, -6, -5, -4, -3, -2, 0])[0]
         print(f"{name}: {len(rel)} substeps; qacc rel median {np.median(rel):.1e} max {rel.max():.1e}; "
               f"log10 histogram (<-7,-6,-5,-4,-3,-2,>) {hist.tolist()}; over {QACC_REL:g}: {int(over.sum())} "
               f"= {int((over & imp).sum())} impact + {int((over & ~imp & stiff).sum())} stiff + "
               f"{int((over & ~imp & ~stiff).sum())} other; row-count mismatches {self.row_mismatch}; "
-              f"qpos abs max {max(self.qpos):.1e}")
+              f"qpos abs max {qpos[same].max():.1e} (same rows), {qpos.max():.1e} (all)")
         assert not (over & ~imp & ~stiff).any(), "a plain substep exceeds the north_star qacc tolerance"
-        assert (rel[~imp] <= QACC_REL_STIFF).all() and rel.max() <= QACC_REL_IMPACT
+        # substeps in which the two arithmetics disagree about a grazing contact solve DIFFERENT problems (a contact
+        # that arrives with velocity switches on with a finite force): counted and limited, not bounded in size
+        assert (rel[~imp] <= QACC_REL_STIFF).all() and rel[same].max() <= QACC_REL_IMPACT
+        assert self.row_mismatch <= 0.02 * len(rel) + 1
         assert over.sum() <= max_over_frac * len(rel), (int(over.sum()), len(rel))
         assert np.median(rel) <= QACC_REL
-        assert max(self.qpos) <= QPOS_ABS
+        assert qpos[same].max() <= QPOS_ABS
 
 
 def _task(**kw):
@@ -77,12 +82,13 @@ def _task(**kw):
 class _Synced:
     """GPU batch of n envs whose env 0 is re-synchronised to the oracle before every step."""
 
-    def __init__(self, task, n=2):
+    def __init__(self, task, n=2, max_contacts=0):
         import torch
         from diffusion_piano_b200 import suite
         from oracle.task_oracle import PianoWithShadowHandsOracle
         self.torch = torch
-        self.env = suite.BatchedEnvironment(task, n, canonical_actions=False, auto_reset=False)
+        self.env = suite.BatchedEnvironment(task, n, canonical_actions=False, auto_reset=False,
+                                            max_contacts=max_contacts)
         self.ora = PianoWithShadowHandsOracle(task)
         self.env.reset(); self.ora.reset()
         z = lambda *s, dt=torch.float32: torch.zeros(s, device="cuda", dtype=dt)
@@ -153,6 +159,27 @@ def test_contact_press_parity_and_activation(cuda_lib):
         np.testing.assert_allclose(rew[0], r_o, atol=2e-5)
     assert seen_contacts >= 2 and pressed > 1e-3
     log.check("finger press", max_over_frac=0.05)
+    s.close()
+
+
+def test_dense_fallback_solver_parity(cuda_lib):
+    """The dense 52x52 factorisation (taken when more than 8 contacts couple two finger chains) forced for every
+    substep through the kernel's test hook (max_contacts bit 512): same parity bar as the multifrontal path,
+    on the finger press and on random control jumps."""
+    s = _Synced(_task(control_timestep=0.005), max_contacts=512)
+    names = s.ora.model.names["actuator"]
+    a = np.zeros(45)
+    a[names.index("rh_shadow_hand/rh_A_WRJ1")] = 0.45; a[names.index("rh_shadow_hand/rh_A_FFJ3")] = 1.2
+    a[22 + names.index("rh_shadow_hand/rh_A_WRJ1")] = 0.45; a[22 + names.index("rh_shadow_hand/rh_A_MFJ3")] = 1.2
+    log = _ParityLog()
+    rng = np.random.RandomState(3)
+    for t in range(200):
+        if t >= 120 and t % 10 == 0:
+            a = _spec_random(s.ora, rng)
+        s.step(a)
+        log.add(s, ctrl_jump=t == 0 or (t >= 120 and t % 10 == 0))
+        assert int(s.cnt[0, 6]) == 1  # this substep did go through the dense solver
+    log.check("dense fallback forced", max_over_frac=0.05)
     s.close()
 
 
