@@ -76,7 +76,9 @@ def train(env, cfg: TrainConfig, process_group=None, agent: Optional[PPOAgent] =
             # With several ranks the decision is global (every rank evaluates `may_be_done` alike, so all of them
             # enter the all-reduce together): a rank leaving alone would strand the others in update's collectives.
             # `step % frames == 0` also catches envs that ended early, auto-reset and are done again later.
-            may_be_done = step % frames == 0 or bool(getattr(env.task, "_wrong_press_termination", False))
+            # (with MIDI augmentations every env has its own episode length: look every step)
+            may_be_done = (step % frames == 0 or bool(getattr(env.task, "_wrong_press_termination", False))
+                           or bool(getattr(env, "_augment", False)))
             if may_be_done:
                 done_here = bool(dones.all())
                 if process_group is not None:
