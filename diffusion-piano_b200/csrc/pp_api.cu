@@ -278,7 +278,7 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   if (cfg->n_steps_lookahead < 0) return fail(PP_ERR_INVALID, "n_steps_lookahead must be >= 0");
   const bool hands = cfg->task == PP_TASK_PIANO_WITH_SHADOW_HANDS;
   if (hands != (model->has_hands != 0)) return fail(PP_ERR_INVALID, "task / model mismatch");
-  if (hands && cfg->has_fingering && !cfg->pairs) return fail(PP_ERR_INVALID, "pairs table required");
+  if (hands && cfg->has_fingering == 1 && !cfg->pairs) return fail(PP_ERR_INVALID, "pairs table required");
   int ndev = 0;
   cudaError_t ce = cudaGetDeviceCount(&ndev);
   if (ce != cudaSuccess || ndev == 0)
@@ -294,7 +294,7 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   const int N = cfg->num_envs, L = cfg->n_steps_lookahead;
   if (hands) {
     e->action_dim = 45;
-    e->obs_dim = (L + 1) * 89 + (cfg->has_fingering ? 10 : 0) + 88 + 1 + 26 + 26;
+    e->obs_dim = (L + 1) * 89 + (cfg->has_fingering == 1 ? 10 : 0) + 88 + 1 + 26 + 26;
     e->act_min.resize(45); e->act_max.resize(45);
     for (int i = 0; i < 44; i++) {
       e->act_min[i] = (float)model->act_ctrlrange[2 * i];
@@ -684,7 +684,7 @@ extern "C" int pp_set_song_bank(pp_env* e, const uint8_t* goal, const int16_t* p
   if (!e || !goal || !song_frames) return fail(PP_ERR_INVALID, "null argument");
   if (e->cfg.task != PP_TASK_PIANO_WITH_SHADOW_HANDS) return fail(PP_ERR_UNSUPPORTED, "song banks: two-hands task only");
   if (n_songs < 1 || n_songs > 65536) return fail(PP_ERR_INVALID, "n_songs %d", n_songs);
-  if (e->cfg.has_fingering && (!pairs || pmax < 1)) return fail(PP_ERR_INVALID, "a fingered task needs the pairs of every song");
+  if (e->cfg.has_fingering == 1 && (!pairs || pmax < 1)) return fail(PP_ERR_INVALID, "a fingered task needs the pairs of every song");
   std::vector<int> off(n_songs), T(n_songs);
   size_t total = 0;
   for (int k = 0; k < n_songs; k++) {

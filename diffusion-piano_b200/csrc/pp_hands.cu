@@ -1824,7 +1824,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   float energy1 = wsum(fabsf(act_force[1]) * fabsf(act_vel[1]));
   // fingering reward (:300-331): fingertip site to key surface point, world offsets
   float fing = 0.f;
-  if (A.has_fingering) {
+  if (A.has_fingering == 1) {
     float tot = 0.f; int cnt = 0;
     for (int p0 = 0; p0 < A.pmax; p0 += 32) {
       int key = -1, finger = 0;
@@ -1855,7 +1855,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       cnt += __popc(__ballot_sync(FULL, has));
     }
     fing = cnt > 0 ? tot / (float)cnt : 0.f;
-  } else {
+  } else if (A.has_fingering == 0) {
     // unfingered MIDI: optimal-transport fingering reward. The kinematics scratch is dead by now.
     __syncwarp();
     fing = do_reset ? 0.f : ot_fingering_reward(&W.a.s.Z[0][0], lane, site, qk, goal_cur, kt);
@@ -1932,7 +1932,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       obs[i] = f < T ? (float)A.goal[(size_t)(song_off + f) * 89 + (i % 89)] : 0.f;
     }
     int off = ng;
-    if (A.has_fingering) {
+    if (A.has_fingering == 1) {
       // (2,5) flags of the fingers used in frame t0 (:391-412)
       unsigned used = 0u;
       for (int p = 0; p < A.pmax; p++) {

@@ -24,7 +24,7 @@ class EngineConfig:
     n_substeps: int
     n_steps_lookahead: int = 0
     canonical_actions: bool = False
-    has_fingering: bool = False
+    has_fingering: int = 0  # 1: fingering reward + observation, 0: optimal-transport fingering reward, 2: neither
     disable_forearm_reward: bool = False
     wrong_press_termination: bool = False
     reward_type: int = _lib.REWARD_NEGATIVE_L2

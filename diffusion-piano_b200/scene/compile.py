@@ -39,6 +39,7 @@ DEFAULT_FRICTION = 1.0
 # reference suite/tasks/base.py:34-37
 RIGHT_HAND_POSITION = (0.4, 0.15, 0.13)
 LEFT_HAND_POSITION = (0.4, -0.15, 0.13)
+ABSENT_HAND_LIFT = 5.0  # metres: where the one-hand task parks the hand it does not have
 HAND_QUATERNION = (-1.0, -1.0, 1.0, 1.0)
 
 
@@ -166,7 +167,7 @@ def _add_hand(bld: _Builder, side: str, position, quaternion, gravcomp: bool, tx
     ma = mirror_axis if left else (lambda a: np.asarray(a, np.float64))
     finger_cls = CLS_LH_FINGER if left else CLS_RH_FINGER
     forearm_cls = CLS_LH_FOREARM if left else CLS_RH_FOREARM
-    info = dict(dof={}, body={}, geoms=[], dof_start=len(bld.dof["type"]))
+    info = dict(dof={}, body={}, geoms=[], dof_start=len(bld.dof["type"]), side=side)
     gc = 1.0 if gravcomp else 0.0
 
     def rec(node, parent):
@@ -305,8 +306,10 @@ def _hand_pairs(infos, disable_hand_collisions: bool):
     def of(info, pred):
         return [gid for name, gid in info["geoms"] if pred(name)]
 
-    rh, lh = infos
-    pairs += [(a, b) for a in of(rh, lambda n: n == "forearm") for b in of(lh, lambda n: n == "forearm")]
+    rh = next((i for i in infos if i["side"] == "right"), None)
+    lh = next((i for i in infos if i["side"] == "left"), None)
+    if rh and lh:
+        pairs += [(a, b) for a in of(rh, lambda n: n == "forearm") for b in of(lh, lambda n: n == "forearm")]
     for info in infos:
         for f0, f1 in zip(_FINGERS[:-1], _FINGERS[1:]):
             seg0 = of(info, lambda n: n.startswith(f0) and n != "lfmetacarpal")
@@ -316,7 +319,8 @@ def _hand_pairs(infos, disable_hand_collisions: bool):
         for f in ("ff", "mf"):
             pairs += [(a, b) for a in thumb for b in of(info, lambda n: n.startswith(f))]
     tip = lambda n: n in ("thmiddle", "thdistal") or (n[2:] in ("middle", "distal") and n[:2] in _FINGERS)
-    pairs += [(a, b) for a in of(rh, tip) for b in of(lh, tip)]
+    if rh and lh:
+        pairs += [(a, b) for a in of(rh, tip) for b in of(lh, tip)]
     return pairs
 
 
@@ -339,6 +343,8 @@ def compile_scene(
     reduced_by_removal: bool = False,
     attachment_yaw: float = 0.0,
     forearm_dofs=("forearm_tx", "forearm_ty"),
+    absent_hand: Optional[str] = None,
+    only_hand: Optional[str] = None,
 ) -> CompiledModel:
     """Builds the task scene the reference assembles in `suite/tasks/base.py:45-197`.
 
@@ -357,7 +363,14 @@ def compile_scene(
     hand) / -yaw (left hand) before the hand's own root quaternion.
     forearm_dofs (`tasks/base.py:104`, `shadow_hand.py:41-69,272-311`): which forearm joints exist. Subsets of the
     default pair are built by LOCKING the missing slide exactly as above (the kernel's tree keeps 26 dofs per hand);
-    the reference's other four (forearm_tz / roll / pitch / yaw) would add dofs to that tree and are not built."""
+    the reference's other four (forearm_tz / roll / pitch / yaw) would add dofs to that tree and are not built.
+
+    absent_hand "left" / "right" (`piano_with_one_shadow_hand.py:96-102`: the other hand is detached from the
+    scene): the step kernel always carries two 26-dof trees, so the absent hand stays in the tables but every one of
+    its dofs is LOCKED as above, its actuators are dead and its root is parked ABSENT_HAND_LIFT metres above the
+    keyboard where it touches nothing; the derived constants are those of the model without it.
+    only_hand "left" / "right" builds the reference's own form instead (the other hand not in the model at all,
+    nv = 114) for the CPU checker: the tests compare the two forms."""
     forearm_dofs = tuple(forearm_dofs)
     extra = [n for n in forearm_dofs if n not in shm.FOREARM_DOFS]
     if extra:
@@ -369,7 +382,11 @@ def compile_scene(
     if hands:
         half_w = pm.BASE_SIZE[1]  # piano.size[1], base.py:160
         for side, position in (("right", RIGHT_HAND_POSITION), ("left", LEFT_HAND_POSITION)):
-            tx_range = (-half_w - position[1], half_w - position[1])
+            if only_hand is not None and side != only_hand:
+                continue
+            tx_range = (-half_w - position[1], half_w - position[1])  # from the hand's own position (base.py:160-164)
+            if side == absent_hand:
+                position = (position[0], position[1], position[2] + ABSENT_HAND_LIFT)
             sign = -1.0 if side == "left" else 1.0
             quat = qmul(axis_angle((0.0, 0.0, 1.0), np.radians(sign * attachment_yaw)), qnorm(HAND_QUATERNION))
             infos.append(_add_hand(bld, side, position, qnorm(quat), gravity_compensation, tx_range,
@@ -377,14 +394,14 @@ def compile_scene(
     locked, dead = [], []
     if hands and reduced_action_space and reduced_by_removal:  # the reference's own construction (for the CPU checker)
         for info in infos:
-            pre = "rh_" if info is infos[0] else "lh_"
+            pre = "lh_" if info["side"] == "left" else "rh_"
             d2 = next(i for i, n in enumerate(bld.dof["name"]) if n.endswith("/" + pre + "THJ2"))
             a2 = next(i for i, n in enumerate(bld.act["name"]) if n.endswith("/" + pre + "A_THJ2"))
             bld.dof["range"][d2] = REDUCED_THUMB_RANGE
             bld.act["ctrlrange"][a2] = REDUCED_THUMB_RANGE
     elif hands and reduced_action_space:
         for info in infos:
-            pre = "rh_" if info is infos[0] else "lh_"
+            pre = "lh_" if info["side"] == "left" else "rh_"
             for jn in REDUCED_EXCLUDED_JOINTS:
                 locked.append(next(i for i, n in enumerate(bld.dof["name"]) if n.endswith("/" + pre + jn)))
                 dead.append(next(i for i, n in enumerate(bld.act["name"]) if n.endswith("/" + pre + "A_" + jn)))
@@ -392,9 +409,14 @@ def compile_scene(
             a2 = next(i for i, n in enumerate(bld.act["name"]) if n.endswith("/" + pre + "A_THJ2"))
             bld.dof["range"][d2] = REDUCED_THUMB_RANGE
             bld.act["ctrlrange"][a2] = REDUCED_THUMB_RANGE
-    if hands and not reduced_by_removal:
+    if hands and absent_hand is not None and only_hand is None:
+        info = next(i for i in infos if i["side"] == absent_hand)
+        model = ("lh" if absent_hand == "left" else "rh") + "_shadow_hand/"
+        locked += list(range(info["dof_start"], info["dof_end"]))
+        dead += [i for i, n in enumerate(bld.act["name"]) if n.startswith(model)]
+    if hands and not reduced_by_removal and only_hand is None:
         for info in infos:  # forearm slides the task does not ask for: locked, their actuators dead
-            model = "lh_shadow_hand/" if info is infos[1] else "rh_shadow_hand/"
+            model = "lh_shadow_hand/" if info["side"] == "left" else "rh_shadow_hand/"
             for dof_name in shm.FOREARM_DOFS:
                 if dof_name not in forearm_dofs:
                     locked.append(info["dof"][dof_name])

@@ -5,7 +5,7 @@ from typing import Any, Mapping, Optional, Union
 
 from .. import music
 from .environment import BatchedEnvironment, Environment, VectorizedPianoEnv
-from .tasks import PianoWithShadowHands, RewardType, SelfActuatedPiano
+from .tasks import HandSide, PianoWithOneShadowHand, PianoWithShadowHands, RewardType, SelfActuatedPiano
 
 _BASE_REPERTOIRE_NAME = "RoboPianist-repertoire-150-{}-v0"
 _DEBUG_BASE_NAME = "RoboPianist-debug-{}-v0"

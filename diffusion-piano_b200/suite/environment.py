@@ -42,15 +42,25 @@ class BatchedEnvironment:
         red = task.reduced_spec() if hasattr(task, "reduced_spec") else None
         self._reduced = red is not None
         self._full_obs_dim, self._full_action_dim = self.obs_dim, self.action_dim
+        self._pos_map = None
         if self._reduced:
             self._act_keep, self._obs_keep = np.asarray(red[0]), np.asarray(red[1])
             self.obs_dim, self.action_dim = len(self._obs_keep), len(self._act_keep)
+            if hasattr(task, "position_map"):  # one-hand task: `<hand>/position`, affine in two joints_pos columns
+                cols, W, c = task.position_map()
+                self._pos_map = (np.asarray(cols, np.int64), np.asarray(W, np.float64), np.asarray(c, np.float64))
+                self.obs_dim += 3
         n = self.num_envs
         self._obs = torch.zeros((n, self._full_obs_dim), dtype=torch.float32, device=self.device)
         if self._reduced:
             self._act_keep_t = torch.as_tensor(self._act_keep, device=self.device)
             self._obs_keep_t = torch.as_tensor(self._obs_keep, device=self.device)
             self._obs_red = torch.zeros((n, self.obs_dim), dtype=torch.float32, device=self.device)
+            if self._pos_map is not None:
+                self._obs_sel = torch.zeros((n, len(self._obs_keep)), dtype=torch.float32, device=self.device)
+                self._pos_cols_t = torch.as_tensor(self._pos_map[0], device=self.device)
+                self._pos_W_t = torch.as_tensor(self._pos_map[1], dtype=torch.float32, device=self.device)
+                self._pos_c_t = torch.as_tensor(self._pos_map[2], dtype=torch.float32, device=self.device)
             self._act_full = torch.zeros((n, self._full_action_dim), dtype=torch.float32, device=self.device)
         self._reward = torch.zeros(n, dtype=torch.float32, device=self.device)
         self._terms = torch.zeros((n, 5), dtype=torch.float32, device=self.device)
@@ -152,7 +162,13 @@ class BatchedEnvironment:
     def _device_obs(self):
         if not self._reduced:
             return self._obs
-        self._torch.index_select(self._obs, 1, self._obs_keep_t, out=self._obs_red)
+        if self._pos_map is None:
+            self._torch.index_select(self._obs, 1, self._obs_keep_t, out=self._obs_red)
+            return self._obs_red
+        k = len(self._obs_keep)
+        self._torch.index_select(self._obs, 1, self._obs_keep_t, out=self._obs_sel)
+        self._obs_red[:, :k].copy_(self._obs_sel)
+        self._obs_red[:, k:] = self._pos_c_t + self._obs_sel.index_select(1, self._pos_cols_t) @ self._pos_W_t
         return self._obs_red
 
     def step_device(self, actions):
@@ -170,6 +186,9 @@ class BatchedEnvironment:
     def _split(self, flat: np.ndarray) -> Dict[str, np.ndarray]:
         if self._reduced:
             flat = flat[:, self._obs_keep]
+            if self._pos_map is not None:
+                cols, W, c = self._pos_map
+                flat = np.concatenate([flat, (c + flat[:, cols].astype(np.float64) @ W).astype(flat.dtype)], 1)
         return OrderedDict((k, flat[:, o:o + s].astype(np.float64)) for k, (o, s) in self.layout.items())
 
     def reset(self) -> Dict[str, np.ndarray]:

@@ -54,7 +54,8 @@ typedef struct pp_config {
   int32_t n_frames;          /* T = len(NoteTrajectory.notes) */
   int32_t pmax;              /* max notes per frame in `pairs` */
   int32_t canonical_actions; /* 1: actions are in [-1,1] and are affinely mapped to the spec */
-  int32_t has_fingering;     /* 1: fingering obs + fingering reward; 0: OT fingering reward */
+  int32_t has_fingering;     /* 1: fingering obs + fingering reward; 0: OT fingering reward; 2: neither
+                              * (piano_with_one_shadow_hand.py:117-118 with disable_fingering_reward) */
   int32_t disable_forearm_reward;
   int32_t wrong_press_termination;
   int32_t reward_type;       /* PP_REWARD_* (self-actuated piano only) */

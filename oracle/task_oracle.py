@@ -106,6 +106,8 @@ class PianoWithShadowHandsOracle(_Base):
         super().__init__(task)
         a = self.model.a
         self.has_fingering = not task._disable_fingering_reward
+        # one-hand task (piano_with_one_shadow_hand.py): "left" / "right", None for the two-hands task
+        self.side = getattr(task, "_side", None)
         self.act_lo, self.act_hi = a["act_ctrlrange"][:, 0].copy(), a["act_ctrlrange"][:, 1].copy()
         # hand.joints order: 24 menagerie joints, then forearm_tx, forearm_ty
         order = list(range(2, 26)) + [0, 1]
@@ -150,6 +152,16 @@ class PianoWithShadowHandsOracle(_Base):
                 self.rh_keys.append((note.key, note.fingering))
             else:
                 self.lh_keys.append((note.key, note.fingering - 5))
+        if self.side is not None:  # piano_with_one_shadow_hand.py:297-318: this hand's notes only, a 5-vector
+            if self.side == "right":
+                self.lh_keys = []
+            else:
+                self.rh_keys = []
+            f = np.zeros(5)
+            for _, finger in self.rh_keys + self.lh_keys:
+                f[finger] = 1.0
+            self.fingering_state = f
+            return
         f = np.zeros((2, 5))
         for hand, keys in enumerate([self.rh_keys, self.lh_keys]):
             for _, finger in keys:
@@ -158,6 +170,18 @@ class PianoWithShadowHandsOracle(_Base):
 
     def observation(self):
         p = self.physics
+        if self.side is not None:  # :320-361: the one hand's joints_pos and position (xpos of its root body)
+            pre = "lh" if self.side == "left" else "rh"
+            body = self.model.names["body"].index(f"{pre}_shadow_hand/{pre}_forearm")
+            obs = OrderedDict([("piano/state", self.normalized_state.copy()),
+                               ("piano/sustain_state", np.array([self.sustain_state])),
+                               (f"{pre}_shadow_hand/joints_pos",
+                                p.qpos[self.lh_joints if self.side == "left" else self.rh_joints].copy()),
+                               (f"{pre}_shadow_hand/position", p.xpos[body].copy()),
+                               ("goal", self.goal_state.ravel().copy())])
+            if self.has_fingering:
+                obs["fingering"] = self.fingering_state.ravel().copy()
+            return obs
         obs = OrderedDict([("piano/state", self.normalized_state.copy()),
                            ("piano/sustain_state", np.array([self.sustain_state])),
                            ("rh_shadow_hand/joints_pos", p.qpos[self.rh_joints].copy()),
@@ -224,7 +248,8 @@ class PianoWithShadowHandsOracle(_Base):
                                                   bounds=(0, _KEY_CLOSE_ENOUGH_TO_PRESSED),
                                                   margin=_KEY_CLOSE_ENOUGH_TO_PRESSED * 10))
         energy = 0.0
-        for sl in (slice(0, 22), slice(22, 44)):
+        hands = {None: (slice(0, 22), slice(22, 44)), "right": (slice(0, 22),), "left": (slice(22, 44),)}[self.side]
+        for sl in hands:
             energy -= self.task._energy_penalty_coef * np.sum(np.abs(force[sl]) * np.abs(vel[sl]))
         terms["energy_reward"] = energy
         key_pos = lambda k: self.physics.geom_xpos[k] + self.key_geom_pos_offset[k]
@@ -236,7 +261,7 @@ class PianoWithShadowHandsOracle(_Base):
             else:
                 terms["fingering_reward"] = float(np.mean(tolerance(
                     np.hstack(dist), bounds=(0, _FINGER_CLOSE_ENOUGH_TO_KEY), margin=_FINGER_CLOSE_ENOUGH_TO_KEY * 10)))
-        else:
+        elif self.side is None:
             if on.size == 0:
                 terms["ot_fingering_reward"] = 1.0
             else:
