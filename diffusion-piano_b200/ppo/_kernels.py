@@ -31,19 +31,14 @@ _SIGNATURES = {
     "ppo_gemm_nt": (I, [P, P, P, I, I, I, P]),
     "ppo_gemm_nn": (I, [P, P, P, I, I, I, P]),
     "ppo_gemm_tn": (I, [P, P, P, I, I, I, P]),
-    "ppo_linear_relu_ln_fwd": (I, [P, P, P, P, P, P, P, P, I, I, I, F, P, P, P, U32, P]),
-    "ppo_ln_gemm_nt": (I, [P, P, P, P, P, F, P, P, P, P, P, I, I, I, P]),
-    "ppo_dropout_mask": (I, [P, I, I, F, P, U32, P]),
     "ppo_relu_ln_fwd": (I, [P, P, P, P, P, P, P, I, I, F, P, P, P, U32, P]),
     "ppo_relu_ln_bwd_dy": (I, [P, P, P, P, P, F, P, I, I, P]),
     "ppo_ln_bwd_gemm_nn": (I, [P, P, P, P, P, F, P, P, P, I, I, I, P]),
     "ppo_relu_ln_colsums": (I, [P, P, P, P, F, P, P, P, P, I, I, P]),
     "ppo_relu_ln_bwd": (I, [P, P, P, P, P, F, P, P, P, P, I, I, P]),
     "ppo_policy_head": (I, [P, P, P, P, P, P, F, F, P, P, P, P, P, P, P, I, I, P]),
-    "ppo_policy_head_fused": (I, [P, P, P, P, P, P, P, F, F, P, P, P, P, P, P, P, P, I, I, I, P]),
     "ppo_value_head_fused": (I, [P, P, P, P, P, P, P, P, I, I, P]),
     "ppo_value_head": (I, [P, P, P, P, P, P, I, P]),
-    "ppo_pdl_probe": (I, [P, I, I, P]),
     "ppo_add_bias": (I, [P, P, P, I, P]),
     "ppo_sample_actions": (I, [P, P, P, P, P, P, P, I, I, P]),
     "ppo_prepare_batch": (I, [P, P, P, P, F, F, P, P, P, P, P, I, P]),
@@ -51,8 +46,6 @@ _SIGNATURES = {
     "ppo_permutation": (I, [P, U32, I, P, P]),
     "ppo_grad_sumsq": (I, [P, I, P, P, P, I, P]),
     "ppo_grad_sumsq_static": (I, [P, I, P, I, P]),
-    "ppo_allreduce_sumsq": (I, [P, P, P, I, I, I, P, P, P, P, P, I, P]),
-    "ppo_allreduce_flag_words": (I, []),
     "ppo_clip_adam": (I, [P, P, P, P, I, P, I, F, F, F, F, F, P]),
     "ppo_advance": (I, [P, I, I, P]),
     "ppo_begin_update": (I, [P, P]),

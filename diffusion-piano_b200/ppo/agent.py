@@ -133,8 +133,7 @@ class PPOAgent:
                  max_grad_norm=0.5, ppo_epochs=10, batch_size=64, device="cuda", checkpoint_dir="checkpoints",
                  use_wandb=False, seed: Optional[int] = 0, process_group=None, dropout_p: float = DROPOUT_P,
                  use_graphs: bool = True, graph_scope: str = "update", gemm: str = "custom",
-                 fuse_policy_head: bool = False, fuse_value_head: bool = True, fuse_ln: bool = False,
-                 cluster_ln: bool = False):
+                 fuse_value_head: bool = True):
         if use_wandb:
             raise NotImplementedError("wandb logging is not part of the device path; read agent.stats() instead")
         if not torch.cuda.is_available():
@@ -152,16 +151,11 @@ class PPOAgent:
         if gemm not in ("custom", "cublas"):
             raise ValueError("gemm must be 'custom' or 'cublas'")
         self.gemm, self.small_m = gemm, 512
-        # heads with the last Linear and its dA inside (ppo_*_head_fused). Measured on B200 (update, B = 4096):
-        # neither 25.3 ms, value head only 25.0 ms, policy head only 29.9 ms (the 45-wide head does 2 x 360 loads
-        # per warp on 16 CTAs: slower than the two GEMM launches it saves) - so only the value head by default
-        self.fuse_policy_head, self.fuse_value_head = bool(fuse_policy_head), bool(fuse_value_head)
-        # block epilogues as the prologue of the next GEMM (ppo_ln_gemm_nt): correct, but every warp of a row group
-        # redoes the LayerNorm of its 4 rows ahead of its k loop - update 26.6 ms against 21.1 ms, so off by default
-        self.fuse_ln = bool(fuse_ln)
-        # ppo_linear_relu_ln_fwd: one thread-block-cluster kernel per block forward (row statistics through
-        # distributed shared memory). Same bits as the two-kernel path; update 21.4 ms against 21.1 ms, so off
-        self.cluster_ln = bool(cluster_ln)
+        # the value head with the critic's last Linear and its dA inside (ppo_value_head_fused): 25.0 ms per update
+        # against 25.3 ms (B200, B = 4096). The other fusions that were built and measured slower (policy head with
+        # its Linear inside, LayerNorm as a GEMM prologue, a cluster-wide Linear + LayerNorm kernel, a peer-memory
+        # all-reduce) live under tools/experiments, not in the product library.
+        self.fuse_value_head = bool(fuse_value_head)
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
@@ -221,15 +215,6 @@ class PPOAgent:
     def _block_fwd(self, net: _Net, blk: int, x, buf, training: bool, p: float, mask_in, rng_stream: int):
         li, ni = net.linears[blk], net.norms[blk]
         use_p = p if net.dropout_after[blk] else 0.0
-        if training and self.cluster_ln and self.gemm == "custom" and x.shape[0] <= self.small_m:
-            # Linear + bias + ReLU + LayerNorm + dropout in one launch (thread-block clusters, row statistics
-            # through distributed shared memory)
-            self._k(self.lib.ppo_linear_relu_ln_fwd, x, net.p[f"network.{li}.weight"], net.p[f"network.{li}.bias"],
-                    net.p[f"network.{ni}.weight"], net.p[f"network.{ni}.bias"], buf["a"][blk], buf["h"][blk],
-                    buf["stats"][blk], x.shape[0], net.dims[blk + 1], net.dims[blk], use_p,
-                    mask_in if use_p > 0 else None, buf["mask"][blk] if use_p > 0 else None, self.ctrl,
-                    rng_stream + blk)
-            return buf["a"][blk]
         self._mm_nt(x, net.p[f"network.{li}.weight"], buf["y"][blk])
         self._k(self.lib.ppo_relu_ln_fwd, buf["y"][blk], net.p[f"network.{li}.bias"], net.p[f"network.{ni}.weight"],
                 net.p[f"network.{ni}.bias"], buf["a"][blk], buf["h"][blk] if training else None,
@@ -243,8 +228,6 @@ class PPOAgent:
         """Three blocks + the last Linear (without its bias: the head kernels add it). Returns y4 (last=False: the
         fused head kernels compute the last Linear themselves)."""
         buf = net.buffers(x.shape[0], training)
-        if training and self.fuse_ln and self.gemm == "custom" and x.shape[0] <= self.small_m:
-            return self._forward_fused(net, x, buf, p, masks, rng_stream, last), buf
         a, mi = x, 0
         for blk in range(3):
             m = None
@@ -254,43 +237,6 @@ class PPOAgent:
         if last:
             self._mm_nt(a, net.p[f"network.{net.linears[3]}.weight"], buf["y"][3])
         return buf["y"][3], buf
-
-    def _forward_fused(self, net: _Net, x, buf, p: float, masks, rng_stream: int, last: bool):
-        """Training forward of a minibatch with every block's epilogue (bias, ReLU, LayerNorm, dropout) computed as
-        the prologue of the NEXT Linear's GEMM (ppo_ln_gemm_nt): 4 dependent launches instead of 7."""
-        rows = x.shape[0]
-        chain = torch.cuda.current_stream(self.device)
-        mi, wait_masks = 0, False
-        for blk in range(3):
-            if p > 0 and net.dropout_after[blk]:
-                if masks is not None:
-                    buf["mask"][blk].copy_(masks[mi])
-                    mi += 1
-                else:  # Philox keep-masks, generated off the chain while the first GEMM runs
-                    if not wait_masks:
-                        net.cstream.wait_stream(chain)
-                        wait_masks = True
-                    with torch.cuda.stream(net.cstream):
-                        self._k(self.lib.ppo_dropout_mask, buf["mask"][blk], rows, net.dims[blk + 1], p, self.ctrl,
-                                rng_stream + blk)
-        self._mm_nt(x, net.p[f"network.{net.linears[0]}.weight"], buf["y"][0])
-        if wait_masks:
-            chain.wait_stream(net.cstream)
-        for blk in range(3):  # epilogue of block blk + the Linear of block blk + 1
-            li, ni = net.linears[blk], net.norms[blk]
-            use_p = p if net.dropout_after[blk] else 0.0
-            mask = buf["mask"][blk] if use_p > 0 else None
-            if blk < 2 or last:
-                w_next = net.p[f"network.{net.linears[blk + 1]}.weight"]
-                self._k(self.lib.ppo_ln_gemm_nt, buf["y"][blk], net.p[f"network.{li}.bias"],
-                        net.p[f"network.{ni}.weight"], net.p[f"network.{ni}.bias"], mask, use_p, buf["a"][blk],
-                        buf["h"][blk], buf["stats"][blk], w_next, buf["y"][blk + 1], rows, w_next.shape[0],
-                        net.dims[blk + 1])
-            else:  # the fused head computes the last Linear itself: only the epilogue is left
-                self._k(self.lib.ppo_relu_ln_fwd, buf["y"][blk], net.p[f"network.{li}.bias"],
-                        net.p[f"network.{ni}.weight"], net.p[f"network.{ni}.bias"], buf["a"][blk], buf["h"][blk],
-                        buf["stats"][blk], rows, net.dims[blk + 1], use_p, mask, None, self.ctrl, rng_stream + blk)
-        return buf["y"][3]
 
     def _backward(self, net: _Net, x, buf, dz, p: float, da_ready: bool = False):
         """dz = gradient with respect to the last Linear's output; fills net.grad (except the head's bias).
@@ -399,18 +345,11 @@ class PPOAgent:
             self._backward(net, mb["states"], buf, mb["dv"], self.dropout_p, da_ready=fused)
             self._optim_step(net, 1)
         net = self.actor
-        fused = small and self.fuse_policy_head
-        y4, buf = self._forward(net, mb["states"], True, last=not fused)
-        if fused:
-            self._k(self.lib.ppo_policy_head_fused, buf["a"][2], net.p["network.9.weight"], net.p["network.9.bias"],
-                    net.p["log_std"], mb["actions"], mb["logp"], mb["adv"], self.epsilon, self.entropy_coef, mb["dz"],
-                    buf["da"][2], net.g["network.9.bias"], net.g["log_std"], mb["new_logp"], self.ctrl, net.scratch,
-                    net.ticket[2:], B, self.action_dim, net.dims[3])
-        else:
-            self._k(self.lib.ppo_policy_head, y4, net.p["network.9.bias"], net.p["log_std"], mb["actions"], mb["logp"],
-                    mb["adv"], self.epsilon, self.entropy_coef, mb["dz"], net.g["network.9.bias"], net.g["log_std"],
-                    mb["new_logp"], self.ctrl, net.scratch, net.ticket[2:], B, self.action_dim)
-        self._backward(net, mb["states"], buf, mb["dz"], 0.0, da_ready=fused)
+        y4, buf = self._forward(net, mb["states"], True)
+        self._k(self.lib.ppo_policy_head, y4, net.p["network.9.bias"], net.p["log_std"], mb["actions"], mb["logp"],
+                mb["adv"], self.epsilon, self.entropy_coef, mb["dz"], net.g["network.9.bias"], net.g["log_std"],
+                mb["new_logp"], self.ctrl, net.scratch, net.ticket[2:], B, self.action_dim)
+        self._backward(net, mb["states"], buf, mb["dz"], 0.0)
         self._optim_step(net, 0)
         main.wait_stream(side)
         return next_mb

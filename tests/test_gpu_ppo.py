@@ -285,49 +285,17 @@ def test_update_matches_reference_and_oracle(torch_cuda):
     assert abs(c.actor_loss - al) < 2e-4 * max(1.0, abs(al))
 
 
-@pytest.mark.parametrize("rows,H,K,p", [(128, 256, 329, 0.1), (128, 128, 256, 0.0), (45, 256, 57, 0.1), (3, 32, 40, 0.0)])
-def test_cluster_linear_relu_ln_matches_two_kernels(torch_cuda, rows, H, K, p):
-    """ppo_linear_relu_ln_fwd (cluster kernel) against ppo_gemm_nt + ppo_relu_ln_fwd: output, post-ReLU values,
-    statistics, and the SAME Philox dropout mask."""
-    torch = torch_cuda
-    from diffusion_piano_b200.ppo import _kernels
-
-    lib = _kernels.load()
-    g = torch.Generator().manual_seed(rows + H)
-    x, W = torch.randn(rows, K, generator=g).cuda(), (torch.randn(H, K, generator=g) / K ** 0.5).cuda()
-    bias, gamma, beta = (0.1 * torch.randn(H, generator=g)).cuda(), (1 + 0.1 * torch.randn(H, generator=g)).cuda(), \
-        (0.1 * torch.randn(H, generator=g)).cuda()
-    ctrl = torch.zeros(ctypes.sizeof(_kernels.PPOCtrl), dtype=torch.uint8, device="cuda")
-    _kernels.check(lib.ppo_ctrl_init(ctrl.data_ptr(), 17, 1e-4, 2e-4, _stream(torch)))
-    f = lambda *s: torch.full(s, 7.0, device="cuda")  # noqa: E731
-    y, out0, h0, st0, out1, h1, st1 = f(rows, H), f(rows, H), f(rows, H), f(rows, 2), f(rows, H), f(rows, H), f(rows, 2)
-    m0, m1 = (torch.zeros(rows, H, dtype=torch.uint8, device="cuda") for _ in range(2))
-    _kernels.check(lib.ppo_gemm_nt(x.data_ptr(), W.data_ptr(), y.data_ptr(), rows, H, K, _stream(torch)))
-    _kernels.check(lib.ppo_relu_ln_fwd(y.data_ptr(), bias.data_ptr(), gamma.data_ptr(), beta.data_ptr(), out0.data_ptr(),
-                                       h0.data_ptr(), st0.data_ptr(), rows, H, p, None, m0.data_ptr() if p > 0 else None,
-                                       ctrl.data_ptr(), 5, _stream(torch)))
-    _kernels.check(lib.ppo_linear_relu_ln_fwd(x.data_ptr(), W.data_ptr(), bias.data_ptr(), gamma.data_ptr(),
-                                              beta.data_ptr(), out1.data_ptr(), h1.data_ptr(), st1.data_ptr(), rows, H, K,
-                                              p, None, m1.data_ptr() if p > 0 else None, ctrl.data_ptr(), 5,
-                                              _stream(torch)))
-    torch.cuda.synchronize()
-    assert torch.equal(m0, m1)
-    assert torch.equal(h0, h1)  # same GEMM arithmetic
-    assert (st0 - st1).abs().max().item() < 1e-5 * max(1.0, st0.abs().max().item())
-    assert (out0 - out1).abs().max().item() < 2e-5
-
-
-def test_fused_heads_match_unfused(torch_cuda):
-    """ppo_policy_head_fused / ppo_value_head_fused (last Linear and its dA inside the head kernel) against the
-    three-launch path: same update on the reference's recorded permutations and masks."""
+def test_fused_value_head_matches_unfused(torch_cuda):
+    """ppo_value_head_fused (the critic's last Linear and its dA inside the head kernel) against the three-launch
+    path: same update on the reference's recorded permutations and masks."""
     torch = torch_cuda
     z, (sd, ad, n, batch, epochs, stride), masks, actor, critic, b = _golden()
     n_mb = epochs * ((n + batch - 1) // batch)
     dm = lambda m: torch.as_tensor(m.astype(np.uint8), device="cuda")  # noqa: E731
     results = []
-    for fused in (False, True):  # True: fused heads and the block epilogues as the next GEMM's prologue
+    for fused in (False, True):
         ag = _agent(torch, sd, ad, actor, critic, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch, ppo_epochs=epochs,
-                    fuse_policy_head=fused, fuse_value_head=fused, fuse_ln=fused, cluster_ln=False)
+                    fuse_value_head=fused)
         ag.update(b["states"], b["actions"], b["rewards"].astype(np.float32), z["log_probs"], b["next_states"],
                   b["dones"], perms=z["perms"], value_masks=[dm(m) for m in masks[0:2]],
                   next_value_masks=[dm(m) for m in masks[2:4]],
@@ -337,26 +305,6 @@ def test_fused_heads_match_unfused(torch_cuda):
         assert (results[0][i] - results[1][i]).abs().max().item() < 4e-6
     assert abs(results[0][2].actor_loss - results[1][2].actor_loss) < 1e-5
     assert abs(results[0][2].critic_loss - results[1][2].critic_loss) < 1e-5
-
-
-def test_cluster_forward_update_matches_default(torch_cuda):
-    """The whole update with the cluster forward kernel (cluster_ln=True) on the reference's recorded permutations
-    and masks: same parameters as the default path."""
-    torch = torch_cuda
-    z, (sd, ad, n, batch, epochs, stride), masks, actor, critic, b = _golden()
-    n_mb = epochs * ((n + batch - 1) // batch)
-    dm = lambda m: torch.as_tensor(m.astype(np.uint8), device="cuda")  # noqa: E731
-    thetas = []
-    for cl in (False, True):
-        ag = _agent(torch, sd, ad, actor, critic, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch, ppo_epochs=epochs,
-                    cluster_ln=cl)
-        ag.update(b["states"], b["actions"], b["rewards"].astype(np.float32), z["log_probs"], b["next_states"],
-                  b["dones"], perms=z["perms"], value_masks=[dm(m) for m in masks[0:2]],
-                  next_value_masks=[dm(m) for m in masks[2:4]],
-                  minibatch_masks=[[dm(m) for m in masks[4 + 2 * i: 6 + 2 * i]] for i in range(n_mb)])
-        thetas.append((ag.actor.theta.clone(), ag.critic.theta.clone()))
-    for i in (0, 1):
-        assert (thetas[0][i] - thetas[1][i]).abs().max().item() < 4e-6
 
 
 def test_graph_update_matches_oracle(torch_cuda):

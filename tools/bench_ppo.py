@@ -13,7 +13,7 @@ sys.path.insert(0, str(ROOT))
 
 
 def measure(envs, steps, warmup, local, world, rank, pg, epochs=10, batch_size=128, impl="product", eager=False,
-            graph_scope="update", schedule="auto", gemm="custom", fuse_ln=False, cluster_ln=False):
+            graph_scope="update", schedule="auto", gemm="custom"):
     """select_actions -> env step -> PPO update, `steps` control steps after `warmup`; returns (JSON-able dict, agent)."""
     import torch
 
@@ -25,7 +25,7 @@ def measure(envs, steps, warmup, local, world, rank, pg, epochs=10, batch_size=1
     if impl == "product":
         agent = PPOAgent(env.obs_dim, env.action_dim, lr=1e-4, gamma=0.99, epsilon=0.2, batch_size=batch_size,
                          ppo_epochs=epochs, device=f"cuda:{local}", seed=0, process_group=pg,
-                         use_graphs=not eager, graph_scope=graph_scope, gemm=gemm, fuse_ln=fuse_ln, cluster_ln=cluster_ln)
+                         use_graphs=not eager, graph_scope=graph_scope, gemm=gemm)
     else:
         sys.path.insert(0, str(ROOT / "tools"))
         from torch_ppo_baseline import TorchPPO
@@ -89,8 +89,6 @@ def main():
                     help="torch: plain-PyTorch restatement of ppo_v2.update (tools/torch_ppo_baseline.py) on the same env")
     ap.add_argument("--graph-scope", default="update", choices=["update", "minibatch"])
     ap.add_argument("--schedule", default="auto", choices=["auto", "lockstep", "divergent"])
-    ap.add_argument("--cluster-ln", action="store_true", help="Linear + LayerNorm as one cluster kernel in the forward")
-    ap.add_argument("--fuse-ln", action="store_true", help="block epilogues as the next GEMM's prologue (slower)")
     ap.add_argument("--gemm", default="custom", choices=["custom", "cublas"])
     ap.add_argument("--blas", default=None, help="torch.backends.cuda.preferred_blas_library (cublas / cublaslt)")
     args = ap.parse_args()
@@ -112,7 +110,7 @@ def main():
         pg = torch.distributed.group.WORLD
     line, agent = measure(args.envs, args.steps, args.warmup, local, world, rank, pg, epochs=args.epochs,
                           batch_size=args.batch_size, impl=args.impl, eager=args.eager, graph_scope=args.graph_scope,
-                          schedule=args.schedule, gemm=args.gemm, fuse_ln=args.fuse_ln, cluster_ln=args.cluster_ln)
+                          schedule=args.schedule, gemm=args.gemm)
     if rank == 0:
         print(json.dumps(line))
     if pg is not None:

@@ -9,7 +9,10 @@ import torch  # noqa: E402
 
 from diffusion_piano_b200.ppo import _kernels  # noqa: E402
 
-lib = _kernels.load()
+sys.path.insert(0, str(Path(__file__).resolve().parent))
+from experiments.load import load_experiments  # noqa: E402
+
+lib = load_experiments()  # product kernels + tools/experiments (this probe's kernel is not in the product library)
 dev = torch.device("cuda", 0)
 S = lambda: torch.cuda.current_stream().cuda_stream  # noqa: E731
 

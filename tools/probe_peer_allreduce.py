@@ -20,7 +20,10 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 td.init_process_group("nccl", device_id=dev)
-lib = _kernels.load()
+sys.path.insert(0, str(Path(__file__).resolve().parent))
+from experiments.load import load_experiments  # noqa: E402
+
+lib = load_experiments()  # product kernels + tools/experiments (this probe's kernel is not in the product library)
 n = 227_000 // 4 * 4
 grad = symm.empty(n, dtype=torch.float32, device=dev)
 flags = symm.empty(lib.ppo_allreduce_flag_words(), dtype=torch.int32, device=dev)
