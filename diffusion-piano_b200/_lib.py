@@ -23,7 +23,7 @@ class PPConfig(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "num_envs", "device", "task", "n_substeps", "n_steps_lookahead", "n_frames", "pmax",
         "canonical_actions", "has_fingering", "disable_forearm_reward", "wrong_press_termination",
-        "reward_type", "auto_reset", "max_contacts")] + [
+        "reward_type", "auto_reset", "max_contacts", "non_legacy_step")] + [
         ("energy_penalty_coef", ctypes.c_double), ("goal", c_void_p), ("pairs", c_void_p)]
 
 

@@ -39,6 +39,7 @@ struct pp_env {
   float *hand_off = nullptr, *hand_off_pending = nullptr;  // per-env y shift of both hands (active / drawn for the next reset)
   bool use_hand_off = false;
   unsigned* stick_bits = nullptr;  // solver warm-start hint carried between steps
+  float* stale = nullptr;          // [N,7,32] state at the last substep's start (cfg.non_legacy_step only)
   float *eval_sum = nullptr, *eval_episode = nullptr;  // musical metrics (MidiEvaluationWrapper)
   int *eval_steps = nullptr, *eval_count = nullptr;
   int* t_idx = nullptr;
@@ -324,6 +325,7 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(dalloc(&e->qfrc_applied, N * nv)); CUDA_OK(dalloc(&e->qacc, N * nv));
   CUDA_OK(dalloc(&e->sustain, N)); CUDA_OK(dalloc(&e->t_idx, N)); CUDA_OK(dalloc(&e->needs_reset, N));
   CUDA_OK(dalloc(&e->hand_off, N)); CUDA_OK(dalloc(&e->hand_off_pending, N)); CUDA_OK(dalloc(&e->stick_bits, N * 2));
+  if (cfg->non_legacy_step && cfg->task == PP_TASK_PIANO_WITH_SHADOW_HANDS) CUDA_OK(dalloc(&e->stale, (size_t)N * 7 * 32));
   CUDA_OK(dalloc(&e->eval_sum, N * 6)); CUDA_OK(dalloc(&e->eval_episode, N * 6));
   CUDA_OK(dalloc(&e->eval_steps, N)); CUDA_OK(dalloc(&e->eval_count, N));
   CUDA_OK(dalloc(&e->act_force, (size_t)N * (e->nu ? e->nu : 1)));
@@ -368,7 +370,7 @@ extern "C" int pp_destroy(pp_env* e) {
                  e->act_min_d, e->act_max_d, e->d_actions, e->d_obs, e->d_reward, e->d_terms, e->d_discount,
                  e->d_done, e->d_mask, e->hand_off, e->hand_off_pending, e->eval_sum, e->eval_episode,
                  e->eval_steps, e->eval_count, e->stick_bits, e->order, e->song_id, e->song_id_pending,
-                 e->song_off, e->song_T};
+                 e->song_off, e->song_T, e->stale};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -455,7 +457,7 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     A.goal = e->goal; A.pairs = e->pairs; A.reset_mask = mask; A.actions = actions;
     A.act_min = e->act_min_d; A.act_max = e->act_max_d;
     A.qfrc_applied = e->use_applied ? e->qfrc_applied : nullptr;
-    A.stick_bits = e->stick_bits;
+    A.stick_bits = e->stick_bits; A.stale = e->stale;
     A.hand_off = e->use_hand_off ? e->hand_off : nullptr; A.hand_off_pending = e->hand_off_pending;
     A.qpos = e->qpos; A.qvel = e->qvel; A.warm = e->warm; A.t_idx = e->t_idx; A.sustain = e->sustain;
     A.needs_reset = e->needs_reset; A.obs = obs; A.reward = reward; A.reward_terms = terms;

@@ -60,6 +60,10 @@ struct HandsArgs {
   const int* song_off;         // [n_songs] first frame of the song inside goal / pairs
   const int* song_T;           // [n_songs] frames of the song
   int n_songs;
+  // legacy_step=False (dm_control Physics.step = plain mj_step, no trailing mj_step1): position- and velocity-dependent
+  // quantities the task reads after the step are those of the LAST SUBSTEP'S START. stale [N,7,32]: hand qpos / qvel
+  // (2 + 2 rows, lane = dof) and key qpos (3 rows) saved there; null = legacy_step=True
+  float* stale;
 };
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);

@@ -623,6 +623,15 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         const int k = lane + 32 * i;
         if (k < PP_NKEY) { W.kq[k] = qk[i]; W.kv[k] = vk[i]; W.kw[k] = ak[i]; W.key_slot[k] = -1; }
       }
+      if (A.stale && sub == nsub - 1) {
+        // legacy_step=False: the task reads positions, contacts and actuator velocities as the last mj_step's forward pass
+        // left them, i.e. at the last substep's start: keep that state for the sensors below
+        float* st = A.stale + (size_t)env * 7 * 32 + lane;
+#pragma unroll
+        for (int h = 0; h < 2; h++) { st[h * 32] = q[h]; st[(2 + h) * 32] = v[h]; }
+#pragma unroll
+        for (int i = 0; i < 3; i++) st[(4 + i) * 32] = qk[i];
+      }
       // ---- mj_kinematics + RNE forward pass
       Kin K;
       forward_kinematics<true>(ht, o, L, q, v, yoff, K);
@@ -1749,6 +1758,23 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       }
     }  // substeps
   }
+  const bool stale = A.stale && nsub > 0;
+  if (stale) {  // body frames of the last substep's start over those of the integrated state
+    float qs[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) qs[h] = A.stale[((size_t)env * 7 + h) * 32 + lane];
+    Kin K;
+    forward_kinematics<false>(ht, o, L, qs, qs, yoff, K);
+    __syncwarp();
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      if (L.dof) {
+        const int g = h * 26 + lane;
+        st3(W.a.k.xpos[g], K.pos[h]);
+        W.a.k.xquat[g][0] = K.quat[h].w; W.a.k.xquat[g][1] = K.quat[h].x; W.a.k.xquat[g][2] = K.quat[h].y; W.a.k.xquat[g][3] = K.quat[h].z;
+      }
+    }
+  }
   t_idx = do_reset ? 0 : t_idx + 1;
 
   // ================================================================== sensors at the integrated state
@@ -1781,8 +1807,9 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   for (int h = 0; h < 2; h++) {
     const int ai = h * 22 + (lane < 22 ? lane : 0);
     const int t0 = ht.act_trn0[ai] - h * 26, t1 = ht.act_trn1[ai] - h * 26;
-    float vv = __shfl_sync(FULL, v[h], t0);
-    const float v1 = __shfl_sync(FULL, v[h], t1 >= 0 ? t1 : 0);
+    const float vs = stale ? A.stale[((size_t)env * 7 + 2 + h) * 32 + lane] : v[h];  // legacy_step=False: mj_fwdVelocity of the last mj_step
+    float vv = __shfl_sync(FULL, vs, t0);
+    const float v1 = __shfl_sync(FULL, vs, t1 >= 0 ? t1 : 0);
     if (ht.act_trn1[ai] >= 0) vv += v1;
     act_vel[h] = lane < 22 ? vv : 0.f;
   }
@@ -1824,6 +1851,9 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   float energy1 = wsum(fabsf(act_force[1]) * fabsf(act_vel[1]));
   // fingering reward (:300-331): fingertip site to key surface point, world offsets
   float fing = 0.f;
+  float qkp[3];  // key angles behind the key geoms' world positions (legacy_step=False: those of the last mj_step's kinematics)
+#pragma unroll
+  for (int i = 0; i < 3; i++) qkp[i] = stale ? A.stale[((size_t)env * 7 + 4 + i) * 32 + lane] : qk[i];
   if (A.has_fingering == 1) {
     float tot = 0.f; int cnt = 0;
     for (int p0 = 0; p0 < A.pmax; p0 += 32) {
@@ -1838,8 +1868,8 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       const f3 tip = shfl3(site, sidx);
       const int kk = has ? key : 0;
       // the key angle lives in the owner lane's registers
-      const float q0 = __shfl_sync(FULL, qk[0], kk & 31), q1 = __shfl_sync(FULL, qk[1], kk & 31),
-                  q2 = __shfl_sync(FULL, qk[2], kk & 31);
+      const float q0 = __shfl_sync(FULL, qkp[0], kk & 31), q1 = __shfl_sync(FULL, qkp[1], kk & 31),
+                  q2 = __shfl_sync(FULL, qkp[2], kk & 31);
       float val = 0.f;
       if (has) {
         const float kqv = (kk >> 5) == 0 ? q0 : (kk >> 5) == 1 ? q1 : q2;
@@ -1858,7 +1888,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   } else if (A.has_fingering == 0) {
     // unfingered MIDI: optimal-transport fingering reward. The kinematics scratch is dead by now.
     __syncwarp();
-    fing = do_reset ? 0.f : ot_fingering_reward(&W.a.s.Z[0][0], lane, site, qk, goal_cur, kt);
+    fing = do_reset ? 0.f : ot_fingering_reward(&W.a.s.Z[0][0], lane, site, qkp, goal_cur, kt);
   }
 
   const bool should_terminate = !do_reset && t_idx == T;

@@ -30,6 +30,7 @@ class EngineConfig:
     reward_type: int = _lib.REWARD_NEGATIVE_L2
     auto_reset: bool = True
     max_contacts: int = 0
+    legacy_step: bool = True  # dm_control Physics.legacy_step (False: derived quantities are one substep old)
     energy_penalty_coef: float = 5e-3
     device: int = 0
 
@@ -60,6 +61,7 @@ class BatchedPianoEngine:
         c.disable_forearm_reward = int(cfg.disable_forearm_reward)
         c.wrong_press_termination = int(cfg.wrong_press_termination)
         c.reward_type, c.auto_reset, c.max_contacts = cfg.reward_type, int(cfg.auto_reset), cfg.max_contacts
+        c.non_legacy_step = int(not cfg.legacy_step)
         c.energy_penalty_coef = cfg.energy_penalty_coef
         c.goal, c.pairs = self._goal.ctypes.data, self._pairs.ctypes.data
         h = ctypes.c_void_p()

@@ -21,7 +21,7 @@ from . import specs
 class BatchedEnvironment:
     def __init__(self, task, num_envs: int, device: int = 0, canonical_actions: bool = False,
                  auto_reset: bool = True, max_contacts: int = 0, random_state=None, schedule: str = "auto",
-                 augmentation_bank_size: int = 64):
+                 augmentation_bank_size: int = 64, legacy_step: bool = True):
         import torch  # device memory + streams only
 
         self._torch = torch
@@ -31,6 +31,9 @@ class BatchedEnvironment:
         cfg.auto_reset = auto_reset
         self._auto_reset = bool(auto_reset)
         cfg.max_contacts = max_contacts
+        # dm_control Physics.legacy_step (composer.Environment(legacy_step=), suite.load): False = plain mj_step, the task
+        # then reads positions, contacts and actuator velocities of the last substep's START
+        cfg.legacy_step = self._legacy_step = bool(legacy_step)
         self.engine = BatchedPianoEngine(task.model, task.song, cfg)
         if schedule != "auto":  # launch shape of the two-hands step (engine.set_schedule); never changes results
             self.engine.set_schedule(schedule)
@@ -61,6 +64,9 @@ class BatchedEnvironment:
                 self._pos_cols_t = torch.as_tensor(self._pos_map[0], device=self.device)
                 self._pos_W_t = torch.as_tensor(self._pos_map[1], dtype=torch.float32, device=self.device)
                 self._pos_c_t = torch.as_tensor(self._pos_map[2], dtype=torch.float32, device=self.device)
+                if not self._legacy_step:  # the root body's xpos is one substep old: q - h v of the forearm slides
+                    self._pos_dofs_t = torch.as_tensor(np.asarray(task.position_dofs(), np.int64), device=self.device)
+                    self._qvel = torch.zeros((n, self.engine.nv), dtype=torch.float32, device=self.device)
             self._act_full = torch.zeros((n, self._full_action_dim), dtype=torch.float32, device=self.device)
         self._reward = torch.zeros(n, dtype=torch.float32, device=self.device)
         self._terms = torch.zeros((n, 5), dtype=torch.float32, device=self.device)
@@ -168,7 +174,12 @@ class BatchedEnvironment:
         k = len(self._obs_keep)
         self._torch.index_select(self._obs, 1, self._obs_keep_t, out=self._obs_sel)
         self._obs_red[:, :k].copy_(self._obs_sel)
-        self._obs_red[:, k:] = self._pos_c_t + self._obs_sel.index_select(1, self._pos_cols_t) @ self._pos_W_t
+        fore = self._obs_sel.index_select(1, self._pos_cols_t)
+        if not self._legacy_step:
+            stream = self._torch.cuda.current_stream(self.device).cuda_stream
+            self.engine.get_state(qvel=self._qvel, stream=stream)
+            fore = fore - self.task.physics_timestep * self._qvel.index_select(1, self._pos_dofs_t)
+        self._obs_red[:, k:] = self._pos_c_t + fore @ self._pos_W_t
         return self._obs_red
 
     def step_device(self, actions):
@@ -188,7 +199,12 @@ class BatchedEnvironment:
             flat = flat[:, self._obs_keep]
             if self._pos_map is not None:
                 cols, W, c = self._pos_map
-                flat = np.concatenate([flat, (c + flat[:, cols].astype(np.float64) @ W).astype(flat.dtype)], 1)
+                fore = flat[:, cols].astype(np.float64)
+                if not self._legacy_step:
+                    self.engine.get_state(qvel=self._qvel)
+                    self._torch.cuda.synchronize(self.device)
+                    fore = fore - self.task.physics_timestep * self._qvel[:, self._pos_dofs_t].double().cpu().numpy()
+                flat = np.concatenate([flat, (c + fore @ W).astype(flat.dtype)], 1)
         return OrderedDict((k, flat[:, o:o + s].astype(np.float64)) for k, (o, s) in self.layout.items())
 
     def reset(self) -> Dict[str, np.ndarray]:
@@ -326,10 +342,8 @@ class Environment:
                  strip_singleton_obs_buffer_dim: bool = True, recompile_physics: bool = False,
                  legacy_step: bool = True):
         del strip_singleton_obs_buffer_dim, recompile_physics
-        if not legacy_step:
-            raise NotImplementedError("only dm_control's legacy_step=True ordering is implemented")
         self._b = BatchedEnvironment(task, 1, device=device, canonical_actions=canonical_actions,
-                                     auto_reset=False, random_state=random_state)
+                                     auto_reset=False, random_state=random_state, legacy_step=legacy_step)
         self.task = task
         self._reset_next_step = True
 

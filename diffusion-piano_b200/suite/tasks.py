@@ -302,6 +302,12 @@ class PianoWithOneShadowHand(PianoWithShadowHands):
                 ordered[key.replace("joints_pos", "position")] = (len(obs_keep), 3)
         return act_keep, obs_keep, ordered
 
+    def position_dofs(self):
+        """Dof indices (engine state rows) of the forearm slides behind `position_map`'s columns, same order."""
+        pre = "lh_" if self._side == "left" else "rh_"
+        return [self.model.names["dof"].index(f"{pre}shadow_hand/{n}") for n in ("forearm_tx", "forearm_ty")
+                if n in self._position_axes]
+
     def position_map(self):
         """(columns of the compacted observation row, W [k, 3], c [3]): position = c + row[columns] @ W."""
         _, _, layout = self.reduced_spec()

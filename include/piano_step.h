@@ -61,6 +61,10 @@ typedef struct pp_config {
   int32_t reward_type;       /* PP_REWARD_* (self-actuated piano only) */
   int32_t auto_reset;        /* 1: an env whose previous step was LAST resets on the next step */
   int32_t max_contacts;      /* 0 = library default */
+  int32_t non_legacy_step;   /* 0: dm_control's default legacy_step=True (mj_step2 ... mj_step1: the task reads positions,
+                              * contacts and actuator velocities of the INTEGRATED state); 1: legacy_step=False (plain
+                              * mj_step: it reads those of the last substep's start; qpos / qvel are the same either way).
+                              * The self-actuated piano task reads nothing position-derived: the flag changes nothing there */
   double energy_penalty_coef;
   const uint8_t *goal;  /* host [T,89]: keys to hold + sustain, per control frame */
   const int16_t *pairs; /* host [T,pmax,2]: (key, finger 0..9), key=-1 padding; may be NULL */

@@ -102,8 +102,11 @@ class SelfActuatedPianoOracle(_Base):
 
 
 class PianoWithShadowHandsOracle(_Base):
-    def __init__(self, task):
+    def __init__(self, task, legacy_step: bool = True):
         super().__init__(task)
+        # dm_control Physics.step: legacy_step=True runs mj_step2 ... mj_step1 (derived quantities at the integrated
+        # state), False runs plain mj_step (they stay those of the last mj_forward, i.e. of the last substep's start)
+        self.legacy_step = bool(legacy_step)
         a = self.model.a
         self.has_fingering = not task._disable_fingering_reward
         # one-hand task (piano_with_one_shadow_hand.py): "left" / "right", None for the two-hands task
@@ -201,12 +204,24 @@ class PianoWithShadowHandsOracle(_Base):
         p = self.physics
         p.ctrl[:] = action[:-1]
         self.sustain_state = action[-1]
-        for _ in range(self.nsub):
+        a = self.model.a
+        j0, j1 = a["act_trn0"], a["act_trn1"]
+        for i in range(self.nsub):
+            if i == self.nsub - 1:  # what the last mj_step's forward pass sees
+                q_start, v_start = p.qpos.copy(), p.qvel.copy()
             p.step()
             self._key_state()
         force = p.actuator_force.copy()  # from the last mj_step2 (pre-integration)
-        p.forward_position(True)  # trailing mj_step1: positions + contacts at the new state
-        vel = p.actuator_velocity.copy()
+        if self.legacy_step:
+            p.forward_position(True)  # trailing mj_step1: positions + contacts at the new state
+            vel = p.actuator_velocity.copy()
+        else:
+            # no trailing mj_step1: xpos / site_xpos / geom_xpos / contacts / actuator_velocity are the last mj_step's
+            q_new = p.qpos.copy()
+            p.qpos[:] = q_start
+            p.forward_position(True)
+            p.qpos[:] = q_new
+            vel = v_start[j0] + np.where(j1 >= 0, v_start[np.maximum(j1, 0)], 0.0)
         return self._after_physics(force, vel)
 
     def epilogue_at(self, qpos, qvel, actuator_force, sustain_state):
