@@ -30,7 +30,7 @@ class PPConfig(ctypes.Structure):
 TASK_SELF_ACTUATED_PIANO, TASK_PIANO_WITH_SHADOW_HANDS = 0, 1
 REWARD_NEGATIVE_L2, REWARD_NEGATIVE_XENT = 0, 1
 NUM_TERMS = 5
-SCHED_AUTO, SCHED_LOCKSTEP, SCHED_DIVERGENT = 0, 1, 2
+SCHED_AUTO, SCHED_LOCKSTEP, SCHED_DIVERGENT, SCHED_COMPACTED = 0, 1, 2, 3
 
 _SIGNATURES = {
     "pp_create": (c_int, [c_void_p, ctypes.POINTER(PPConfig), ctypes.POINTER(c_void_p)]),

@@ -12,5 +12,6 @@ trap 'rm -rf "$OBJ"' EXIT
 $NVCC $COMMON "$@" -c pp_api.cu -o "$OBJ/pp_api.o" 2>&1
 $NVCC $COMMON "$@" -c pp_piano_only.cu -o "$OBJ/pp_piano_only.o" 2>&1
 $NVCC $COMMON -prec-div=false -prec-sqrt=false "$@" -c pp_hands.cu -o "$OBJ/pp_hands.o" 2>&1
-$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o ../libpiano_step.so "$OBJ/pp_api.o" "$OBJ/pp_piano_only.o" "$OBJ/pp_hands.o" 2>&1
+$NVCC $COMMON -prec-div=false -prec-sqrt=false "$@" -c pp_hands_split.cu -o "$OBJ/pp_hands_split.o" 2>&1
+$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o ../libpiano_step.so "$OBJ/pp_api.o" "$OBJ/pp_piano_only.o" "$OBJ/pp_hands.o" "$OBJ/pp_hands_split.o" 2>&1
 $NVCC $COMMON "$@" -shared ppo_kernels.cu -o ../libppo_kernels.so 2>&1

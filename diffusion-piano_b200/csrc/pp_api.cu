@@ -54,6 +54,13 @@ struct pp_env {
   // launch shape (pp_set_schedule): envs per block and whether the envs are ordered by expected work
   int sched_mode = PP_SCHED_AUTO, block_envs = 2, tune_calls = 0;
   bool sort_work = false, tuned = false;
+  // PP_SCHED_COMPACTED: per substep a prologue launch, a Newton launch whose warps pull envs from a list, a finish launch
+  bool compacted = false;
+  int sms = 0;                    // multiprocessors of the device
+  float* sp_regs = nullptr;       // allocated at the first compacted step
+  float4* sp_smem = nullptr;
+  uint8_t* sp_skip = nullptr;
+  int *sp_list = nullptr, *sp_counts = nullptr;
   int* order = nullptr;  // [N]
   // song bank (pp_set_song_bank): goal / pairs then hold n_songs songs back to back
   int n_songs = 0, bank_pmax = 0;
@@ -370,7 +377,7 @@ extern "C" int pp_destroy(pp_env* e) {
                  e->act_min_d, e->act_max_d, e->d_actions, e->d_obs, e->d_reward, e->d_terms, e->d_discount,
                  e->d_done, e->d_mask, e->hand_off, e->hand_off_pending, e->eval_sum, e->eval_episode,
                  e->eval_steps, e->eval_count, e->stick_bits, e->order, e->song_id, e->song_id_pending,
-                 e->song_off, e->song_T, e->stale};
+                 e->song_off, e->song_T, e->stale, e->sp_regs, e->sp_smem, e->sp_skip, e->sp_list, e->sp_counts};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {e->h_actions, e->h_obs, e->h_reward, e->h_terms, e->h_discount, e->h_done};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -392,8 +399,11 @@ extern "C" int pp_obs_dim(const pp_env* e) { return e ? e->obs_dim : 0; }
 extern "C" long long pp_launch_count(const pp_env* e) { return e ? e->launches : 0; }
 extern "C" int pp_set_schedule(pp_env* e, int mode) {
   if (!e) return fail(PP_ERR_INVALID, "null handle");
-  if (mode != PP_SCHED_AUTO && mode != PP_SCHED_LOCKSTEP && mode != PP_SCHED_DIVERGENT)
+  if (mode != PP_SCHED_AUTO && mode != PP_SCHED_LOCKSTEP && mode != PP_SCHED_DIVERGENT && mode != PP_SCHED_COMPACTED)
     return fail(PP_ERR_INVALID, "schedule mode %d", mode);
+  if (mode == PP_SCHED_COMPACTED && e->cfg.task != PP_TASK_PIANO_WITH_SHADOW_HANDS)
+    return fail(PP_ERR_INVALID, "the compacted schedule belongs to the two-hands step");
+  e->compacted = mode == PP_SCHED_COMPACTED;
   e->sched_mode = mode;
   e->tuned = mode != PP_SCHED_AUTO;
   e->tune_calls = 0;
@@ -497,6 +507,22 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
         e->tuned = true;
       }
     }
+    if (e->compacted && full && mode == PP_MODE_STEP) {
+      const size_t N = c.num_envs;
+      if (!e->sp_regs) {
+        cudaDeviceGetAttribute(&e->sms, cudaDevAttrMultiProcessorCount, c.device);
+        CUDA_OK(dalloc(&e->sp_regs, N * PP_SP_NREG * 32));
+        CUDA_OK(dalloc(&e->sp_smem, N * pp_hands_split_smem_words()));
+        CUDA_OK(dalloc(&e->sp_skip, N));
+        CUDA_OK(dalloc(&e->sp_list, N * PP_SP_BUCKETS));
+        CUDA_OK(dalloc(&e->sp_counts, (size_t)c.n_substeps * (PP_SP_BUCKETS + 1)));
+      }
+      A.sp_regs = e->sp_regs; A.sp_smem = e->sp_smem; A.sp_skip = e->sp_skip;
+      e->launches += pp_launch_hands_split(A, s, e->sms, e->sp_list, e->sp_counts);
+      cudaError_t err = cudaGetLastError();
+      if (err != cudaSuccess) return fail(PP_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(err));
+      return PP_OK;
+    }
     if (sort) {
       pp_launch_work_order(e->counters, e->order, c.num_envs, s);
       e->launches++;
@@ -554,7 +580,7 @@ extern "C" int pp_step_host(pp_env* e, const float* actions, float* obs, float* 
   // (~10 %) than the copy overlap of the pieces (~5 %).
   const bool tuning = e->sched_mode == PP_SCHED_AUTO && !e->tuned;
   const bool split = e->cfg.task == PP_TASK_PIANO_WITH_SHADOW_HANDS && N >= 1024 && e->host_chunks > 1 && !tuning &&
-                     !e->sort_work;
+                     !e->sort_work && !e->compacted;
   const int pieces = split ? e->host_chunks : 1;
   const size_t per = split ? ((N / pieces + 9) / 10) * 10 : N;  // a multiple of both block shapes (2 and 10 envs)
   if (split) {

@@ -64,7 +64,20 @@ struct HandsArgs {
   // quantities the task reads after the step are those of the LAST SUBSTEP'S START. stale [N,7,32]: hand qpos / qvel
   // (2 + 2 rows, lane = dof) and key qpos (3 rows) saved there; null = legacy_step=True
   float* stale;
+  // split schedule (pp_hands.cu MODE): one substep = prologue kernel, Newton kernel over the list of stepping envs,
+  // finish kernel; the solver state of an env waits in sp_regs / sp_smem between them
+  int sub_index;            // substep this launch works on
+  float* sp_regs;           // [N, PP_SP_NREG, 32] per-lane solver state
+  float4* sp_smem;          // [N, sizeof(WarpShared) / 16] the env's shared-memory image
+  uint8_t* sp_skip;         // [N] env reset at substep 0 and sits the control step out
+  int* sp_list_out;         // prologue: the envs that step, in PP_SP_BUCKETS lists of [N]; sp_count_out[k] = entries of list k
+  int* sp_count_out;
+  const int* sp_list_in;    // Newton kernel: the same list; *sp_cursor = next entry to take
+  const int* sp_count_in;
+  int* sp_cursor;
 };
+constexpr int PP_SP_NREG = 64;
+constexpr int PP_SP_BUCKETS = 7;  // lists of the split schedule: dense fallback, then 5+, 4, 3, 2, 1, 0 cross-front contacts
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);
 // launches the step for envs [env_begin, env_begin + env_count) (env_count < 0: to the end); returns the number of kernels
@@ -73,3 +86,6 @@ int pp_launch_hands(const HandsArgs& A, cudaStream_t stream, int env_begin = 0, 
 // order[slot] = env, by decreasing counters[env*8+4] (Newton iterations of the env's previous control step)
 void pp_launch_work_order(const int* counters, int* order, int num_envs, cudaStream_t stream);
 size_t pp_hands_smem_bytes();
+// split schedule (pp_hands_split.cu): one control step as prologue / Newton-trip / finish launches per substep
+int pp_launch_hands_split(const HandsArgs& A, cudaStream_t stream, int sms, int* list, int* counts);
+size_t pp_hands_split_smem_words();  // float4 words of an env's shared-memory image

@@ -537,16 +537,58 @@ __device__ __forceinline__ void forward_kinematics(const HandTables& ht, const O
 }  // namespace
 
 // ====================================================================== the step kernel
+// ---- split schedule: an env's solver state between the kernels of a substep (see MODE below)
+__device__ __forceinline__ void sp_put(float* r, int& k, float x) { r[(k++) * 32] = x; }
+__device__ __forceinline__ void sp_put(float* r, int& k, int x) { r[(k++) * 32] = __int_as_float(x); }
+__device__ __forceinline__ void sp_put(float* r, int& k, unsigned x) { r[(k++) * 32] = __uint_as_float(x); }
+__device__ __forceinline__ void sp_put(float* r, int& k, bool x) { r[(k++) * 32] = x ? 1.f : 0.f; }
+__device__ __forceinline__ void sp_get(const float* r, int& k, float& x) { x = r[(k++) * 32]; }
+__device__ __forceinline__ void sp_get(const float* r, int& k, int& x) { x = __float_as_int(r[(k++) * 32]); }
+__device__ __forceinline__ void sp_get(const float* r, int& k, unsigned& x) { x = __float_as_uint(r[(k++) * 32]); }
+__device__ __forceinline__ void sp_get(const float* r, int& k, bool& x) { x = r[(k++) * 32] != 0.f; }
+#define SP_PUT(x) sp_put(r_, k_, x);
+#define SP_GET(x) sp_get(r_, k_, x);
+// what a Newton trip changes (the last one integrates q and v) ...
+#define PP_SP_RW(OP) OP(a[0]) OP(a[1]) OP(Ma[0]) OP(Ma[1]) OP(sMa) OP(sa) OP(jar[0]) OP(jar[1]) OP(jar[2]) OP(jar[3]) \
+  OP(zone_old) OP(iter) OP(ls_total) OP(euler) OP(q[0]) OP(q[1]) OP(v[0]) OP(v[1])
+// ... and what the substep's prologue hands to the loop and to the finish
+#define PP_SP_RO(OP) OP(fs[0]) OP(fs[1]) OP(fsk[0]) OP(fsk[1]) OP(fsk[2]) OP(cD) OP(cmu) OP(fD[0]) OP(fD[1]) \
+  OP(faref[0]) OP(faref[1]) OP(floss[0]) OP(floss[1]) OP(lsg[0]) OP(lsg[1]) OP(lD[0]) OP(lD[1]) OP(laref[0]) OP(laref[1]) \
+  OP(sM) OP(sfs) OP(ssg) OP(sD) OP(saref) OP(ncon) OP(ndrop) OP(nslot) OP(my_nent) OP(my_slot) OP(nlr) OP(nefc) \
+  OP(lrb) OP(slot_lr_mask) OP(my_lr) OP(dense_mode) OP(slot_lr) OP(act_force[0]) OP(act_force[1])
+#define PP_SP_REGS() float* r_ = A.sp_regs + (size_t)env * PP_SP_NREG * 32 + lane; int k_ = 0
+#define PP_SP_SAVE_ALL() do { PP_SP_REGS(); PP_SP_RW(SP_PUT) PP_SP_RO(SP_PUT) } while (0)
+#define PP_SP_SAVE_RW() do { PP_SP_REGS(); PP_SP_RW(SP_PUT) } while (0)
+#define PP_SP_LOAD_ALL() do { PP_SP_REGS(); PP_SP_RW(SP_GET) PP_SP_RO(SP_GET) } while (0)
+// bytes [b0, b1) of the warp's shared memory to / from the env's image (16-byte words, both ends rounded outwards)
+template <bool STORE>
+__device__ __forceinline__ void sp_copy_smem(const HandsArgs& A, int env, WarpShared& W, int lane, size_t b0, size_t b1) {
+  float4* img = A.sp_smem + (size_t)env * (sizeof(WarpShared) / 16);
+  float4* sm = reinterpret_cast<float4*>(&W);
+  if (STORE) {
+    for (int i = (int)(b0 / 16) + lane; i < (int)((b1 + 15) / 16); i += 32) img[i] = sm[i];
+  } else {
+    // asynchronous copies (LDGSTS): all in flight at once instead of one global latency per 16 bytes of the lane
+    const unsigned sbase = (unsigned)__cvta_generic_to_shared(sm);
+    for (int i = (int)(b0 / 16) + lane; i < (int)((b1 + 15) / 16); i += 32)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sbase + 16u * (unsigned)i), "l"(img + i) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  }
+}
 // WPB warps (= envs) per block. With WPB > 1 the warps of a block meet at the phase boundaries
 // of every substep, so that they fetch the same stretch of the (instruction-cache bound) code
 // together; the meeting is skipped for a block in which any env resets (it runs no substeps).
-template <int WPB>
-__global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(HandsArgs A, int env_base) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  WarpShared& W = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
+// MODE: 0 = the whole control step in one launch. The split schedule cuts every substep into three launches so that no
+// env waits for the slowest Newton loop of its block while every warp of an SM still runs the same phase of the code:
+// PP_SPLIT_PRO = substep `A.sub_index` up to the top of the Newton loop (an env that resets does so here, at substep 0,
+// and sits the rest of the control step out), PP_SPLIT_NEWTON = the Newton loop, by warps that take the next env of
+// the list whenever they are done with one, PP_SPLIT_FIN = the rest of the substep and, after the last one, the task
+// epilogue. Same code, same arithmetic: the three kernels are this function with the other phases compiled out.
+constexpr int PP_SPLIT_PRO = 1, PP_SPLIT_NEWTON = 2, PP_SPLIT_FIN = 3;
+template <int WPB, int MODE>
+__device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W, const int env) {
   const int lane = threadIdx.x & 31;
-  const int slot_ = env_base + blockIdx.x * WPB + (threadIdx.x >> 5);
-  const int env = A.order ? A.order[slot_] : slot_;
   const DevModel& dm = *A.dm;
   const Options& o = dm.opt;
   const HandTables& ht = dm.hand;
@@ -556,11 +598,16 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   const int l = L.dof ? lane : 25;  // safe table index
 
   int t_idx = A.t_idx[env];
+  const bool first_launch = MODE == 0 || (MODE == PP_SPLIT_PRO && A.sub_index == 0);
   const bool do_reset = A.mode == PP_MODE_RESET ? (A.reset_mask ? A.reset_mask[env] != 0 : true)
-                                                : (A.auto_reset && A.needs_reset[env]);
+                                                : (first_launch && A.auto_reset && A.needs_reset[env]);
+  bool sits_out = false;
+  if (MODE == PP_SPLIT_PRO && A.sub_index == 0) { if (lane == 0) A.sp_skip[env] = do_reset ? 1 : 0; }
+  else if (MODE == PP_SPLIT_PRO || MODE == PP_SPLIT_FIN) sits_out = A.sp_skip[env] != 0;
   bool meet = false;
-  if (WPB > 1) meet = __syncthreads_and(A.mode != PP_MODE_RESET && !do_reset) != 0;
+  if (WPB > 1 && MODE != PP_SPLIT_NEWTON) meet = __syncthreads_and(A.mode != PP_MODE_RESET && !do_reset && !sits_out) != 0;
   if (A.mode == PP_MODE_RESET && !do_reset) return;
+  if (sits_out) return;
 #define PP_MEET() do { if (WPB > 1 && meet) __syncthreads(); } while (0)
 
   // ---- state: lane l holds hand dof l of both hands and keys l, l+32, l+64
@@ -614,8 +661,64 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   }
   // ================================================================ substeps (+ the trailing mj_step1)
   const int nsub = do_reset ? 0 : A.n_substeps;
+  if (MODE == PP_SPLIT_FIN && A.sub_index > 0) {  // the sums of the control step's earlier substeps
+    const int* cn = A.counters + (size_t)env * 8;
+    sum_iter = cn[4]; sum_ls = cn[5]; sum_dense = cn[6]; sum_coupled = cn[7];
+  }
   {
-    for (int sub = 0;; sub++) {
+    bool resume = MODE == PP_SPLIT_NEWTON || MODE == PP_SPLIT_FIN;  // enter the first substep of the launch at its Newton loop
+    for (int sub = MODE == 0 ? 0 : A.sub_index;; sub++) {
+      // state that crosses the phases of a substep (split schedule: saved / loaded between the kernels)
+      float fs[2], fsk[3], cD, cmu, fD[2], faref[2], floss[2], lsg[2], lD[2], laref[2];
+      float sM, sfs, sa, ssg, sD, saref, a[2], Ma[2], sMa, jar[4];
+      int ncon, ndrop, nslot, my_nent, my_slot, nlr, nefc, zone_old, iter, ls_total;
+      unsigned lrb, slot_lr_mask;
+      bool my_lr, dense_mode, slot_lr, euler;
+      float (*Ht)[9] = W.a.s.Ht;
+      const int posl = lane < 4 ? lane : 4 + lane - L.ni.cs;  // own position in own ancestor list
+      // front lane identity: lane = replica*16 + hand*8 + chain
+      const int frep = lane >> 4, fh = (lane >> 3) & 1, fc = lane & 7;
+      const bool fvalid = fc < 5;
+      const int fce = fc == 0 ? 7 : fc == 1 ? 11 : fc == 2 ? 15 : fc == 3 ? 20 : 25;
+      const int fn = (fc == 3 || fc == 4) ? 5 : 4;
+      const int fcs = fce - fn + 1;
+      const int fg0 = fh * 26;
+
+      // out = M x for x in W.va: ancestors from registers, descendants from the pristine copy Mt
+      auto matvec_M = [&](float out[2]) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          float s = 0.f;
+          if (L.dof) {
+#pragma unroll
+            for (int j = 0; j < 9; j++) {
+              const int an = j < 4 ? j : L.ni.cs + j - 4;
+              const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
+              if (valid) s += W.Mt[h * 26 + lane][j] * W.va[h * 26 + an];
+            }
+            for (int d = lane + 1; d < lane + L.ni.nsub; d++) s += W.Mt[h * 26 + d][posl] * W.va[h * 26 + d];
+          }
+          out[h] = s;
+        }
+      };
+      // H_t <- M: tree entries only (the diagonal rows are added when the fronts are loaded)
+      auto build_M = [&]() {
+        if (L.dof) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+#pragma unroll
+            for (int j = 0; j < 9; j++) {
+              const int an = j < 4 ? j : L.ni.cs + j - 4;
+              const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
+              if (valid) Ht[h * 26 + lane][j] = W.Mt[h * 26 + lane][j];
+            }
+          }
+        }
+        __syncwarp();
+      };
+      const float scale = 1.f / (o.meaninertia * (float)PP_NV);
+      const int maxit = min(o.iterations, 50);
+      if (!resume) {
       PP_MEET();
       // ---- key state to shared memory
 #pragma unroll
@@ -747,7 +850,6 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         }
       }
       // ---- mj_fwdActuation (position servos on joints / 2-joint fixed tendons) + qfrc_smooth
-      float fs[2];
 #pragma unroll
       for (int h = 0; h < 2; h++) {
         float f = 0.f;
@@ -767,7 +869,6 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         const float applied = (A.qfrc_applied && L.dof) ? A.qfrc_applied[sbase + PP_NKEY + h * PP_HD + lane] : 0.f;
         fs[h] = L.dof ? (-damp_h * v[h] - bias[h] + fa + applied) : 0.f;
       }
-      float fsk[3];
 #pragma unroll
       for (int i = 0; i < 3; i++) {
         const int k = lane + 32 * i;
@@ -780,7 +881,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
 
       PP_MEET();
       // ================================================================ mj_collision
-      int ncon = 0, ndrop = 0;
+      ncon = 0; ndrop = 0;
       {
         f3 gc[2], gax[2]; float gr = 0.f, ghl = 0.f; int gnode = 0; bool finger = false;
         const bool hasg = lane < ngh;
@@ -911,12 +1012,12 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
 #pragma unroll
       for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = v[h];
       // key slots: contacts on the same key share one slot
-      int nslot = 0;
-      int my_nent = 0; float cD = 0.f, caref[4] = {0.f, 0.f, 0.f, 0.f}; int my_slot = -1;
+      nslot = 0;
+      my_nent = 0; cD = 0.f; float caref[4] = {0.f, 0.f, 0.f, 0.f}; my_slot = -1;
       unsigned cm[2] = {0u, 0u};
-      int ids = 0, kind = 0, key = -1, nlr = 0;
-      unsigned lrb = 0u;
-      bool my_lr = false, dense_mode = false;
+      int ids = 0, kind = 0, key = -1; nlr = 0;
+      lrb = 0u;
+      my_lr = false; dense_mode = false;
       if (lane < ncon) { ids = W.c_ids[lane]; kind = (ids >> 6) & 1; key = kind == 0 ? (ids >> 8) : -1; }
       {
         const bool wants = lane < ncon && kind == 0 && key < PP_NKEY && key >= 0;
@@ -1021,10 +1122,10 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       } else if (lane < ncon) {
         W.c_mask[0][lane] = 0u; W.c_mask[1][lane] = 0u; W.c_slot[lane] = -1; W.c_nent[lane] = 0; W.c_lr[lane] = 0;
       }
-      const float cmu = (lane < ncon) ? o.pair_friction[kind == 0 ? PP_PAIRCLS_PIANO : PP_PAIRCLS_HAND] : 0.f;
+      cmu = (lane < ncon) ? o.pair_friction[kind == 0 ? PP_PAIRCLS_PIANO : PP_PAIRCLS_HAND] : 0.f;
       __syncwarp();
       // slot bookkeeping: the root path (one finger of one hand) that owns each touched key
-      bool slot_lr = false;  // a low-rank contact touches this key: its slot entry is needed in every solved vector
+      slot_lr = false;  // a low-rank contact touches this key: its slot entry is needed in every solved vector
       if (lane < nslot) {
         unsigned u0 = 0u, u1 = 0u;
         for (int c = 0; c < ncon; c++)
@@ -1035,11 +1136,10 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         W.slot_mask[lane] = u0 | u1;  // an in-front contact touches one hand only
         W.slot_hand[lane] = u1 ? 1 : 0;
       }
-      const unsigned slot_lr_mask = __ballot_sync(FULL, slot_lr);
+      slot_lr_mask = __ballot_sync(FULL, slot_lr);
 
       // per-dof rows: frictionloss (always) and joint limit (when violated)
-      float fD[2], faref[2], floss[2], lsg[2], lD[2], laref[2];
-      int nefc = 4 * ncon;
+      nefc = 4 * ncon;
       {
         float Kf, Bf;
         pp_kb(o.friction_solref, o.friction_solimp, o.h, Kf, Bf);
@@ -1058,7 +1158,7 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         }
       }
       // key-slot scalars (lane s < nslot)
-      float sM = 1.f, sfs = 0.f, sa = 0.f, ssg = 0.f, sD = 0.f, saref = 0.f; int skey = 0;
+      sM = 1.f; sfs = 0.f; sa = 0.f; ssg = 0.f; sD = 0.f; saref = 0.f; int skey = 0;
       if (lane < nslot) {
         skey = W.slot_key[lane];
         const float kq_ = W.kq[skey], kv_ = W.kv[skey];
@@ -1075,59 +1175,15 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       // H_t = M + diagonal rows + in-front contact cliques (one lane per finger-chain front, the
       // 4x4 root front replicated), cross-front contacts enter as a Woodbury correction. The last
       // trip of the loop reuses the same code for mj_Euler's (M + h diag(b)) solve.
-      float (*Ht)[9] = W.a.s.Ht;
-      const int posl = lane < 4 ? lane : 4 + lane - L.ni.cs;  // own position in own ancestor list
       // warm start: the previous substep's acceleration; a dof whose frictionloss row ended in its quadratic
       // zone ("sticking") starts at the row's new reference acceleration instead, which keeps it there.
       // (The minimiser is unique, so the start only changes the number of Newton iterations: -9 % on the
       // bench workload, measured on the fp64 restatement.)
-      float a[2];
 #pragma unroll
       for (int h = 0; h < 2; h++) a[h] = (stick[h] && floss[h] > 0.f) ? faref[h] : acc[h];
-      float Ma[2] = {0.f, 0.f}, sMa = 0.f;
-      float jar[4] = {0.f, 0.f, 0.f, 0.f};
-      int zone_old = 0;  // zones (active bits) of the lane's in-front contact rows and slot row H_t was last assembled with
-      const bool con_on = lane < ncon && my_slot != -2;
-      // front lane identity: lane = replica*16 + hand*8 + chain
-      const int frep = lane >> 4, fh = (lane >> 3) & 1, fc = lane & 7;
-      const bool fvalid = fc < 5;
-      const int fce = fc == 0 ? 7 : fc == 1 ? 11 : fc == 2 ? 15 : fc == 3 ? 20 : 25;
-      const int fn = (fc == 3 || fc == 4) ? 5 : 4;
-      const int fcs = fce - fn + 1;
-      const int fg0 = fh * 26;
-
-      // out = M x for x in W.va: ancestors from registers, descendants from the pristine copy Mt
-      auto matvec_M = [&](float out[2]) {
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-          float s = 0.f;
-          if (L.dof) {
-#pragma unroll
-            for (int j = 0; j < 9; j++) {
-              const int an = j < 4 ? j : L.ni.cs + j - 4;
-              const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
-              if (valid) s += W.Mt[h * 26 + lane][j] * W.va[h * 26 + an];
-            }
-            for (int d = lane + 1; d < lane + L.ni.nsub; d++) s += W.Mt[h * 26 + d][posl] * W.va[h * 26 + d];
-          }
-          out[h] = s;
-        }
-      };
-      // H_t <- M: tree entries only (the diagonal rows are added when the fronts are loaded)
-      auto build_M = [&]() {
-        if (L.dof) {
-#pragma unroll
-          for (int h = 0; h < 2; h++) {
-#pragma unroll
-            for (int j = 0; j < 9; j++) {
-              const int an = j < 4 ? j : L.ni.cs + j - 4;
-              const bool valid = j < 4 ? (j <= lane) : (lane >= 4 && an <= lane);
-              if (valid) Ht[h * 26 + lane][j] = W.Mt[h * 26 + lane][j];
-            }
-          }
-        }
-        __syncwarp();
-      };
+      Ma[0] = Ma[1] = 0.f; sMa = 0.f;
+      jar[0] = jar[1] = jar[2] = jar[3] = 0.f;
+      zone_old = 0;
       // Ma at the warm start
 #pragma unroll
       for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = a[h];
@@ -1135,15 +1191,30 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       matvec_M(Ma);
       if (lane < nslot) { W.va[52 + lane] = sa; sMa = sM * sa; }
       __syncwarp();
-      if (con_on) {
+      if (lane < ncon && my_slot != -2) {
         const f3 ua = contact_ux(W, lane, my_nent);
         jar[0] = ua.x + cmu * ua.y - caref[0]; jar[1] = ua.x - cmu * ua.y - caref[1];
         jar[2] = ua.x + cmu * ua.z - caref[2]; jar[3] = ua.x - cmu * ua.z - caref[3];
       }
-      const float scale = 1.f / (o.meaninertia * (float)PP_NV);
-      int iter = 0, ls_total = 0;
-      const int maxit = min(o.iterations, 50);
-      bool euler = false;
+      iter = 0; ls_total = 0;
+      euler = false;
+      if (MODE == PP_SPLIT_PRO) {  // the env's solver state waits for the trip kernels
+        PP_SP_SAVE_ALL();
+        __syncwarp();
+        sp_copy_smem<true>(A, env, W, lane, offsetof(WarpShared, kq), sizeof(WarpShared));
+        if (lane == 0) {
+          // lists by the cost class of the env's trips: every cross-front contact adds 3 right-hand sides to each solve
+          const int k = dense_mode ? 0 : PP_SP_BUCKETS - 1 - min(nlr, PP_SP_BUCKETS - 2);
+          A.sp_list_out[(size_t)k * A.num_envs + atomicAdd(A.sp_count_out + k, 1)] = env;
+        }
+        return;
+      }
+      } else {
+        PP_SP_LOAD_ALL();
+        sp_copy_smem<false>(A, env, W, lane, offsetof(WarpShared, kq), sizeof(WarpShared));  // all behind the phase union
+        __syncwarp();
+      }
+      const bool con_on = lane < ncon && my_slot != -2;
 #ifndef PP_TRIP_MEET
 #define PP_TRIP_MEET 1
 #endif
@@ -1152,7 +1223,10 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
       // miss the instruction cache on most fetches (ncu, random actions: 51 % hit rate, 57 % of the stall
       // samples "no instruction"; with the meeting the warps fetch the same stretch of code together).
       bool fin = false;
+      if (MODE != PP_SPLIT_FIN)
       for (;;) {
+        // Newton kernel: the block's warps start every trip together (see the kernel below), whatever env they are on
+        if (MODE == PP_SPLIT_NEWTON && WPB > 1) __syncthreads_and(0);
         if (PP_TRIP_MEET && WPB > 1 && meet) {
           if (__syncthreads_and(fin)) break;
           if (fin) continue;
@@ -1706,6 +1780,10 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
         // already catches those steps.)
         if ((!changed && fabsf(alpha - 1.f) < 1e-3f) || iter >= maxit) euler = true;
       }
+      if (MODE == PP_SPLIT_NEWTON) {  // the loop is over: the finish kernel takes the env from here
+        PP_SP_SAVE_RW();
+        return;
+      }
       // ---- solution: hand dofs, touched keys (slots), untouched keys in closed form
 #pragma unroll
       for (int h = 0; h < 2; h++) {
@@ -1755,6 +1833,33 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
 #pragma unroll
         for (int i = 0; i < 3; i++) { const int k = lane + 32 * i; if (k < PP_NKEY && (W.kq[k] < 0.f || W.kq[k] > kt.hi[k])) nk++; }
         cnt_nefc = nefc + (int)wsum((float)nk);
+      }
+      resume = false;
+      if (MODE == PP_SPLIT_FIN && sub + 1 < nsub) {
+        // between two substeps of the split schedule the env lives in the handle's state arrays
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          if (L.dof) {
+            A.qpos[sbase + PP_NKEY + h * PP_HD + lane] = q[h];
+            A.qvel[sbase + PP_NKEY + h * PP_HD + lane] = v[h];
+            A.warm[sbase + PP_NKEY + h * PP_HD + lane] = acc[h];
+          }
+          if (A.stick_bits) {
+            const unsigned b = __ballot_sync(FULL, stick[h]);
+            if (lane == 0) A.stick_bits[(size_t)env * 2 + h] = b;
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+          const int k = lane + 32 * i;
+          if (k < PP_NKEY) { A.qpos[sbase + k] = qk[i]; A.qvel[sbase + k] = vk[i]; A.warm[sbase + k] = ak[i]; }
+        }
+        if (lane == 0) {
+          int* cn = A.counters + (size_t)env * 8;
+          cn[0] = cnt_ncon; cn[1] = cnt_nefc; cn[2] = cnt_iter; cn[3] = cnt_drop;
+          cn[4] = sum_iter; cn[5] = sum_ls; cn[6] = sum_dense; cn[7] = sum_coupled;
+        }
+        return;
       }
     }  // substeps
   }
@@ -1990,29 +2095,93 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
   }
 }
 
+template <int WPB, int MODE = 0>
+__global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(HandsArgs A, int env_base) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpShared& W = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
+  if (MODE == PP_SPLIT_NEWTON) {
+    // Persistent warps: each takes the next env of the substep's list whenever its env's loop is over, so no warp
+    // waits for the slowest env of a block. The block's warps still meet at the top of every trip - left to
+    // themselves they spread over the loop body and wait for instructions (measured: 59 % of the stall samples) - but
+    // a warp spends the meeting's round on its own env's next trip, not idle. A warp that finds the list empty
+    // keeps voting until all have.
+    // The lists are taken one after the other, heaviest class first: the warps of a block then mostly hold envs of
+    // one class, whose trips take similar times.
+    int cnt[PP_SP_BUCKETS], n = 0;
+#pragma unroll
+    for (int k = 0; k < PP_SP_BUCKETS; k++) { cnt[k] = A.sp_count_in[k]; n += cnt[k]; }
+    for (;;) {
+      int i = 0;
+      if ((threadIdx.x & 31) == 0) i = atomicAdd(A.sp_cursor, 1);
+      i = __shfl_sync(FULL, i, 0);
+      if (i >= n) break;
+      int k = 0;
+#pragma unroll
+      for (int b = 0; b < PP_SP_BUCKETS - 1; b++) if (k == b && i >= cnt[b]) { i -= cnt[b]; k = b + 1; }
+      hands_step_env<WPB, MODE>(A, W, A.sp_list_in[(size_t)k * A.num_envs + i]);
+      __syncwarp();
+    }
+    if (WPB > 1) while (!__syncthreads_and(1)) {}
+  } else {
+    const int slot = env_base + blockIdx.x * WPB + (threadIdx.x >> 5);
+    hands_step_env<WPB, MODE>(A, W, A.order ? A.order[slot] : slot);
+  }
+}
+
 // The shared-memory attribute is per device and per kernel: set on every device this process launches on
 // (a second handle on another GPU of the same process must not inherit the first one's "configured").
-template <int WPB>
+template <int WPB, int MODE = 0>
 static void configure_kernel() {
   static bool configured[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64 || !configured[dev]) {
-    cudaFuncSetAttribute(pp_hands_step_kernel<WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaFuncSetAttribute(pp_hands_step_kernel<WPB, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)(sizeof(WarpShared) * WPB));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
 }
-template <int WPB>
+template <int WPB, int MODE = 0>
 static int launch_wpb(const HandsArgs& A, cudaStream_t stream, int env_begin, int env_count) {
   const size_t smem = sizeof(WarpShared);
-  configure_kernel<WPB>();
-  configure_kernel<1>();
+  configure_kernel<WPB, MODE>();
+  configure_kernel<1, MODE>();
   const int nblk = env_count / WPB, tail = env_count - nblk * WPB;
-  if (nblk) pp_hands_step_kernel<WPB><<<nblk, 32 * WPB, smem * WPB, stream>>>(A, env_begin);
-  if (WPB > 1 && tail) pp_hands_step_kernel<1><<<tail, 32, smem, stream>>>(A, env_begin + nblk * WPB);
+  if (nblk) pp_hands_step_kernel<WPB, MODE><<<nblk, 32 * WPB, smem * WPB, stream>>>(A, env_begin);
+  if (WPB > 1 && tail) pp_hands_step_kernel<1, MODE><<<tail, 32, smem, stream>>>(A, env_begin + nblk * WPB);
   return (nblk ? 1 : 0) + (WPB > 1 && tail ? 1 : 0);
 }
+#ifdef PP_HANDS_SPLIT_TU
+#ifndef PP_SP_NEWTON_WPB
+#define PP_SP_NEWTON_WPB 10
+#endif
+#ifndef PP_SP_EDGE_WPB
+#define PP_SP_EDGE_WPB 10
+#endif
+// One control step of the split schedule: per substep the prologue launch (appends every stepping env to the list), the
+// Newton launch (one block per SM slot, warps pull envs from the list), the finish launch. counts: [n_substeps,
+// PP_SP_BUCKETS + 1] ints (envs per list, cursor), zeroed here; list: [PP_SP_BUCKETS, num_envs].
+int pp_launch_hands_split(const HandsArgs& A0, cudaStream_t stream, int sms, int* list, int* counts) {
+  constexpr int WN = PP_SP_NEWTON_WPB, WE = PP_SP_EDGE_WPB;
+  HandsArgs A = A0;
+  const int N = A.num_envs, nsub = A.n_substeps;
+  constexpr int CS = PP_SP_BUCKETS + 1;
+  cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)nsub * CS, stream);
+  configure_kernel<WN, PP_SPLIT_NEWTON>();
+  const size_t smem = sizeof(WarpShared);
+  const int grid = std::min((N + WN - 1) / WN, sms * (10 / WN));
+  int launches = 0;
+  for (int s = 0; s < nsub; s++) {
+    A.sub_index = s;
+    A.sp_list_out = list; A.sp_count_out = counts + CS * s;
+    A.sp_list_in = list; A.sp_count_in = counts + CS * s; A.sp_cursor = counts + CS * s + PP_SP_BUCKETS;
+    launches += launch_wpb<WE, PP_SPLIT_PRO>(A, stream, 0, N);
+    pp_hands_step_kernel<WN, PP_SPLIT_NEWTON><<<grid, 32 * WN, smem * WN, stream>>>(A, 0);
+    launches += 1 + launch_wpb<WE, PP_SPLIT_FIN>(A, stream, 0, N);
+  }
+  return launches;
+}
+#else
 #ifndef PP_WPB
 #define PP_WPB 2
 #endif
@@ -2056,3 +2225,5 @@ void pp_launch_work_order(const int* counters, int* order, int num_envs, cudaStr
   pp_work_order_kernel<<<1, 1024, 0, stream>>>(counters, order, num_envs);
 }
 size_t pp_hands_smem_bytes() { return sizeof(WarpShared); }
+size_t pp_hands_split_smem_words() { return sizeof(WarpShared) / 16; }
+#endif  // PP_HANDS_SPLIT_TU

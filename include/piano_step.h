@@ -162,7 +162,7 @@ int pp_get_diag(pp_env *env, float *qacc_dev, float *actuator_force_dev,
  *                       actions; the reference's loop, parallelized_base_v2.py:116-166, is this case);
  *   PP_SCHED_AUTO       (default) times both on full-batch steps 4..15 of the handle (CUDA events) and keeps the
  *                       faster. Results are identical in every mode: an env's result never depends on its block. */
-enum { PP_SCHED_AUTO = 0, PP_SCHED_LOCKSTEP = 1, PP_SCHED_DIVERGENT = 2 };
+enum { PP_SCHED_AUTO = 0, PP_SCHED_LOCKSTEP = 1, PP_SCHED_DIVERGENT = 2, PP_SCHED_COMPACTED = 3 };
 int pp_set_schedule(pp_env *env, int mode);
 int pp_get_schedule(const pp_env *env, int *mode, int *block_envs, int *sorted_by_work);
 

@@ -39,10 +39,44 @@ def test_schedules_give_identical_results():
     assert s1 == {"mode": "divergent", "block_envs": 10, "sorted_by_work": 1}
     auto, s2, _ = _run("auto")  # 20 steps: tuned after step 16, either shape may win at this size
     assert s2["mode"] == "auto" and s2["block_envs"] in (2, 10)
-    for other in (div, auto):
+    # per substep a prologue / Newton / finish launch, the Newton warps pulling envs from cost-class lists: the same
+    # code with the other phases compiled out, hence the same bits
+    comp, s3, c3 = _run("compacted")
+    assert s3["mode"] == "compacted"
+    np.testing.assert_array_equal(c0, c3)
+    for other in (div, auto, comp):
         for (o0, r0, t0), (o1, r1, t1) in zip(ref, other):
             np.testing.assert_array_equal(o0, o1)
             np.testing.assert_array_equal(r0, r1)
             np.testing.assert_array_equal(t0, t1)
     np.testing.assert_array_equal(c0, c1)  # same Newton / line-search iteration counts per env
     assert c0[:, 4].std() > 0  # the envs really did different amounts of work
+
+
+def test_compacted_schedule_with_resets_and_options():
+    """The compacted schedule through episode ends (auto-reset at substep 0 of the next step), the optimal-transport
+    reward, the one-substep-old derived quantities of legacy_step=False and a batch that is no multiple of 10."""
+    import torch
+    from diffusion_piano_b200 import music, suite
+
+    task = suite.PianoWithShadowHands(music.load("CMajorScaleTwoHands"), n_steps_lookahead=2, control_timestep=0.25,
+                                      disable_fingering_reward=True, wrong_press_termination=True)
+    outs = {}
+    for sched in ("lockstep", "compacted"):
+        env = suite.BatchedEnvironment(task, 57, canonical_actions=True, auto_reset=True, schedule=sched,
+                                       legacy_step=False)
+        g = torch.Generator(device="cuda")
+        g.manual_seed(7)
+        env.reset_device()
+        rows, n_done = [], 0
+        for _ in range(30):
+            a = torch.rand((57, 45), device="cuda", generator=g) * 2 - 1
+            obs, rew, done, terms, disc = env.step_device(a)
+            n_done += int(done.sum())
+            rows.append([x.cpu().numpy().copy() for x in (obs, rew, done, terms, disc)])
+        outs[sched] = rows
+        env.close()
+        assert n_done > 57  # every env ended at least one episode (wrong presses end them early)
+    for a, b in zip(outs["lockstep"], outs["compacted"]):
+        for x, y in zip(a, b):
+            np.testing.assert_array_equal(x, y)

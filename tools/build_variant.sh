@@ -10,6 +10,7 @@ mkdir -p ../../build
 $NVCC $COMMON "$@" -c pp_api.cu -o "$OBJ/pp_api.o" &
 $NVCC $COMMON "$@" -c pp_piano_only.cu -o "$OBJ/pp_piano_only.o" &
 $NVCC $COMMON -prec-div=false -prec-sqrt=false -Xptxas -v "$@" -c pp_hands.cu -o "$OBJ/pp_hands.o" 2> "../../build/$name.ptxas.txt" &
+$NVCC $COMMON -prec-div=false -prec-sqrt=false "$@" -c pp_hands_split.cu -o "$OBJ/pp_hands_split.o" &
 wait
-$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o "../../build/$name.so" "$OBJ/pp_api.o" "$OBJ/pp_piano_only.o" "$OBJ/pp_hands.o"
+$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o "../../build/$name.so" "$OBJ/pp_api.o" "$OBJ/pp_piano_only.o" "$OBJ/pp_hands.o" "$OBJ/pp_hands_split.o"
 grep -A1 "pp_hands_step_kernelILi" "../../build/$name.ptxas.txt" | grep -E "registers|spill" | head -4
