@@ -57,6 +57,7 @@ _SIGNATURES = {
     "pp_launch_count": (ctypes.c_longlong, [c_void_p]),
     "pp_set_schedule": (c_int, [c_void_p, c_int]),
     "pp_get_schedule": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "pp_schedule_in_force": (c_int, [c_void_p]),
     "pp_last_error": (ctypes.c_char_p, []),
     "pp_version": (ctypes.c_char_p, []),
 }

@@ -418,6 +418,10 @@ extern "C" int pp_get_schedule(const pp_env* e, int* mode, int* block_envs, int*
   if (sorted_by_work) *sorted_by_work = e->sort_work ? 1 : 0;
   return PP_OK;
 }
+extern "C" int pp_schedule_in_force(const pp_env* e) {
+  if (!e) return fail(PP_ERR_INVALID, "null handle");
+  return e->compacted ? PP_SCHED_COMPACTED : e->sort_work ? PP_SCHED_DIVERGENT : PP_SCHED_LOCKSTEP;
+}
 extern "C" const char* pp_last_error(void) { return g_err.c_str(); }
 extern "C" const char* pp_version(void) { return "piano_step 0.1 (sm_100a)"; }
 extern "C" int pp_action_bounds(const pp_env* e, float* lo, float* hi) {
@@ -482,32 +486,37 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
     static const bool no_sort = getenv("PP_NO_SORT") != nullptr;  // experiment knob: launch shape without the work order
     if (no_sort) sort = false;
     int tune_slot = -1;
+    bool compacted = e->compacted;
     if (e->sched_mode == PP_SCHED_AUTO && !e->tuned && full && mode == PP_MODE_STEP) {
       const int k = e->tune_calls++;
       if (k >= PP_TUNE_SKIP && k < PP_TUNE_SKIP + PP_TUNE_STEPS) {
         tune_slot = k - PP_TUNE_SKIP;
-        const bool divergent = tune_slot & 1;
-        block_envs = divergent ? 10 : 2;
-        sort = divergent;
+        const int cand = tune_slot % 3;  // lockstep, divergent, compacted in turn
+        block_envs = cand == 1 ? 10 : 2;
+        sort = cand == 1;
+        compacted = cand == 2;
         if (!e->tune_ev[0])
           for (auto& ev : e->tune_ev) cudaEventCreate(&ev);
         cudaEventRecord(e->tune_ev[2 * tune_slot], s);
       } else if (k == PP_TUNE_SKIP + PP_TUNE_STEPS) {
-        float t[2] = {0.f, 0.f};
+        float t[3] = {0.f, 0.f, 0.f};
         cudaEventSynchronize(e->tune_ev[2 * PP_TUNE_STEPS - 1]);
         for (int i = 0; i < PP_TUNE_STEPS; i++) {
           float ms = 0.f;
           cudaEventElapsedTime(&ms, e->tune_ev[2 * i], e->tune_ev[2 * i + 1]);
-          t[i & 1] += ms;
+          t[i % 3] += ms;
         }
-        const bool divergent = t[1] < 0.97f * t[0];
-        e->block_envs = block_envs = divergent ? 10 : 2;
-        e->sort_work = divergent;
-        sort = divergent;
+        // the lockstep shape unless another one is at least 3 % faster (it also lets pp_step_host overlap its copies)
+        int best = 0;
+        if (t[1] < 0.97f * t[0]) best = 1;
+        if (t[2] < 0.97f * t[0] && t[2] < t[1]) best = 2;
+        e->block_envs = block_envs = best == 1 ? 10 : 2;
+        e->sort_work = sort = best == 1;
+        e->compacted = compacted = best == 2;
         e->tuned = true;
       }
     }
-    if (e->compacted && full && mode == PP_MODE_STEP) {
+    if (compacted && full && mode == PP_MODE_STEP) {
       const size_t N = c.num_envs;
       if (!e->sp_regs) {
         cudaDeviceGetAttribute(&e->sms, cudaDevAttrMultiProcessorCount, c.device);
@@ -519,6 +528,7 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
       }
       A.sp_regs = e->sp_regs; A.sp_smem = e->sp_smem; A.sp_skip = e->sp_skip;
       e->launches += pp_launch_hands_split(A, s, e->sms, e->sp_list, e->sp_counts);
+      if (tune_slot >= 0) cudaEventRecord(e->tune_ev[2 * tune_slot + 1], s);
       cudaError_t err = cudaGetLastError();
       if (err != cudaSuccess) return fail(PP_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(err));
       return PP_OK;

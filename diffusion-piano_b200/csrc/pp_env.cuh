@@ -77,7 +77,7 @@ struct HandsArgs {
   int* sp_cursor;
 };
 constexpr int PP_SP_NREG = 64;
-constexpr int PP_SP_BUCKETS = 7;  // lists of the split schedule: dense fallback, then 5+, 4, 3, 2, 1, 0 cross-front contacts
+constexpr int PP_SP_BUCKETS = 10;  // lists of the split schedule: dense fallback, then 8, 7, .. 0 cross-front contacts (LRC = 8)
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);
 // launches the step for envs [env_begin, env_begin + env_count) (env_count < 0: to the end); returns the number of kernels

@@ -1223,10 +1223,16 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
       // miss the instruction cache on most fetches (ncu, random actions: 51 % hit rate, 57 % of the stall
       // samples "no instruction"; with the meeting the warps fetch the same stretch of code together).
       bool fin = false;
+#ifdef PP_SP_TIMING
+      long long dbg_t0 = 0, dbg_cyc = 0; int dbg_redo = 0;
+#endif
       if (MODE != PP_SPLIT_FIN)
       for (;;) {
         // Newton kernel: the block's warps start every trip together (see the kernel below), whatever env they are on
         if (MODE == PP_SPLIT_NEWTON && WPB > 1) __syncthreads_and(0);
+#ifdef PP_SP_TIMING  // diagnostic build (tools/trip_cost_model.py): cycles the env's trips take, without the meetings
+        if (MODE == PP_SPLIT_NEWTON) { if (dbg_t0) dbg_cyc += clock64() - dbg_t0; dbg_t0 = clock64(); }
+#endif
         if (PP_TRIP_MEET && WPB > 1 && meet) {
           if (__syncthreads_and(fin)) break;
           if (fin) continue;
@@ -1372,6 +1378,9 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         }
         float shss = sM + sc;  // H(slot, slot), lane < nslot
         if (redo) {
+#ifdef PP_SP_TIMING
+          dbg_redo++;
+#endif
           build_M();
           for (int s = 0; s < nslot; s++) {
             if (lane < 9) W.a.s.Kc[s][lane] = 0.f;
@@ -1781,6 +1790,10 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         if ((!changed && fabsf(alpha - 1.f) < 1e-3f) || iter >= maxit) euler = true;
       }
       if (MODE == PP_SPLIT_NEWTON) {  // the loop is over: the finish kernel takes the env from here
+#ifdef PP_SP_TIMING
+        dbg_cyc += clock64() - dbg_t0;
+        if (lane == 0) { A.counters[(size_t)env * 8 + 1] = (int)(dbg_cyc >> 4); A.counters[(size_t)env * 8 + 3] = dbg_redo; }
+#endif
         PP_SP_SAVE_RW();
         return;
       }
@@ -1856,7 +1869,10 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         }
         if (lane == 0) {
           int* cn = A.counters + (size_t)env * 8;
-          cn[0] = cnt_ncon; cn[1] = cnt_nefc; cn[2] = cnt_iter; cn[3] = cnt_drop;
+          cn[0] = cnt_ncon; cn[2] = cnt_iter;
+#ifndef PP_SP_TIMING
+          cn[1] = cnt_nefc; cn[3] = cnt_drop;
+#endif
           cn[4] = sum_iter; cn[5] = sum_ls; cn[6] = sum_dense; cn[7] = sum_coupled;
         }
         return;
@@ -2037,7 +2053,12 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
     A.sustain[env] = sustain;
     A.needs_reset[env] = done ? 1 : 0;
     int* cn = A.counters + (size_t)env * 8;
-    cn[0] = cnt_ncon; cn[1] = cnt_nefc; cn[2] = cnt_iter; cn[3] = cnt_drop;
+    cn[0] = cnt_ncon; cn[2] = cnt_iter;
+#ifndef PP_SP_TIMING
+    cn[1] = cnt_nefc; cn[3] = cnt_drop;
+#else
+    if (MODE == 0) { cn[1] = cnt_nefc; cn[3] = cnt_drop; }
+#endif
     cn[4] = sum_iter; cn[5] = sum_ls; cn[6] = sum_dense; cn[7] = sum_coupled;
     if (A.mode == PP_MODE_STEP) {
       float terms[5] = {0.f, 0.f, 0.f, 0.f, 0.f};

@@ -163,8 +163,9 @@ class BatchedPianoEngine:
 
     def set_schedule(self, mode) -> None:
         """Launch shape of the two-hands step: "auto" (default, timed on steps 4..15), "lockstep" (2 envs per
-        block: every env replays the same actions) or "divergent" (10 envs per block, ordered by expected work:
-        actions differ per env). Never changes results (include/piano_step.h, pp_set_schedule)."""
+        block: every env replays the same actions), "divergent" (10 envs per block, ordered by expected work:
+        actions differ per env) or "compacted" (prologue / Newton / finish launches per substep, Newton warps pulling
+        envs from cost-class lists: large batches with per-env actions). Never changes results (include/piano_step.h)."""
         modes = {"auto": _lib.SCHED_AUTO, "lockstep": _lib.SCHED_LOCKSTEP, "divergent": _lib.SCHED_DIVERGENT,
                  "compacted": _lib.SCHED_COMPACTED}
         _lib.check(self.lib.pp_set_schedule(self._h, modes.get(mode, mode)))
@@ -172,7 +173,9 @@ class BatchedPianoEngine:
     def get_schedule(self) -> Dict[str, int]:
         m, b, s = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
         _lib.check(self.lib.pp_get_schedule(self._h, ctypes.addressof(m), ctypes.addressof(b), ctypes.addressof(s)))
-        return {"mode": ("auto", "lockstep", "divergent", "compacted")[m.value], "block_envs": b.value, "sorted_by_work": s.value}
+        names = ("auto", "lockstep", "divergent", "compacted")
+        return {"mode": names[m.value], "block_envs": b.value, "sorted_by_work": s.value,
+                "in_force": names[self.lib.pp_schedule_in_force(self._h)]}
 
     @property
     def launch_count(self) -> int:

@@ -160,11 +160,22 @@ int pp_get_diag(pp_env *env, float *qacc_dev, float *actuator_force_dev,
  *   PP_SCHED_DIVERGENT  10 envs per block, envs ordered by the Newton iterations of their previous step so that a
  *                       block's envs need similar work - best when the actions differ per env (training, random
  *                       actions; the reference's loop, parallelized_base_v2.py:116-166, is this case);
- *   PP_SCHED_AUTO       (default) times both on full-batch steps 4..15 of the handle (CUDA events) and keeps the
- *                       faster. Results are identical in every mode: an env's result never depends on its block. */
+ *   PP_SCHED_COMPACTED  every substep as three launches of the same step code - prologue (kinematics .. constraint
+ *                       rows), Newton loop, finish (integration of the keys, after the last substep the task
+ *                       epilogue) - with the solver state of an env parked in device memory in between (about 30 KB
+ *                       per env, allocated at the first such step). The Newton launch is one persistent block per
+ *                       SM whose warps take the next env of a list whenever their env's loop is over, the lists
+ *                       ordered by cost class (cross-finger contacts = right-hand sides per solve): no warp idles
+ *                       while a block-mate iterates, and the block's warps still run the same trip of the loop
+ *                       together. Best for large batches with per-env actions (1.6x the divergent shape at 16384);
+ *   PP_SCHED_AUTO       (default) times the three in turn on full-batch steps 4..15 of the handle (CUDA events) and
+ *                       keeps the lockstep shape unless another is 3 % faster. Results are identical in every mode:
+ *                       an env's result never depends on its block or launch. pp_schedule_in_force = the shape the
+ *                       next step uses (PP_SCHED_LOCKSTEP / DIVERGENT / COMPACTED). */
 enum { PP_SCHED_AUTO = 0, PP_SCHED_LOCKSTEP = 1, PP_SCHED_DIVERGENT = 2, PP_SCHED_COMPACTED = 3 };
 int pp_set_schedule(pp_env *env, int mode);
 int pp_get_schedule(const pp_env *env, int *mode, int *block_envs, int *sorted_by_work);
+int pp_schedule_in_force(const pp_env *env);
 
 /* number of kernels launched by this handle since creation (for bench's gpu_launches) */
 long long pp_launch_count(const pp_env *env);

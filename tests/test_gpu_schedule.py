@@ -34,15 +34,15 @@ def test_schedules_give_identical_results():
     if not torch.cuda.is_available():
         pytest.skip("needs a CUDA device")
     ref, s0, c0 = _run("lockstep")
-    assert s0 == {"mode": "lockstep", "block_envs": 2, "sorted_by_work": 0}
+    assert s0 == {"mode": "lockstep", "block_envs": 2, "sorted_by_work": 0, "in_force": "lockstep"}
     div, s1, c1 = _run("divergent")
-    assert s1 == {"mode": "divergent", "block_envs": 10, "sorted_by_work": 1}
+    assert s1 == {"mode": "divergent", "block_envs": 10, "sorted_by_work": 1, "in_force": "divergent"}
     auto, s2, _ = _run("auto")  # 20 steps: tuned after step 16, either shape may win at this size
     assert s2["mode"] == "auto" and s2["block_envs"] in (2, 10)
     # per substep a prologue / Newton / finish launch, the Newton warps pulling envs from cost-class lists: the same
     # code with the other phases compiled out, hence the same bits
     comp, s3, c3 = _run("compacted")
-    assert s3["mode"] == "compacted"
+    assert s3["mode"] == "compacted" == s3["in_force"]
     np.testing.assert_array_equal(c0, c3)
     for other in (div, auto, comp):
         for (o0, r0, t0), (o1, r1, t1) in zip(ref, other):

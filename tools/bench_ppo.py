@@ -88,7 +88,7 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "torch", "torch-hostgae"],
                     help="torch: plain-PyTorch restatement of ppo_v2.update (tools/torch_ppo_baseline.py) on the same env")
     ap.add_argument("--graph-scope", default="update", choices=["update", "minibatch"])
-    ap.add_argument("--schedule", default="auto", choices=["auto", "lockstep", "divergent"])
+    ap.add_argument("--schedule", default="auto", choices=["auto", "lockstep", "divergent", "compacted"])
     ap.add_argument("--gemm", default="custom", choices=["custom", "cublas"])
     ap.add_argument("--blas", default=None, help="torch.backends.cuda.preferred_blas_library (cublas / cublaslt)")
     args = ap.parse_args()
