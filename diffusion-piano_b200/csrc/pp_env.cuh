@@ -67,6 +67,7 @@ struct HandsArgs {
   // split schedule (pp_hands.cu MODE): one substep = prologue kernel, Newton kernel over the list of stepping envs,
   // finish kernel; the solver state of an env waits in sp_regs / sp_smem between them
   int sub_index;            // substep this launch works on
+  int sp_chain;             // finish kernel: go on into the next substep's prologue (all but the last substep)
   float* sp_regs;           // [N, PP_SP_NREG, 32] per-lane solver state
   float4* sp_smem;          // [N, sizeof(WarpShared) / 16] the env's shared-memory image
   uint8_t* sp_skip;         // [N] env reset at substep 0 and sits the control step out

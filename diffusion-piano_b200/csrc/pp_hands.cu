@@ -589,6 +589,9 @@ constexpr int PP_SPLIT_PRO = 1, PP_SPLIT_NEWTON = 2, PP_SPLIT_FIN = 3;
 template <int WPB, int MODE>
 __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W, const int env) {
   const int lane = threadIdx.x & 31;
+#ifdef PP_SP_TIMING
+  const long long dbg_entry = clock64();
+#endif
   const DevModel& dm = *A.dm;
   const Options& o = dm.opt;
   const HandTables& ht = dm.hand;
@@ -1198,7 +1201,7 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
       }
       iter = 0; ls_total = 0;
       euler = false;
-      if (MODE == PP_SPLIT_PRO) {  // the env's solver state waits for the trip kernels
+      if (MODE == PP_SPLIT_PRO || MODE == PP_SPLIT_FIN) {  // the env's solver state waits for the Newton kernel
         PP_SP_SAVE_ALL();
         __syncwarp();
         sp_copy_smem<true>(A, env, W, lane, offsetof(WarpShared, kq), sizeof(WarpShared));
@@ -1224,14 +1227,21 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
       // samples "no instruction"; with the meeting the warps fetch the same stretch of code together).
       bool fin = false;
 #ifdef PP_SP_TIMING
-      long long dbg_t0 = 0, dbg_cyc = 0; int dbg_redo = 0;
+      long long dbg_t0 = 0, dbg_cyc = 0, dbg_first = 0, dbg_refill = 0; int dbg_redo = 0, dbg_trips = 0;
 #endif
       if (MODE != PP_SPLIT_FIN)
       for (;;) {
         // Newton kernel: the block's warps start every trip together (see the kernel below), whatever env they are on
-        if (MODE == PP_SPLIT_NEWTON && WPB > 1) __syncthreads_and(0);
 #ifdef PP_SP_TIMING  // diagnostic build (tools/trip_cost_model.py): cycles the env's trips take, without the meetings
-        if (MODE == PP_SPLIT_NEWTON) { if (dbg_t0) dbg_cyc += clock64() - dbg_t0; dbg_t0 = clock64(); }
+        if (MODE == PP_SPLIT_NEWTON) {
+          const long long now = clock64();
+          if (dbg_t0) { dbg_cyc += now - dbg_t0; if (dbg_trips == 1) dbg_first = now - dbg_t0; }
+          else dbg_refill = now - dbg_entry;
+        }
+#endif
+        if (MODE == PP_SPLIT_NEWTON && WPB > 1) __syncthreads_and(0);
+#ifdef PP_SP_TIMING
+        if (MODE == PP_SPLIT_NEWTON) { dbg_t0 = clock64(); dbg_trips++; }
 #endif
         if (PP_TRIP_MEET && WPB > 1 && meet) {
           if (__syncthreads_and(fin)) break;
@@ -1791,10 +1801,16 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
       }
       if (MODE == PP_SPLIT_NEWTON) {  // the loop is over: the finish kernel takes the env from here
 #ifdef PP_SP_TIMING
-        dbg_cyc += clock64() - dbg_t0;
-        if (lane == 0) { A.counters[(size_t)env * 8 + 1] = (int)(dbg_cyc >> 4); A.counters[(size_t)env * 8 + 3] = dbg_redo; }
 #endif
         PP_SP_SAVE_RW();
+#ifdef PP_SP_TIMING
+        {
+          const long long last = clock64() - dbg_t0;  // the mj_Euler trip and the hand-over
+          dbg_cyc += last;
+          int* cn = A.counters + (size_t)env * 8;
+          if (lane == 0) { cn[1] = (int)(dbg_cyc >> 4); cn[3] = (int)(dbg_first >> 4); cn[5] = (int)(last >> 4); cn[6] = (int)(dbg_refill >> 4); }
+        }
+#endif
         return;
       }
       // ---- solution: hand dofs, touched keys (slots), untouched keys in closed form
@@ -1873,9 +1889,12 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
 #ifndef PP_SP_TIMING
           cn[1] = cnt_nefc; cn[3] = cnt_drop;
 #endif
-          cn[4] = sum_iter; cn[5] = sum_ls; cn[6] = sum_dense; cn[7] = sum_coupled;
+          cn[4] = sum_iter; cn[7] = sum_coupled;
+#ifndef PP_SP_TIMING
+          cn[5] = sum_ls; cn[6] = sum_dense;
+#endif
         }
-        return;
+        if (!A.sp_chain) return;  // chained: straight on into the next substep's prologue, which ends this launch
       }
     }  // substeps
   }
@@ -2059,7 +2078,11 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
 #else
     if (MODE == 0) { cn[1] = cnt_nefc; cn[3] = cnt_drop; }
 #endif
-    cn[4] = sum_iter; cn[5] = sum_ls; cn[6] = sum_dense; cn[7] = sum_coupled;
+    cn[4] = sum_iter; cn[7] = sum_coupled;
+#ifdef PP_SP_TIMING
+    if (MODE == 0)
+#endif
+    { cn[5] = sum_ls; cn[6] = sum_dense; }
     if (A.mode == PP_MODE_STEP) {
       float terms[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
       if (!do_reset) {
@@ -2145,6 +2168,10 @@ __global__ void __launch_bounds__(32 * WPB, 10 / WPB) pp_hands_step_kernel(Hands
     if (WPB > 1) while (!__syncthreads_and(1)) {}
   } else {
     const int slot = env_base + blockIdx.x * WPB + (threadIdx.x >> 5);
+    if (MODE != 0 && slot >= A.num_envs) {  // split launches round the grid up: the spare warps of the last block
+      if (WPB > 1) __syncthreads_and(0);    // answer the entry vote (the block then runs without meetings) and leave
+      return;
+    }
     hands_step_env<WPB, MODE>(A, W, A.order ? A.order[slot] : slot);
   }
 }
@@ -2179,28 +2206,34 @@ static int launch_wpb(const HandsArgs& A, cudaStream_t stream, int env_begin, in
 #ifndef PP_SP_EDGE_WPB
 #define PP_SP_EDGE_WPB 10
 #endif
-// One control step of the split schedule: per substep the prologue launch (appends every stepping env to the list), the
-// Newton launch (one block per SM slot, warps pull envs from the list), the finish launch. counts: [n_substeps,
+// One control step of the split schedule: per substep the Newton launch (one block per SM slot, warps pull envs from the
+// lists) and, between two of them, one launch that finishes a substep and runs the next one's prologue (which appends
+// every stepping env to its list); the first prologue and the last finish (with the task epilogue) stand alone. counts: [n_substeps,
 // PP_SP_BUCKETS + 1] ints (envs per list, cursor), zeroed here; list: [PP_SP_BUCKETS, num_envs].
 int pp_launch_hands_split(const HandsArgs& A0, cudaStream_t stream, int sms, int* list, int* counts) {
-  constexpr int WN = PP_SP_NEWTON_WPB, WE = PP_SP_EDGE_WPB;
+  constexpr int WN = PP_SP_NEWTON_WPB, WE = PP_SP_EDGE_WPB, CS = PP_SP_BUCKETS + 1;
   HandsArgs A = A0;
   const int N = A.num_envs, nsub = A.n_substeps;
-  constexpr int CS = PP_SP_BUCKETS + 1;
   cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)nsub * CS, stream);
   configure_kernel<WN, PP_SPLIT_NEWTON>();
+  configure_kernel<WE, PP_SPLIT_PRO>();
+  configure_kernel<WE, PP_SPLIT_FIN>();
   const size_t smem = sizeof(WarpShared);
-  const int grid = std::min((N + WN - 1) / WN, sms * (10 / WN));
-  int launches = 0;
+  const int grid_n = std::min((N + WN - 1) / WN, sms * (10 / WN)), grid_e = (N + WE - 1) / WE;
+  A.sp_list_out = list; A.sp_list_in = list;
   for (int s = 0; s < nsub; s++) {
+    // substep s's prologue: on its own first, then on the tail of the launch that finishes substep s - 1
+    A.sub_index = s ? s - 1 : 0; A.sp_chain = s ? 1 : 0;
+    A.sp_count_out = counts + CS * s;
+    if (s == 0) pp_hands_step_kernel<WE, PP_SPLIT_PRO><<<grid_e, 32 * WE, smem * WE, stream>>>(A, 0);
+    else pp_hands_step_kernel<WE, PP_SPLIT_FIN><<<grid_e, 32 * WE, smem * WE, stream>>>(A, 0);
     A.sub_index = s;
-    A.sp_list_out = list; A.sp_count_out = counts + CS * s;
-    A.sp_list_in = list; A.sp_count_in = counts + CS * s; A.sp_cursor = counts + CS * s + PP_SP_BUCKETS;
-    launches += launch_wpb<WE, PP_SPLIT_PRO>(A, stream, 0, N);
-    pp_hands_step_kernel<WN, PP_SPLIT_NEWTON><<<grid, 32 * WN, smem * WN, stream>>>(A, 0);
-    launches += 1 + launch_wpb<WE, PP_SPLIT_FIN>(A, stream, 0, N);
+    A.sp_count_in = counts + CS * s; A.sp_cursor = counts + CS * s + PP_SP_BUCKETS;
+    pp_hands_step_kernel<WN, PP_SPLIT_NEWTON><<<grid_n, 32 * WN, smem * WN, stream>>>(A, 0);
   }
-  return launches;
+  A.sub_index = nsub - 1; A.sp_chain = 0;
+  pp_hands_step_kernel<WE, PP_SPLIT_FIN><<<grid_e, 32 * WE, smem * WE, stream>>>(A, 0);
+  return 2 * nsub + 1;
 }
 #else
 #ifndef PP_WPB
