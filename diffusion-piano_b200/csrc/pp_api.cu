@@ -361,6 +361,14 @@ extern "C" int pp_create(const pp_model* model, const pp_config* cfg, pp_env** o
   CUDA_OK(dalloc(&e->d_actions, (size_t)N * e->action_dim)); CUDA_OK(dalloc(&e->d_obs, (size_t)N * e->obs_dim));
   CUDA_OK(dalloc(&e->d_reward, N)); CUDA_OK(dalloc(&e->d_terms, (size_t)N * 5));
   CUDA_OK(dalloc(&e->d_discount, N)); CUDA_OK(dalloc(&e->d_done, N)); CUDA_OK(dalloc(&e->d_mask, N));
+  // test knob: PP_SCHEDULE=1|2|3 makes that launch shape the handle's initial one (the GPU suite is run once per shape)
+  if (const char* v = getenv("PP_SCHEDULE"))
+    if (cfg->task == PP_TASK_PIANO_WITH_SHADOW_HANDS && atoi(v) >= PP_SCHED_LOCKSTEP && atoi(v) <= PP_SCHED_COMPACTED) {
+      e->sched_mode = atoi(v); e->tuned = true;
+      e->block_envs = e->sched_mode == PP_SCHED_DIVERGENT ? 10 : 2;
+      e->sort_work = e->sched_mode == PP_SCHED_DIVERGENT;
+      e->compacted = e->sched_mode == PP_SCHED_COMPACTED;
+    }
   *out = e;
   int r = pp_reset(e, nullptr, nullptr, nullptr);
   if (r != PP_OK) return r;
@@ -525,6 +533,8 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
         CUDA_OK(dalloc(&e->sp_skip, N));
         CUDA_OK(dalloc(&e->sp_list, N * PP_SP_BUCKETS));
         CUDA_OK(dalloc(&e->sp_counts, (size_t)c.n_substeps * (PP_SP_BUCKETS + 1)));
+        // dalloc's cudaMemset runs on the legacy default stream, which a non-blocking stream (pp_step_host's) does not wait for
+        CUDA_OK(cudaDeviceSynchronize());
       }
       A.sp_regs = e->sp_regs; A.sp_smem = e->sp_smem; A.sp_skip = e->sp_skip;
       e->launches += pp_launch_hands_split(A, s, e->sms, e->sp_list, e->sp_counts);

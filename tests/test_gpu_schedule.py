@@ -28,7 +28,8 @@ def _run(schedule, n=333, steps=20):
     return out, sched, cnt.cpu().numpy()
 
 
-def test_schedules_give_identical_results():
+def test_schedules_give_identical_results(monkeypatch):
+    monkeypatch.delenv("PP_SCHEDULE", raising=False)  # the suite-wide knob (pp_create) would replace "auto"
     import torch
 
     if not torch.cuda.is_available():
