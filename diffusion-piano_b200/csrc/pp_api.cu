@@ -522,6 +522,11 @@ static int launch(pp_env* e, int mode, const uint8_t* mask, const float* actions
         e->sort_work = sort = best == 1;
         e->compacted = compacted = best == 2;
         e->tuned = true;
+        if (!e->compacted && e->sp_regs) {  // the parked-state buffers (30 KB per env) were only needed for the timing
+          cudaStreamSynchronize(s);
+          for (void* p : {(void*)e->sp_regs, (void*)e->sp_smem, (void*)e->sp_skip, (void*)e->sp_list, (void*)e->sp_counts}) cudaFree(p);
+          e->sp_regs = nullptr; e->sp_smem = nullptr; e->sp_skip = nullptr; e->sp_list = nullptr; e->sp_counts = nullptr;
+        }
       }
     }
     if (compacted && full && mode == PP_MODE_STEP) {
