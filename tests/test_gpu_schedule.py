@@ -81,3 +81,33 @@ def test_compacted_schedule_with_resets_and_options():
     for a, b in zip(outs["lockstep"], outs["compacted"]):
         for x, y in zip(a, b):
             np.testing.assert_array_equal(x, y)
+
+
+@pytest.mark.parametrize("n", [1, 9, 10, 11, 148 * 10 + 1, 1999])
+def test_compacted_schedule_batch_sizes(n, monkeypatch):
+    """Batch sizes around the block shape (10 envs) and the persistent grid (one block per SM): spare warps in the last
+    block, fewer envs than warps, more blocks than SMs. Two handles step at the same time on different streams (the
+    host-buffer API runs on the handle's own non-blocking stream)."""
+    import torch
+    from diffusion_piano_b200 import music, suite
+
+    monkeypatch.delenv("PP_SCHEDULE", raising=False)
+    task = suite.PianoWithShadowHands(music.load("CMajorScaleTwoHands"), n_steps_lookahead=1)
+    ref = suite.BatchedEnvironment(task, n, canonical_actions=True, schedule="lockstep")
+    dev = suite.BatchedEnvironment(task, n, canonical_actions=True, schedule="compacted")
+    host = suite.BatchedEnvironment(task, n, canonical_actions=True, schedule="compacted")
+    ref.reset_device(); dev.reset_device(); host.reset()
+    rng = np.random.RandomState(n)
+    for _ in range(4):
+        a = rng.uniform(-1, 1, (n, 45)).astype(np.float32)
+        at = torch.as_tensor(a, device="cuda")
+        o_d, r_d, d_d, t_d, _ = dev.step_device(at)  # asynchronous: still running while `host` steps
+        o_h, r_h, d_h = host.step(a)
+        o_r, r_r, d_r, t_r, _ = ref.step_device(at)
+        flat = np.concatenate([o_h[k] for k, _ in sorted(host.layout.items(), key=lambda kv: kv[1][0])], axis=1)
+        assert torch.equal(o_d, o_r) and torch.equal(r_d, r_r) and torch.equal(t_d, t_r) and torch.equal(d_d, d_r)
+        np.testing.assert_array_equal(flat, o_r.cpu().numpy().astype(np.float64))
+        np.testing.assert_array_equal(r_h, r_r.cpu().numpy().astype(np.float64))
+        assert np.isfinite(flat).all()
+    for e in (ref, dev, host):
+        e.close()
