@@ -78,7 +78,7 @@ struct HandsArgs {
   int* sp_cursor;
 };
 constexpr int PP_SP_NREG = 64;
-constexpr int PP_SP_BUCKETS = 10;  // lists of the split schedule: dense fallback, then 8, 7, .. 0 cross-front contacts (LRC = 8)
+constexpr int PP_SP_BUCKETS = 12;  // lists of the split schedule: 11+, 10, .. 0 cross-front contacts, heaviest first
 
 void pp_launch_piano_only(const PianoOnlyArgs& A, cudaStream_t stream);
 // launches the step for envs [env_begin, env_begin + env_count) (env_count < 0: to the end); returns the number of kernels

@@ -550,12 +550,12 @@ __device__ __forceinline__ void sp_get(const float* r, int& k, bool& x) { x = r[
 #define SP_GET(x) sp_get(r_, k_, x);
 // what a Newton trip changes (the last one integrates q and v) ...
 #define PP_SP_RW(OP) OP(a[0]) OP(a[1]) OP(Ma[0]) OP(Ma[1]) OP(sMa) OP(sa) OP(jar[0]) OP(jar[1]) OP(jar[2]) OP(jar[3]) \
-  OP(zone_old) OP(iter) OP(ls_total) OP(euler) OP(q[0]) OP(q[1]) OP(v[0]) OP(v[1])
+  OP(zone_old) OP(iter) OP(ls_total) OP(euler) OP(dense_mode) OP(q[0]) OP(q[1]) OP(v[0]) OP(v[1])
 // ... and what the substep's prologue hands to the loop and to the finish
 #define PP_SP_RO(OP) OP(fs[0]) OP(fs[1]) OP(fsk[0]) OP(fsk[1]) OP(fsk[2]) OP(cD) OP(cmu) OP(fD[0]) OP(fD[1]) \
   OP(faref[0]) OP(faref[1]) OP(floss[0]) OP(floss[1]) OP(lsg[0]) OP(lsg[1]) OP(lD[0]) OP(lD[1]) OP(laref[0]) OP(laref[1]) \
   OP(sM) OP(sfs) OP(ssg) OP(sD) OP(saref) OP(ncon) OP(ndrop) OP(nslot) OP(my_nent) OP(my_slot) OP(nlr) OP(nefc) \
-  OP(lrb) OP(slot_lr_mask) OP(my_lr) OP(dense_mode) OP(slot_lr) OP(act_force[0]) OP(act_force[1])
+  OP(lrb) OP(slot_lr_mask) OP(my_lr) OP(slot_lr) OP(act_force[0]) OP(act_force[1])
 #define PP_SP_REGS() float* r_ = A.sp_regs + (size_t)env * PP_SP_NREG * 32 + lane; int k_ = 0
 #define PP_SP_SAVE_ALL() do { PP_SP_REGS(); PP_SP_RW(SP_PUT) PP_SP_RO(SP_PUT) } while (0)
 #define PP_SP_SAVE_RW() do { PP_SP_REGS(); PP_SP_RW(SP_PUT) } while (0)
@@ -1042,14 +1042,14 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         // A contact is "in front" when its jacobian lives on one root path (one finger chain + the
         // 4 root dofs) plus a key owned by that finger. Hand-hand contacts and contacts on a key
         // already owned by another finger couple two fronts: they are solved as a low-rank
-        // correction (at most LRC of them, the rest are dropped and counted).
+        // correction while the ranks of their active rows sum to LRR at most (else that trip factorises densely).
         const int n1_ = (ids >> 1) & 31;
         const int my_front = (ids & 1) * 8 + (n1_ >= 21 ? 4 : n1_ >= 16 ? 3 : n1_ >= 12 ? 2 : n1_ >= 8 ? 1 : 0);
         const int owner = __shfl_sync(FULL, my_front, __ffs(same) - 1);
         my_lr = lane < ncon && my_slot != -2 && (kind == 1 || dbg_all_lr || (wants && owner != my_front));
         lrb = __ballot_sync(FULL, my_lr);
         nlr = __popc(lrb);
-        dense_mode = nlr > LRC || dbg_dense;  // too many cross-finger contacts for the low-rank path
+        dense_mode = false;  // set by the trips that need the dense factorisation (rank of the low-rank part > LRR)
       }
       __syncwarp();
       if (lane < ncon && my_slot != -2) {
@@ -1186,7 +1186,7 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
       for (int h = 0; h < 2; h++) a[h] = (stick[h] && floss[h] > 0.f) ? faref[h] : acc[h];
       Ma[0] = Ma[1] = 0.f; sMa = 0.f;
       jar[0] = jar[1] = jar[2] = jar[3] = 0.f;
-      zone_old = 0;
+      zone_old = -1;
       // Ma at the warm start
 #pragma unroll
       for (int h = 0; h < 2; h++) if (L.dof) W.va[h * 26 + lane] = a[h];
@@ -1207,7 +1207,7 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         sp_copy_smem<true>(A, env, W, lane, offsetof(WarpShared, kq), sizeof(WarpShared));
         if (lane == 0) {
           // lists by the cost class of the env's trips: every cross-front contact adds 3 right-hand sides to each solve
-          const int k = dense_mode ? 0 : PP_SP_BUCKETS - 1 - min(nlr, PP_SP_BUCKETS - 2);
+          const int k = PP_SP_BUCKETS - 1 - min(nlr, PP_SP_BUCKETS - 1);
           A.sp_list_out[(size_t)k * A.num_envs + atomicAdd(A.sp_count_out + k, 1)] = env;
         }
         return;
@@ -1284,10 +1284,36 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
           for (int h = 0; h < 2; h++) grad[h] = L.dof ? (Ma[h] - fs[h] - ff[h] - lsg[h] * lf[h] - gj[h]) : 0.f;
           if (lane < nslot) sgrad = sMa - sfs - ssg * sf - gjs;
         }
+        // Rank of the low-rank part: W = V V^T per cross-front contact (3x3 Cholesky of the active pyramid rows' weight,
+        // rank <= 3; a contact none of whose rows is active has rank 0), columns U v_j. The multifrontal + Woodbury path
+        // takes any number of such contacts as long as their ranks sum to LRR at most - decided trip by trip, because a
+        // dense trip costs three times a low-rank one of full rank (profiles/r02_trip_cost_model.txt).
         int m = 0;
+        float V[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // lower 3x3: (00, 10, 20, 11, 21, 22)
+        unsigned bal[3] = {0u, 0u, 0u};
+        if (!euler && nlr > 0) {
+          if (my_lr) {
+            const float w0 = W.c_w[0][lane], w1 = W.c_w[1][lane], w2 = W.c_w[2][lane], w3 = W.c_w[3][lane], w4 = W.c_w[4][lane];
+            if (w0 > 0.f) {
+              const float l00 = sqrtf(w0), l10 = w1 / l00, l20 = w3 / l00;
+              const float d1 = w2 - l10 * l10;
+              const float l11 = d1 > 1e-6f * w2 ? sqrtf(d1) : 0.f;
+              const float l21 = l11 > 0.f ? -l20 * l10 / l11 : 0.f;
+              const float d2 = w4 - l20 * l20 - l21 * l21;
+              const float l22 = d2 > 1e-6f * w4 ? sqrtf(d2) : 0.f;
+              V[0] = l00; V[1] = l10; V[2] = l20; V[3] = l11; V[4] = l21; V[5] = l22;
+            }
+          }
+          bal[0] = __ballot_sync(FULL, V[0] != 0.f); bal[1] = __ballot_sync(FULL, V[3] != 0.f);
+          bal[2] = __ballot_sync(FULL, V[5] != 0.f);
+          m = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2]);
+        }
+        const bool dense_now = !euler && (dbg_dense || m > LRR);
+        dense_mode |= dense_now;  // diagnostic (counters[6]): the substep took the dense path at least once
         float p[2] = {0.f, 0.f}, sp = 0.f;
-        if (dense_mode && !euler) {
+        if (dense_now) {
           // ---- dense fallback: full Hessian of the 52 hand dofs, every contact as a clique
+          zone_old = -1;  // overwrites the slots' 1 / H_ss: the next multifrontal trip assembles H_t again
           float* Hd = W.a.s.Hd;
           for (int i = lane; i < 52 * 53 / 2; i += 32) Hd[i] = 0.f;
           for (int s = 0; s < nslot; s++) { W.a.s.Kcd[s][lane] = 0.f; if (lane + 32 < 52) W.a.s.Kcd[s][lane + 32] = 0.f; }
@@ -1378,7 +1404,7 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         // slots) only changes when an in-front contact row or a slot's limit row changes zone: kept otherwise
         bool redo = false;
         if (!euler) {
-          bool chg = iter == 0;
+          bool chg = zone_old < 0;  // nothing assembled yet (first trip, or the trip before factorised densely)
           int zone = 0;
           if (con_on && !my_lr) zone = (cc[0] != 0.f ? 1 : 0) | (cc[1] != 0.f ? 2 : 0) | (cc[2] != 0.f ? 4 : 0) | (cc[3] != 0.f ? 8 : 0);
           if (lane < nslot && sc != 0.f) zone |= 16;
@@ -1500,31 +1526,12 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         }
         // ---- right-hand sides. Row 0: -grad (Euler: f_smooth + f_constraint = M qacc); rows 1..m:
         // sqrt(D) J_r^T of the active rows of the low-rank contacts.
-        float V[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // lower 3x3: (00, 10, 20, 11, 21, 22)
-        unsigned bal[3] = {0u, 0u, 0u};
         int vrow[3] = {0, 0, 0};
         float (*Z)[ZS] = W.a.s.Z;
         const float sb = -sgrad;
         {
-          // W = V V^T (3x3 Cholesky of the active pyramid rows' weight, rank <= 3): columns U v_j
-          if (!euler && nlr > 0) {
-            if (my_lr) {
-              const float w0 = W.c_w[0][lane], w1 = W.c_w[1][lane], w2 = W.c_w[2][lane], w3 = W.c_w[3][lane], w4 = W.c_w[4][lane];
-              if (w0 > 0.f) {
-                const float l00 = sqrtf(w0), l10 = w1 / l00, l20 = w3 / l00;
-                const float d1 = w2 - l10 * l10;
-                const float l11 = d1 > 1e-6f * w2 ? sqrtf(d1) : 0.f;
-                const float l21 = l11 > 0.f ? -l20 * l10 / l11 : 0.f;
-                const float d2 = w4 - l20 * l20 - l21 * l21;
-                const float l22 = d2 > 1e-6f * w4 ? sqrtf(d2) : 0.f;
-                V[0] = l00; V[1] = l10; V[2] = l20; V[3] = l11; V[4] = l21; V[5] = l22;
-              }
-            }
-            bal[0] = __ballot_sync(FULL, V[0] != 0.f); bal[1] = __ballot_sync(FULL, V[3] != 0.f);
-            bal[2] = __ballot_sync(FULL, V[5] != 0.f);
-            m = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2]);
+          if (!euler && nlr > 0)
             for (int i = lane; i < m * ZS; i += 32) (&Z[1][0])[i] = 0.f;
-          }
 #pragma unroll
           for (int h = 0; h < 2; h++) if (L.dof) Z[0][h * 26 + lane] = euler ? Ma[h] : -grad[h];
           if (lane < nslot) Z[0][52 + lane] = euler ? 0.f : sb;
