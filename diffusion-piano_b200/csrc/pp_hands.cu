@@ -1284,14 +1284,14 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
           for (int h = 0; h < 2; h++) grad[h] = L.dof ? (Ma[h] - fs[h] - ff[h] - lsg[h] * lf[h] - gj[h]) : 0.f;
           if (lane < nslot) sgrad = sMa - sfs - ssg * sf - gjs;
         }
-        // Rank of the low-rank part: W = V V^T per cross-front contact (3x3 Cholesky of the active pyramid rows' weight,
-        // rank <= 3; a contact none of whose rows is active has rank 0), columns U v_j. The multifrontal + Woodbury path
-        // takes any number of such contacts as long as their ranks sum to LRR at most - decided trip by trip, because a
-        // dense trip costs three times a low-rank one of full rank (profiles/r02_trip_cost_model.txt).
+        // The multifrontal + Woodbury path takes any number of cross-front contacts as long as the ranks of their active
+        // rows' weights (W = V V^T per contact, rank <= 3; 0 when no row is active) sum to LRR at most - decided trip by
+        // trip, because a dense trip costs three times a low-rank one of full rank (profiles/r02_trip_cost_model.txt).
+        // Only counted here, and only when there are more than LRC such contacts; V itself is built with the right-hand sides.
         int m = 0;
-        float V[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // lower 3x3: (00, 10, 20, 11, 21, 22)
-        unsigned bal[3] = {0u, 0u, 0u};
-        if (!euler && nlr > 0) {
+        bool dense_now = dbg_dense && !euler;
+        if (!euler && nlr > LRC) {
+          int rk = 0;
           if (my_lr) {
             const float w0 = W.c_w[0][lane], w1 = W.c_w[1][lane], w2 = W.c_w[2][lane], w3 = W.c_w[3][lane], w4 = W.c_w[4][lane];
             if (w0 > 0.f) {
@@ -1300,15 +1300,11 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
               const float l11 = d1 > 1e-6f * w2 ? sqrtf(d1) : 0.f;
               const float l21 = l11 > 0.f ? -l20 * l10 / l11 : 0.f;
               const float d2 = w4 - l20 * l20 - l21 * l21;
-              const float l22 = d2 > 1e-6f * w4 ? sqrtf(d2) : 0.f;
-              V[0] = l00; V[1] = l10; V[2] = l20; V[3] = l11; V[4] = l21; V[5] = l22;
+              rk = 1 + (l11 != 0.f ? 1 : 0) + (d2 > 1e-6f * w4 ? 1 : 0);
             }
           }
-          bal[0] = __ballot_sync(FULL, V[0] != 0.f); bal[1] = __ballot_sync(FULL, V[3] != 0.f);
-          bal[2] = __ballot_sync(FULL, V[5] != 0.f);
-          m = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2]);
+          dense_now |= (int)wsum((float)rk) > LRR;
         }
-        const bool dense_now = !euler && (dbg_dense || m > LRR);
         dense_mode |= dense_now;  // diagnostic (counters[6]): the substep took the dense path at least once
         float p[2] = {0.f, 0.f}, sp = 0.f;
         if (dense_now) {
@@ -1526,12 +1522,31 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         }
         // ---- right-hand sides. Row 0: -grad (Euler: f_smooth + f_constraint = M qacc); rows 1..m:
         // sqrt(D) J_r^T of the active rows of the low-rank contacts.
+        float V[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // lower 3x3: (00, 10, 20, 11, 21, 22)
+        unsigned bal[3] = {0u, 0u, 0u};
         int vrow[3] = {0, 0, 0};
         float (*Z)[ZS] = W.a.s.Z;
         const float sb = -sgrad;
         {
-          if (!euler && nlr > 0)
+          // W = V V^T (3x3 Cholesky of the active pyramid rows' weight, rank <= 3): columns U v_j
+          if (!euler && nlr > 0) {
+            if (my_lr) {
+              const float w0 = W.c_w[0][lane], w1 = W.c_w[1][lane], w2 = W.c_w[2][lane], w3 = W.c_w[3][lane], w4 = W.c_w[4][lane];
+              if (w0 > 0.f) {
+                const float l00 = sqrtf(w0), l10 = w1 / l00, l20 = w3 / l00;
+                const float d1 = w2 - l10 * l10;
+                const float l11 = d1 > 1e-6f * w2 ? sqrtf(d1) : 0.f;
+                const float l21 = l11 > 0.f ? -l20 * l10 / l11 : 0.f;
+                const float d2 = w4 - l20 * l20 - l21 * l21;
+                const float l22 = d2 > 1e-6f * w4 ? sqrtf(d2) : 0.f;
+                V[0] = l00; V[1] = l10; V[2] = l20; V[3] = l11; V[4] = l21; V[5] = l22;
+              }
+            }
+            bal[0] = __ballot_sync(FULL, V[0] != 0.f); bal[1] = __ballot_sync(FULL, V[3] != 0.f);
+            bal[2] = __ballot_sync(FULL, V[5] != 0.f);
+            m = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2]);
             for (int i = lane; i < m * ZS; i += 32) (&Z[1][0])[i] = 0.f;
+          }
 #pragma unroll
           for (int h = 0; h < 2; h++) if (L.dof) Z[0][h * 26 + lane] = euler ? Ma[h] : -grad[h];
           if (lane < nslot) Z[0][52 + lane] = euler ? 0.f : sb;
