@@ -1,7 +1,8 @@
 """Warp-stall samples of an `ncu --set full --import-source on` report by source region and stall reason.
 
-usage: python tools/ncu_stalls.py <report.ncu-rep> <libpiano_step.so> <kernel substring> [bucket lines] [top N]
-Lines are the OUTERMOST call site of inlined code (nvdisasm -gi), like tools/ncu_lines.py.
+usage: python tools/ncu_stalls.py <report.ncu-rep> <libpiano_step.so> <kernel substring> [bucket lines] [top N] [max line]
+Lines are the OUTERMOST call site of inlined code (nvdisasm -gi), like tools/ncu_lines.py; with [max line], the outermost
+one BELOW that line (the step body is itself inlined into the kernel wrappers near the end of pp_hands.cu).
 """
 import csv
 import re
@@ -19,21 +20,26 @@ def main():
     rep, so, kern = sys.argv[1:4]
     bucket = int(sys.argv[4]) if len(sys.argv) > 4 else 20
     top = int(sys.argv[5]) if len(sys.argv) > 5 else 40
+    max_line = int(sys.argv[6]) if len(sys.argv) > 6 else 1 << 30
     tmp = Path(tempfile.mkdtemp())
     subprocess.run(["cuobjdump", "-xelf", "all", str(Path(so).resolve())], cwd=tmp, check=True, capture_output=True)
     lines = None
     for cubin in tmp.glob("*.cubin"):
         sass = subprocess.run(["nvdisasm", "-gi", "-c", str(cubin)], capture_output=True, text=True).stdout.splitlines()
-        cur, infunc, out = None, False, []
+        cur, infunc, out, fresh = None, False, [], True
         for ln in sass:
             if ".section" in ln and ".text." in ln:
                 infunc = kern in ln
             m = re.search(r'//## File ".*?([^/"]+)", line (\d+)', ln)
             if m:
-                cur = (m.group(1), int(m.group(2)))
+                if int(m.group(2)) < max_line or cur is None or fresh:
+                    cur = (m.group(1), int(m.group(2)))
+                fresh = False
                 continue
-            if infunc and re.match(r"\s+/\*[0-9a-f]{4,}\*/", ln):
-                out.append(cur)
+            if re.match(r"\s+/\*[0-9a-f]{4,}\*/", ln):
+                fresh = True  # the next //## File line starts a new inline chain
+                if infunc:
+                    out.append(cur)
         if out and (lines is None or len(out) > len(lines)):
             lines = out
     raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
