@@ -1214,7 +1214,9 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
       }
       } else {
         PP_SP_LOAD_ALL();
-        sp_copy_smem<false>(A, env, W, lane, offsetof(WarpShared, kq), sizeof(WarpShared));  // all behind the phase union
+        // the Newton loop needs everything behind the phase union, the finish only the key state and the key -> slot map
+        sp_copy_smem<false>(A, env, W, lane, offsetof(WarpShared, kq),
+                            MODE == PP_SPLIT_FIN ? offsetof(WarpShared, slot_key) : sizeof(WarpShared));
         __syncwarp();
       }
       const bool con_on = lane < ncon && my_slot != -2;
