@@ -586,6 +586,13 @@ __device__ __forceinline__ void sp_copy_smem(const HandsArgs& A, int env, WarpSh
 // the list whenever they are done with one, PP_SPLIT_FIN = the rest of the substep and, after the last one, the task
 // epilogue. Same code, same arithmetic: the three kernels are this function with the other phases compiled out.
 constexpr int PP_SPLIT_PRO = 1, PP_SPLIT_NEWTON = 2, PP_SPLIT_FIN = 3;
+// diagnostic build -DPP_SP_TIMING (tools/trip_cost_model.py): the Newton kernel leaves the cycles of an env's trips in
+// counters 1, 3, 5, 6, which the finish then keeps
+#ifdef PP_SP_TIMING
+constexpr bool kSpTiming = true;
+#else
+constexpr bool kSpTiming = false;
+#endif
 template <int WPB, int MODE>
 __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W, const int env) {
   const int lane = threadIdx.x & 31;
@@ -1824,8 +1831,6 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         if ((!changed && fabsf(alpha - 1.f) < 1e-3f) || iter >= maxit) euler = true;
       }
       if (MODE == PP_SPLIT_NEWTON) {  // the loop is over: the finish kernel takes the env from here
-#ifdef PP_SP_TIMING
-#endif
         PP_SP_SAVE_RW();
 #ifdef PP_SP_TIMING
         {
@@ -1909,14 +1914,8 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
         }
         if (lane == 0) {
           int* cn = A.counters + (size_t)env * 8;
-          cn[0] = cnt_ncon; cn[2] = cnt_iter;
-#ifndef PP_SP_TIMING
-          cn[1] = cnt_nefc; cn[3] = cnt_drop;
-#endif
-          cn[4] = sum_iter; cn[7] = sum_coupled;
-#ifndef PP_SP_TIMING
-          cn[5] = sum_ls; cn[6] = sum_dense;
-#endif
+          cn[0] = cnt_ncon; cn[2] = cnt_iter; cn[4] = sum_iter; cn[7] = sum_coupled;
+          if (!kSpTiming) { cn[1] = cnt_nefc; cn[3] = cnt_drop; cn[5] = sum_ls; cn[6] = sum_dense; }
         }
         if (!A.sp_chain) return;  // chained: straight on into the next substep's prologue, which ends this launch
       }
@@ -2096,17 +2095,8 @@ __device__ __forceinline__ void hands_step_env(const HandsArgs& A, WarpShared& W
     A.sustain[env] = sustain;
     A.needs_reset[env] = done ? 1 : 0;
     int* cn = A.counters + (size_t)env * 8;
-    cn[0] = cnt_ncon; cn[2] = cnt_iter;
-#ifndef PP_SP_TIMING
-    cn[1] = cnt_nefc; cn[3] = cnt_drop;
-#else
-    if (MODE == 0) { cn[1] = cnt_nefc; cn[3] = cnt_drop; }
-#endif
-    cn[4] = sum_iter; cn[7] = sum_coupled;
-#ifdef PP_SP_TIMING
-    if (MODE == 0)
-#endif
-    { cn[5] = sum_ls; cn[6] = sum_dense; }
+    cn[0] = cnt_ncon; cn[2] = cnt_iter; cn[4] = sum_iter; cn[7] = sum_coupled;
+    if (!kSpTiming || MODE == 0) { cn[1] = cnt_nefc; cn[3] = cnt_drop; cn[5] = sum_ls; cn[6] = sum_dense; }
     if (A.mode == PP_MODE_STEP) {
       float terms[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
       if (!do_reset) {
