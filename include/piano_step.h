@@ -167,7 +167,7 @@ int pp_get_diag(pp_env *env, float *qacc_dev, float *actuator_force_dev,
  *                       SM whose warps take the next env of a list whenever their env's loop is over, the lists
  *                       ordered by cost class (cross-finger contacts = right-hand sides per solve): no warp idles
  *                       while a block-mate iterates, and the block's warps still run the same trip of the loop
- *                       together. Best for large batches with per-env actions (1.6x the divergent shape at 16384);
+ *                       together. Best for batches of thousands of envs with per-env actions (1.2x the divergent shape at 4096 envs, 1.4x at 16384);
  *   PP_SCHED_AUTO       (default) times the three in turn on full-batch steps 4..15 of the handle (CUDA events) and
  *                       keeps the lockstep shape unless another is 3 % faster. Results are identical in every mode:
  *                       an env's result never depends on its block or launch. pp_schedule_in_force = the shape the
